@@ -1,0 +1,251 @@
+"""CPU oracle for the ProtoSeg prototype head: a numpy restatement of the reference algorithm.
+
+TEST INFRASTRUCTURE.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs may import this; the product package never does.
+
+Parity status: PINNED — every function here is checked in tests/test_oracle_golden.py against
+fixtures produced by running the unmodified reference (oracle/make_golden.py -> tests/golden/).
+
+Reference lines restated:
+  l2_distances           model.py:203-221   (PPNet._l2_convolution, expanded ||z-p||^2, relu)
+  distance_2_similarity  model.py:231-237   ('log': log((d+1)/(d+eps)), 'linear': -d)
+  head_forward           model.py:259-283   (patch branch: NCHW->(M,N), similarity, last layer)
+  step_loss              segmentation/module.py:143-222 (CE on non-void, KLD on distances, masked L1)
+  step_grads             autograd of the above (module.py:236), written out analytically
+  patch_class_mask       segmentation/push.py:201-230 (pixel -> patch via int(i / (H/h)))
+  push_search_image      segmentation/push.py:249-307 (class-filtered per-prototype argmin + RF box)
+  push_finalize          segmentation/push.py:142-152 (de-dup with np.unique(axis=0))
+"""
+import numpy as np
+
+EPS = 1e-4  # model.py:50
+
+
+def l2_distances(z, P, dtype=np.float32):
+    """z (B,K,h,w), P (N,K) -> d (B,N,h,w) = relu(sum z^2 - 2 z.p + sum p^2)   [model.py:207-219]"""
+    z = z.astype(dtype)
+    P = P.astype(dtype)
+    B, K, h, w = z.shape
+    zf = z.reshape(B, K, h * w)
+    x2 = (zf * zf).sum(axis=1, dtype=dtype)                     # (B,hw)   conv2d(x**2, ones)
+    p2 = (P * P).sum(axis=1, dtype=dtype)                       # (N,)
+    xp = np.einsum('nk,bkm->bnm', P, zf).astype(dtype)          # conv2d(x, prototypes)
+    inter = (-2 * xp + p2[None, :, None]).astype(dtype)
+    d = np.maximum(x2[:, None, :] + inter, 0).astype(dtype)
+    return d.reshape(B, P.shape[0], h, w)
+
+
+def distance_2_similarity(d, mode='log', eps=EPS):
+    if mode == 'log':
+        return np.log((d + d.dtype.type(1)) / (d + d.dtype.type(eps)))
+    if mode == 'linear':
+        return -d
+    raise ValueError(mode)
+
+
+def head_forward(z, P, W, mode='log', dtype=np.float32):
+    """-> logits (B,h,w,C), distances (B,N,h,w), activations (M,N)   [model.py:264-283]"""
+    d = l2_distances(z, P, dtype)
+    B, N, h, w = d.shape
+    dv = np.ascontiguousarray(d.transpose(0, 2, 3, 1)).reshape(-1, N)
+    act = distance_2_similarity(dv, mode)
+    logits = (act @ W.astype(dtype).T).astype(dtype)
+    return logits.reshape(B, h, w, -1), d, act
+
+
+def class_identity(N, C):
+    """prototype j belongs to class j // (N/C)   [model.py:66-71]"""
+    ident = np.zeros((N, C), dtype=np.float64)
+    per = N // C
+    for c in range(C):
+        ident[c * per:(c + 1) * per, c] = 1
+    return ident
+
+
+def _logsumexp(a, axis):
+    m = a.max(axis=axis, keepdims=True)
+    return (m + np.log(np.exp(a - m).sum(axis=axis, keepdims=True))).squeeze(axis)
+
+
+def kld_groups(target_img, C):
+    """The (image, label) groups module.py:169-178 loops over: labels taken BEFORE the void shift."""
+    for b in range(target_img.shape[0]):
+        for cls in np.unique(target_img[b]):
+            if cls < 0 or cls >= C:
+                continue
+            yield b, int(cls), np.nonzero(target_img[b] == cls)[0]
+
+
+def step_loss(z, P, W, target, ignore_void=True, weights=(1.0, 0.25, 1e-4), ident=None,
+              dtype=np.float64, want_grads=True):
+    """fwd + CE + KLD + L1 (+ analytic backward).  target (B,h,w) int, already resized.
+
+    Returns dict(loss, cross_entropy, kld_loss, l1, n_correct, n_patches, [dz, dP, dW]).
+    module.py:143-222; the backward is what loss.backward() (module.py:236) yields.
+    """
+    w_ce, w_kld, w_l1 = weights
+    z = z.astype(dtype)
+    P = P.astype(dtype)
+    W = W.astype(dtype)
+    B, K, h, w = z.shape
+    N, C = P.shape[0], W.shape[0]
+    if ident is None:
+        ident = class_identity(N, C)
+    hw = h * w
+    M = B * hw
+    zf = z.reshape(B, K, hw).transpose(0, 2, 1).reshape(M, K)           # (M,K)
+    pre = (zf * zf).sum(1)[:, None] - 2 * zf @ P.T + (P * P).sum(1)[None, :]
+    d = np.maximum(pre, 0)                                              # (M,N)
+    s = np.log((d + 1) / (d + EPS))
+    logits = s @ W.T                                                    # (M,C)
+    tflat = target.reshape(-1).astype(np.int64)
+    target_img = target.reshape(B, hw).astype(np.int64)
+    if ignore_void:
+        keep = np.nonzero(tflat != 0)[0]
+        tt = tflat[keep] - 1
+    else:
+        keep = np.arange(M)
+        tt = tflat
+    lg = logits[keep]
+    lse = _logsumexp(lg, 1)
+    ce = float((lse - lg[np.arange(len(keep)), tt]).mean())
+    n_correct = int((lg.argmax(1) == tt).sum())
+
+    # KLD over distances (module.py:167-208)
+    terms = []   # (b, protos, pixel idx, i, j, kld)
+    d_img = d.reshape(B, hw, N)
+    for b, cls, pix in kld_groups(target_img, C):
+        protos = np.nonzero(ident[:, cls])[0]
+        if len(protos) < 2 or len(pix) < 2:
+            continue
+        a = d_img[b][np.ix_(pix, protos)]                               # (n, J) distances
+        la = a - _logsumexp(a, 0)[None, :]                              # log_softmax over pixels
+        q = np.exp(la)
+        for i in range(len(protos)):
+            for j in range(i + 1, len(protos)):
+                kld1 = (q[:, j] * (la[:, j] - la[:, i])).sum()          # kl_div(log_p1, log_p2, log_target)
+                kld2 = (q[:, i] * (la[:, i] - la[:, j])).sum()
+                terms.append((b, protos, pix, i, j, (kld1 + kld2) / 2.0, q, a))
+    if terms:
+        kvals = np.array([t[5] for t in terms])
+        kld_loss = float(np.exp(-kvals).mean())
+    else:
+        kld_loss = 0.0
+    l1_mask = 1 - ident.T
+    l1 = float(np.abs(W * l1_mask).sum())
+    loss = w_ce * ce + w_kld * kld_loss + w_l1 * l1
+    out = dict(loss=loss, cross_entropy=ce, kld_loss=kld_loss, l1=l1, n_correct=n_correct,
+               n_patches=int(len(keep)), logits=logits.reshape(B, h, w, C),
+               dist=d.reshape(B, hw, N).transpose(0, 2, 1).reshape(B, N, h, w))
+    if not want_grads:
+        return out
+
+    # ---- backward ----
+    dlogits = np.zeros((M, C), dtype=dtype)
+    sm = np.exp(lg - lse[:, None])
+    sm[np.arange(len(keep)), tt] -= 1
+    dlogits[keep] = sm * (w_ce / len(keep))
+    dW = dlogits.T @ s + w_l1 * np.sign(W) * l1_mask
+    Gd = (dlogits @ W) * (1 / (d + 1) - 1 / (d + EPS))
+    if terms:
+        T = len(terms)
+        Gk = np.zeros((B, hw, N), dtype=dtype)
+        for (b, protos, pix, i, j, kld, q, a) in terms:
+            c = w_kld * (-np.exp(-kld)) / T
+            delta = a[:, j] - a[:, i]
+            Ej = (q[:, j] * delta).sum()
+            Ei = (q[:, i] * delta).sum()
+            gj = 0.5 * (q[:, j] * (delta - Ej) + q[:, j] - q[:, i])
+            gi = 0.5 * (-q[:, i] * (delta - Ei) - q[:, j] + q[:, i])
+            Gk[b, pix, protos[j]] += c * gj
+            Gk[b, pix, protos[i]] += c * gi
+        Gd = Gd + Gk.reshape(M, N)
+    Gd = Gd * (pre > 0)                                                 # relu backward
+    rs = Gd.sum(1)
+    dzf = 2 * (rs[:, None] * zf - Gd @ P)
+    dP = 2 * (Gd.sum(0)[:, None] * P - Gd.T @ zf)
+    out.update(dz=dzf.reshape(B, hw, K).transpose(0, 2, 1).reshape(B, K, h, w), dP=dP, dW=dW,
+               dlogits=dlogits, Gd=Gd)
+    return out
+
+
+# ----------------------------------------------------------------------------- push
+def patch_luts(H, Wimg, h, w):
+    """pixel -> patch index with the reference's float expression int(pixel / (H / h))  [push.py:201-202,217,219]"""
+    ph = H / h
+    pw = Wimg / w
+    rows = np.array([int(i / ph) for i in range(H)], dtype=np.int32)
+    cols = np.array([int(j / pw) for j in range(Wimg)], dtype=np.int32)
+    return rows, cols
+
+
+def patch_class_mask(labels, h, w):
+    """labels (H,W) ints, 0 = void -> (h,w) uint32 bitmask: bit c set iff >=1 pixel of label c+1
+    falls in the patch footprint   [push.py:214-223]"""
+    H, Wimg = labels.shape
+    rows, cols = patch_luts(H, Wimg, h, w)
+    mask = np.zeros((h, w), dtype=np.uint32)
+    lab = labels.astype(np.int64)
+    bits = np.where(lab > 0, np.left_shift(np.uint32(1), np.clip(lab - 1, 0, 31).astype(np.uint32)),
+                    np.uint32(0)).astype(np.uint32)
+    np.bitwise_or.at(mask, (rows[:, None].repeat(Wimg, 1), cols[None, :].repeat(H, 0)), bits)
+    return mask
+
+
+def rf_box(patch_i, patch_j, H, Wimg, h, w):
+    """[push.py:288-292]"""
+    ph = H / h
+    pw = Wimg / w
+    return (int(patch_i * ph), int(patch_i * ph + ph) + 1, int(patch_j * pw), int(patch_j * pw + pw) + 1)
+
+
+def push_search_image(z_img, P, mask, proto_class, dist=None):
+    """One image: z (K,h,w), mask (h,w) uint32 -> per prototype (min distance, flat argmin or -1).
+    Ties resolve to the LOWEST flat patch index (the reference's order is set-hash order,
+    push.py:230,259-262 — SURVEY §7.4-6; exact in-image ties are logged by the tests)."""
+    K, h, w = z_img.shape
+    if dist is None:
+        dist = l2_distances(z_img[None], P)[0]
+    d = dist.reshape(P.shape[0], h * w)
+    mflat = mask.reshape(-1)
+    N = P.shape[0]
+    dmin = np.full(N, np.inf, dtype=np.float64)
+    amin = np.full(N, -1, dtype=np.int64)
+    for j in range(N):
+        cand = np.nonzero((mflat >> np.uint32(proto_class[j])) & np.uint32(1))[0]
+        if len(cand) == 0:
+            continue
+        k = np.argmin(d[j, cand])
+        dmin[j] = d[j, cand[k]]
+        amin[j] = cand[k]
+    return dmin, amin
+
+
+def push_search(z_imgs, P, labels, C):
+    """Whole dataset: strict '<' keeps the earliest image   [push.py:55-61,101-133,265-280]"""
+    n_img, K, h, w = z_imgs.shape
+    N = P.shape[0]
+    proto_class = (np.arange(N) // (N // C)).astype(np.int64)
+    gmin = np.full(N, np.inf)
+    gpatch = np.zeros((N, K))
+    gidx = np.full(N, -1, dtype=np.int64)          # img * h*w + patch
+    rf = np.full((N, 6), -1, dtype=np.int64)
+    H, Wimg = labels.shape[1:]
+    for i in range(n_img):
+        mask = patch_class_mask(labels[i], h, w)
+        dmin, amin = push_search_image(z_imgs[i], P, mask, proto_class)
+        for j in range(N):
+            if amin[j] >= 0 and dmin[j] < gmin[j]:
+                gmin[j] = dmin[j]
+                gidx[j] = i * h * w + amin[j]
+                pi, pj = divmod(int(amin[j]), w)
+                gpatch[j] = z_imgs[i][:, pi, pj]
+                rf[j] = (i,) + rf_box(pi, pj, H, Wimg, h, w) + (proto_class[j],)
+    return gmin, gpatch, gidx, rf
+
+
+def push_finalize(gpatch):
+    """np.unique(axis=0) de-dup   [push.py:147-149] -> (sorted unique_index, duplicate_idx)"""
+    _, unique_index = np.unique(gpatch, axis=0, return_index=True)
+    dup = [i for i in range(gpatch.shape[0]) if i not in unique_index]
+    return np.sort(unique_index), np.array(dup, dtype=np.int64)
