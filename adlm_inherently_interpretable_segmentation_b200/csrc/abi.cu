@@ -1,0 +1,219 @@
+// C ABI of libadlm_head.so (see include/adlm_head.h): argument checking, precision-mode dispatch,
+// error reporting.  No allocation, no synchronisation: every entry point only enqueues work on the
+// caller's stream.
+#include <atomic>
+#include <cstdarg>
+#include <cstring>
+
+#include "common.cuh"
+#include "tc_head.cuh"
+
+namespace adlm {
+
+static thread_local char g_err[512] = "";
+static std::atomic<unsigned long long> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+void count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+
+// ---- per-kernel event timing (bench.py roofline leg) ----
+static int g_time_tag = 0, g_time_cap = 0, g_time_n = 0;
+static cudaEvent_t* g_time_ev = nullptr;   // 2 per sample
+
+KernelTimer::KernelTimer(int tag, cudaStream_t st) : slot_(-1), st_(st) {
+  if (tag == g_time_tag && g_time_ev != nullptr && g_time_n < g_time_cap) {
+    slot_ = g_time_n++;
+    cudaEventRecord(g_time_ev[2 * slot_], st_);
+  }
+}
+KernelTimer::~KernelTimer() {
+  if (slot_ >= 0) cudaEventRecord(g_time_ev[2 * slot_ + 1], st_);
+}
+
+static int check_shape(const char* fn, int B, int K, int HW, int N, int C) {
+  if (B <= 0 || K <= 0 || HW <= 0 || N <= 0 || C <= 0) {
+    set_error("%s: non-positive size (B=%d K=%d HW=%d N=%d C=%d)", fn, B, K, HW, N, C);
+    return ADLM_E_INVALID;
+  }
+  if (K > ADLM_MAX_K) { set_error("%s: unsupported: K=%d > %d", fn, K, ADLM_MAX_K); return ADLM_E_UNSUPPORTED; }
+  if (C > ADLM_MAX_C) { set_error("%s: unsupported: C=%d > %d", fn, C, ADLM_MAX_C); return ADLM_E_UNSUPPORTED; }
+  if ((long long)B * HW >= (1ll << 31)) { set_error("%s: unsupported: B*HW >= 2^31", fn); return ADLM_E_UNSUPPORTED; }
+  return ADLM_OK;
+}
+
+int head_fwd_dispatch(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
+                      float* logits, float* dist, float* sim, int32_t* argmax, const StepExtras& ex,
+                      cudaStream_t st) {
+  switch (prec_mode) {
+    case ADLM_PREC_FP32:
+      return simt_head_fwd(s, z, P, W, logits, dist, sim, argmax, ex, st);
+    case ADLM_PREC_TF32:
+    case ADLM_PREC_TF32X3:
+      return tc_head_fwd(s, prec_mode, z, P, W, logits, dist, sim, argmax, ex, st);
+    default:
+      set_error("unknown prec_mode %d", prec_mode);
+      return ADLM_E_INVALID;
+  }
+}
+
+int head_bwd_dispatch(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
+                      const float* dlogits, const float* ddist, const float* dsim, float* dz, float* dP,
+                      float* dW, const StepExtras& ex, cudaStream_t st) {
+  switch (prec_mode) {
+    case ADLM_PREC_FP32:
+      return simt_head_bwd(s, z, P, W, dlogits, ddist, dsim, dz, dP, dW, ex, st);
+    case ADLM_PREC_TF32:
+    case ADLM_PREC_TF32X3:
+      return tc_head_bwd(s, prec_mode, z, P, W, dlogits, ddist, dsim, dz, dP, dW, ex, st);
+    default:
+      set_error("unknown prec_mode %d", prec_mode);
+      return ADLM_E_INVALID;
+  }
+}
+
+}  // namespace adlm
+
+using namespace adlm;
+
+extern "C" {
+
+const char* adlm_last_error(void) { return g_err; }
+int adlm_abi_version(void) { return ADLM_ABI_VERSION; }
+unsigned long long adlm_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int adlm_timing_begin(int kernel_tag, int max_samples) {
+  ADLM_CHECK_ARG(kernel_tag > 0 && max_samples > 0 && max_samples <= (1 << 20), "bad tag or sample count");
+  ADLM_CHECK_ARG(g_time_ev == nullptr, "timing already active");
+  g_time_ev = new cudaEvent_t[2 * (size_t)max_samples];
+  for (int i = 0; i < 2 * max_samples; ++i) ADLM_CUDA(cudaEventCreate(&g_time_ev[i]));
+  g_time_cap = max_samples;
+  g_time_n = 0;
+  g_time_tag = kernel_tag;
+  return ADLM_OK;
+}
+
+int adlm_timing_end(float* ms_out) {
+  ADLM_CHECK_ARG(g_time_ev != nullptr && ms_out != nullptr, "timing not active or null output");
+  const int n = g_time_n;
+  g_time_tag = 0;
+  int rc = n;
+  for (int i = 0; i < n; ++i) {
+    cudaError_t e = cudaEventSynchronize(g_time_ev[2 * i + 1]);
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&ms_out[i], g_time_ev[2 * i], g_time_ev[2 * i + 1]);
+    if (e != cudaSuccess) { set_error("adlm_timing_end: %s", cudaGetErrorString(e)); rc = ADLM_E_CUDA; break; }
+  }
+  for (int i = 0; i < 2 * g_time_cap; ++i) cudaEventDestroy(g_time_ev[i]);
+  delete[] g_time_ev;
+  g_time_ev = nullptr;
+  g_time_cap = g_time_n = 0;
+  return rc;
+}
+
+int adlm_head_fwd(const float* z, int B, int K, int HW, const float* P, const float* W, int N, int C,
+                  float eps, int act_mode, int prec_mode, float* logits, float* dist, float* sim,
+                  int32_t* argmax, void* stream) {
+  int rc = check_shape(__func__, B, K, HW, N, C);
+  if (rc != ADLM_OK) return rc;
+  ADLM_CHECK_ARG(z && P && W && logits, "z, P, W and logits must be non-null");
+  ADLM_CHECK_ARG(act_mode == ADLM_ACT_LOG || act_mode == ADLM_ACT_LINEAR, "unknown act_mode");
+  HeadShape s{B, K, HW, N, C, eps, act_mode};
+  return head_fwd_dispatch(s, prec_mode, z, P, W, logits, dist, sim, argmax, StepExtras{}, (cudaStream_t)stream);
+}
+
+int adlm_head_bwd(const float* z, int B, int K, int HW, const float* P, const float* W, int N, int C,
+                  float eps, int act_mode, int prec_mode, const float* dlogits, const float* ddist,
+                  const float* dsim, float* dz, float* dP, float* dW, void* stream) {
+  int rc = check_shape(__func__, B, K, HW, N, C);
+  if (rc != ADLM_OK) return rc;
+  ADLM_CHECK_ARG(z && P && W, "z, P and W must be non-null");
+  ADLM_CHECK_ARG(dlogits || ddist || dsim, "at least one upstream gradient is required");
+  ADLM_CHECK_ARG(dz || dP || dW, "at least one output gradient is required");
+  ADLM_CHECK_ARG(act_mode == ADLM_ACT_LOG || act_mode == ADLM_ACT_LINEAR, "unknown act_mode");
+  HeadShape s{B, K, HW, N, C, eps, act_mode};
+  return head_bwd_dispatch(s, prec_mode, z, P, W, dlogits, ddist, dsim, dz, dP, dW, StepExtras{},
+                           (cudaStream_t)stream);
+}
+
+size_t adlm_step_workspace_bytes(int B, int K, int HW, int N, int C) {
+  (void)K;
+  if (B <= 0 || HW <= 0 || N <= 0 || C <= 0) return 0;
+  return step_workspace_bytes(B, HW, N, C);
+}
+
+int adlm_step_fwd_bwd(const float* z, int B, int K, int HW, const float* P, const float* W, int N, int C,
+                      float eps, int prec_mode, const int32_t* target, const int32_t* proto_class,
+                      int ignore_void, float w_ce, float w_kld, float w_l1, float grad_scale,
+                      const int32_t* global_counts,
+                      float* logits_out, int32_t* argmax_out, float* dz, float* dP, float* dW,
+                      double* scalars, void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = check_shape(__func__, B, K, HW, N, C);
+  if (rc != ADLM_OK) return rc;
+  ADLM_CHECK_ARG(z && P && W && target && proto_class && scalars && workspace, "null pointer argument");
+  ADLM_CHECK_ARG(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  if (workspace_bytes < step_workspace_bytes(B, HW, N, C)) {
+    set_error("%s: workspace too small (%zu < %zu)", __func__, workspace_bytes, step_workspace_bytes(B, HW, N, C));
+    return ADLM_E_WORKSPACE;
+  }
+  HeadShape s{B, K, HW, N, C, eps, ADLM_ACT_LOG};
+  return step_fwd_bwd_impl(s, prec_mode, z, P, W, target, proto_class, ignore_void, w_ce, w_kld, w_l1,
+                           grad_scale, global_counts, logits_out, argmax_out, dz, dP, dW, scalars, workspace,
+                           (cudaStream_t)stream);
+}
+
+int adlm_step_counts(const int32_t* target, int B, int HW, const int32_t* proto_class, int N, int C,
+                     int ignore_void, int32_t* counts_out, void* workspace, size_t workspace_bytes,
+                     void* stream) {
+  ADLM_CHECK_ARG(target && proto_class && counts_out && workspace, "null pointer argument");
+  ADLM_CHECK_ARG(B > 0 && HW > 0 && N > 0 && C > 0, "non-positive size");
+  ADLM_CHECK_SUPPORTED(C <= ADLM_MAX_C, "C > 128");
+  ADLM_CHECK_ARG(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  if (workspace_bytes < step_workspace_bytes(B, HW, N, C)) {
+    set_error("%s: workspace too small", __func__);
+    return ADLM_E_WORKSPACE;
+  }
+  return step_counts_impl(target, B, HW, proto_class, N, C, ignore_void, counts_out, workspace,
+                          (cudaStream_t)stream);
+}
+
+int adlm_patch_class_mask(const uint8_t* labels, int n_img, int H, int Wimg, const int32_t* row_lut,
+                          const int32_t* col_lut, int h, int w, uint32_t* mask_out, void* stream) {
+  ADLM_CHECK_ARG(labels && row_lut && col_lut && mask_out, "null pointer argument");
+  ADLM_CHECK_ARG(n_img > 0 && H > 0 && Wimg > 0 && h > 0 && w > 0, "non-positive size");
+  ADLM_CHECK_SUPPORTED(n_img <= 65535, "n_img > 65535 per call (split the shard)");
+  ADLM_CHECK_SUPPORTED((size_t)w * sizeof(uint32_t) <= 48 * 1024, "feature map wider than 12288 patches");
+  return patch_class_mask_impl(labels, n_img, H, Wimg, row_lut, col_lut, h, w, mask_out, (cudaStream_t)stream);
+}
+
+int adlm_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mask, const float* P, int N,
+                   const int32_t* proto_class, long long patch_base, int prec_mode,
+                   unsigned long long* packed_min, void* stream) {
+  ADLM_CHECK_ARG(z && mask && P && proto_class && packed_min, "null pointer argument");
+  ADLM_CHECK_ARG(n_img > 0 && K > 0 && HW > 0 && N > 0 && patch_base >= 0, "bad size");
+  ADLM_CHECK_SUPPORTED(K <= ADLM_MAX_K, "K > 256");
+  ADLM_CHECK_SUPPORTED(patch_base + (long long)n_img * HW < (1ll << 32), "global patch id needs more than 32 bits");
+  switch (prec_mode) {
+    case ADLM_PREC_FP32:
+      return simt_push_scan(z, n_img, K, HW, mask, P, N, proto_class, patch_base, packed_min, (cudaStream_t)stream);
+    case ADLM_PREC_TF32:
+    case ADLM_PREC_TF32X3:
+      return tc_push_scan(z, n_img, K, HW, mask, P, N, proto_class, patch_base, prec_mode, packed_min,
+                          (cudaStream_t)stream);
+    default:
+      set_error("unknown prec_mode %d", prec_mode);
+      return ADLM_E_INVALID;
+  }
+}
+
+int adlm_push_gather(const float* z, int n_img, int K, int HW, long long patch_base,
+                     const unsigned long long* packed_min, int N, float* proto_out, void* stream) {
+  ADLM_CHECK_ARG(z && packed_min && proto_out, "null pointer argument");
+  ADLM_CHECK_ARG(n_img > 0 && K > 0 && HW > 0 && N > 0 && patch_base >= 0, "bad size");
+  return push_gather_impl(z, n_img, K, HW, patch_base, packed_min, N, proto_out, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,138 @@
+// Shared helpers for the ProtoSeg prototype-head kernels (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/adlm_head.h"
+
+namespace adlm {
+
+void set_error(const char* fmt, ...);
+void count_launch(int n = 1);
+
+#define ADLM_CHECK_ARG(cond, msg)                                   \
+  do {                                                              \
+    if (!(cond)) {                                                  \
+      adlm::set_error("%s: %s", __func__, msg);                     \
+      return ADLM_E_INVALID;                                        \
+    }                                                               \
+  } while (0)
+
+#define ADLM_CHECK_SUPPORTED(cond, msg)                             \
+  do {                                                              \
+    if (!(cond)) {                                                  \
+      adlm::set_error("%s: unsupported: %s", __func__, msg);        \
+      return ADLM_E_UNSUPPORTED;                                    \
+    }                                                               \
+  } while (0)
+
+#define ADLM_CUDA(call)                                                              \
+  do {                                                                               \
+    cudaError_t e__ = (call);                                                        \
+    if (e__ != cudaSuccess) {                                                        \
+      adlm::set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call,                   \
+                      cudaGetErrorString(e__));                                      \
+      return ADLM_E_CUDA;                                                            \
+    }                                                                                \
+  } while (0)
+
+#define ADLM_LAUNCH_CHECK()                                                          \
+  do {                                                                               \
+    adlm::count_launch();                                                            \
+    cudaError_t e__ = cudaGetLastError();                                            \
+    if (e__ != cudaSuccess) {                                                        \
+      adlm::set_error("%s:%d launch -> %s", __FILE__, __LINE__,                      \
+                      cudaGetErrorString(e__));                                      \
+      return ADLM_E_CUDA;                                                            \
+    }                                                                                \
+  } while (0)
+
+// RAII bracket used by the launchers: records events around the launch when bench.py asked for this tag
+struct KernelTimer {
+  KernelTimer(int tag, cudaStream_t st);
+  ~KernelTimer();
+  int slot_;
+  cudaStream_t st_;
+};
+
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// model.py:233 / :235 and their derivatives wrt d
+__device__ __forceinline__ float act_fwd(float d, float eps, int act_mode) {
+  if (act_mode == ADLM_ACT_LOG) return __logf(__fdividef(d + 1.0f, d + eps));
+  return -d;
+}
+__device__ __forceinline__ float act_fwd_precise(float d, float eps, int act_mode) {
+  if (act_mode == ADLM_ACT_LOG) return logf((d + 1.0f) / (d + eps));
+  return -d;
+}
+__device__ __forceinline__ float act_grad(float d, float eps, int act_mode) {
+  if (act_mode == ADLM_ACT_LOG) return 1.0f / (d + 1.0f) - 1.0f / (d + eps);
+  return -1.0f;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ---- launchers implemented in the .cu files -------------------------------------------------
+struct HeadShape {
+  int B, K, HW, N, C;
+  float eps;
+  int act_mode;
+};
+
+// optional extras of the fused step
+struct StepExtras {
+  const int32_t* target = nullptr;       // [B,HW] labels (un-shifted)
+  const int32_t* proto_class = nullptr;  // [N]
+  const int32_t* proto_rank = nullptr;   // [N] rank of the prototype inside its class
+  float* own_dist = nullptr;             // [B*HW, JMAX] fwd: distances to the label's own class
+  const float* own_grad = nullptr;       // [B*HW, JMAX] bwd: dL/d(own_dist) from the KLD term
+};
+
+int simt_head_fwd(const HeadShape& s, const float* z, const float* P, const float* W,
+                  float* logits, float* dist, float* sim, int32_t* argmax,
+                  const StepExtras& ex, cudaStream_t st);
+int simt_head_bwd(const HeadShape& s, const float* z, const float* P, const float* W,
+                  const float* dlogits, const float* ddist, const float* dsim,
+                  float* dz, float* dP, float* dW, const StepExtras& ex, cudaStream_t st);
+
+// precision-mode dispatch (abi.cu)
+int head_fwd_dispatch(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
+                      float* logits, float* dist, float* sim, int32_t* argmax, const StepExtras& ex,
+                      cudaStream_t st);
+int head_bwd_dispatch(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
+                      const float* dlogits, const float* ddist, const float* dsim, float* dz, float* dP,
+                      float* dW, const StepExtras& ex, cudaStream_t st);
+
+// fused step (loss.cu)
+struct StepWorkspace;
+size_t step_workspace_bytes(int B, int HW, int N, int C);
+int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
+                      const int32_t* target, const int32_t* proto_class, int ignore_void,
+                      float w_ce, float w_kld, float w_l1, float grad_scale, const int32_t* global_counts,
+                      float* logits_out, int32_t* argmax_out, float* dz, float* dP, float* dW,
+                      double* scalars, void* workspace, cudaStream_t st);
+int step_counts_impl(const int32_t* target, int B, int HW, const int32_t* proto_class, int N, int C,
+                     int ignore_void, int32_t* counts_out, void* workspace, cudaStream_t st);
+
+// push (push.cu)
+int patch_class_mask_impl(const uint8_t* labels, int n_img, int H, int Wimg, const int32_t* row_lut,
+                          const int32_t* col_lut, int h, int w, uint32_t* mask_out, cudaStream_t st);
+int simt_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mask, const float* P, int N,
+                   const int32_t* proto_class, long long patch_base, unsigned long long* packed_min,
+                   cudaStream_t st);
+int push_gather_impl(const float* z, int n_img, int K, int HW, long long patch_base,
+                     const unsigned long long* packed_min, int N, float* proto_out, cudaStream_t st);
+
+}  // namespace adlm

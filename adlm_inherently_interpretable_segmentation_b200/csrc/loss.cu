@@ -1,0 +1,467 @@
+// Loss side of the fused step: label histogram, cross entropy (+ its gradient), the KLD
+// prototype-diversity loss on distances (+ its gradient), masked L1, final scalars.
+//
+// Reference: segmentation/module.py:143-222.  Quirks kept on purpose:
+//   * KLD groups are keyed by the UN-shifted label (module.py:150,170-178): with ignore_void the
+//     void pixels (label 0) pair up with class-0 prototypes, label l with class l, label C is skipped;
+//   * the KLD runs on distances, not similarities (module.py:142,153);
+//   * groups with < 2 prototypes or < 2 pixels are skipped (module.py:186-188);
+//   * kld_loss = mean over all (image, label, pair) of exp(-(kl(p2||p1) + kl(p1||p2)) / 2).
+//
+// Algebra used (la = log_softmax over the group's pixels, q = exp(la), E_a[f] = sum_m q_a(m) f(m)):
+//   kl_div(la_i, la_j, log_target) = sum q_j (la_j - la_i)  =>  kld_ij = (E_j[d_j-d_i] - E_i[d_j-d_i]) / 2
+// so one J x J matrix A[a][b] = E_a[d_b] per group gives every pair.  Gradient wrt d_a(m):
+//   sum_b c_ab * ( q_a ((d_a - d_b) - (A[a][a] - A[a][b])) + q_a - q_b ),  c_ab = -(w/T) exp(-kld_ab) / 2.
+#include "common.cuh"
+
+namespace adlm {
+
+constexpr int JMAX = ADLM_MAX_PROTOS_PER_CLASS;
+// per-group table written by k_kld_stats and read by k_kld_grad
+constexpr int GT_LSE = 0;                  // [JMAX] log-sum-exp of each prototype's distances
+constexpr int GT_CSUM = JMAX;              // [JMAX] C_a = sum_b c_ab
+constexpr int GT_R = 2 * JMAX;             // [JMAX] R_a = sum_b c_ab (A[a][a] - A[a][b])
+constexpr int GT_C = 3 * JMAX;             // [JMAX][JMAX] c_ab
+constexpr int GT_VALID = 3 * JMAX + JMAX * JMAX;
+constexpr int GT_SIZE = GT_VALID + 8;      // floats per group (multiple of 8)
+
+int group_table_floats() { return GT_SIZE; }
+
+namespace {
+
+// hist[b][l], l in [0, C]; labels outside [0, C] are ignored everywhere.
+__global__ void k_label_hist(const int32_t* __restrict__ target, int HW, int C, int* __restrict__ hist) {
+  extern __shared__ int sh[];
+  const int b = blockIdx.y;
+  for (int i = threadIdx.x; i <= C; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  const int32_t* t = target + (size_t)b * HW;
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < HW; p += gridDim.x * blockDim.x) {
+    const int l = t[p];
+    if (l >= 0 && l <= C) atomicAdd(&sh[l], 1);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i <= C; i += blockDim.x)
+    if (sh[i]) atomicAdd(&hist[b * (C + 1) + i], sh[i]);
+}
+
+// counts[0] = number of CE patches, counts[1] = number of KLD terms; cls_count[c] = prototypes of class c.
+// Also zeroes the double accumulators.
+__global__ void k_loss_prepare(const int* __restrict__ hist, const int32_t* __restrict__ proto_class,
+                               int B, int C, int N, int ignore_void, int* __restrict__ cls_count,
+                               int* __restrict__ counts, double* __restrict__ accum) {
+  __shared__ int s_cls[ADLM_MAX_C];
+  __shared__ int s_valid, s_terms;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) s_cls[c] = 0;
+  if (threadIdx.x == 0) { s_valid = 0; s_terms = 0; }
+  __syncthreads();
+  for (int n = threadIdx.x; n < N; n += blockDim.x) {
+    const int c = proto_class[n];
+    if (c >= 0 && c < C) atomicAdd(&s_cls[c], 1);
+  }
+  __syncthreads();
+  int valid = 0, terms = 0;
+  for (int i = threadIdx.x; i < B * (C + 1); i += blockDim.x) {
+    const int l = i % (C + 1), cnt = hist[i];
+    if (ignore_void) { if (l >= 1) valid += cnt; }          // class = l-1 in [0, C)
+    else             { if (l < C) valid += cnt; }
+    if (l < C && cnt >= 2 && s_cls[l] >= 2) terms += s_cls[l] * (s_cls[l] - 1) / 2;
+  }
+  atomicAdd(&s_valid, valid);
+  atomicAdd(&s_terms, terms);
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) cls_count[c] = s_cls[c];
+  if (threadIdx.x == 0) { counts[0] = s_valid; counts[1] = s_terms; }
+  if (threadIdx.x < 4) accum[threadIdx.x] = 0.0;
+}
+
+// One thread per pixel: CE contribution, correctness, dlogits (module.py:156-165,210-211).
+__global__ void k_ce(const float* __restrict__ logits, const int32_t* __restrict__ target, long long M,
+                     int C, int ignore_void, float w_ce_scaled, const int* __restrict__ counts,
+                     float* __restrict__ dlogits, double* __restrict__ accum) {
+  const long long m = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  float loss = 0.f;
+  int correct = 0;
+  if (m < M) {
+    const float* lg = logits + m * C;
+    int t = target[m];
+    bool valid;
+    if (ignore_void) { valid = (t >= 1 && t <= C); t -= 1; }
+    else             { valid = (t >= 0 && t < C); }
+    if (valid) {
+      float mx = lg[0];
+      int am = 0;
+      for (int c = 1; c < C; ++c) { const float v = lg[c]; if (v > mx) { mx = v; am = c; } }
+      float se = 0.f;
+      for (int c = 0; c < C; ++c) se += expf(lg[c] - mx);
+      const float lse = mx + logf(se);
+      loss = lse - lg[t];
+      correct = (am == t);
+      if (dlogits) {
+        const float sc = w_ce_scaled / (float)counts[0];
+        for (int c = 0; c < C; ++c) {
+          const float pr = expf(lg[c] - lse);
+          dlogits[m * C + c] = sc * (pr - (c == t ? 1.f : 0.f));
+        }
+      }
+    } else if (dlogits) {
+      for (int c = 0; c < C; ++c) dlogits[m * C + c] = 0.f;
+    }
+  }
+  loss = warp_sum(loss);
+  const float fc = warp_sum((float)correct);
+  if ((threadIdx.x & 31) == 0) {
+    if (loss != 0.f) atomicAdd(&accum[0], (double)loss);
+    if (fc != 0.f) atomicAdd(&accum[1], (double)fc);
+  }
+}
+
+// One CTA per (label l = blockIdx.x, image b = blockIdx.y).  256 threads = 64 pixel lanes x 4 quarters of
+// the second prototype index.
+__global__ void __launch_bounds__(256)
+k_kld_stats(const float* __restrict__ own, const int32_t* __restrict__ target, const int* __restrict__ hist,
+            const int* __restrict__ cls_count, const int* __restrict__ counts, int HW, int C,
+            float coef /* w_kld * grad_scale */, float* __restrict__ gtab, double* __restrict__ accum) {
+  const int l = blockIdx.x, b = blockIdx.y;
+  float* gt = gtab + ((size_t)b * C + l) * GT_SIZE;
+  const int J = min(cls_count[l], JMAX);
+  const int cnt = hist[b * (C + 1) + l];
+  const int tid = threadIdx.x;
+  if (J < 2 || cnt < 2) {
+    if (tid == 0) gt[GT_VALID] = 0.f;
+    return;
+  }
+  __shared__ float s_mx[JMAX];
+  __shared__ float s_S[JMAX];
+  __shared__ float s_T[JMAX][JMAX];
+  __shared__ float s_red[8][JMAX];
+  __shared__ float s_kl[JMAX][JMAX];
+  const int lane64 = tid & 63, q = tid >> 6;
+  const int32_t* t = target + (size_t)b * HW;
+  const float* ob = own + (size_t)b * HW * JMAX;
+
+  // pass A: per-prototype max over the group's pixels
+  float mx[JMAX];
+#pragma unroll
+  for (int j = 0; j < JMAX; ++j) mx[j] = -INFINITY;
+  for (int p = tid; p < HW; p += 256) {
+    if (t[p] == l) {
+      const float4* o4 = reinterpret_cast<const float4*>(ob + (size_t)p * JMAX);
+#pragma unroll
+      for (int v = 0; v < JMAX / 4; ++v) {
+        const float4 x = o4[v];
+        mx[4 * v] = fmaxf(mx[4 * v], x.x); mx[4 * v + 1] = fmaxf(mx[4 * v + 1], x.y);
+        mx[4 * v + 2] = fmaxf(mx[4 * v + 2], x.z); mx[4 * v + 3] = fmaxf(mx[4 * v + 3], x.w);
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < JMAX; ++j) mx[j] = warp_max(mx[j]);
+  if ((tid & 31) == 0) {
+#pragma unroll
+    for (int j = 0; j < JMAX; ++j) s_red[tid >> 5][j] = mx[j];
+  }
+  for (int i = tid; i < JMAX * JMAX; i += 256) (&s_T[0][0])[i] = 0.f;
+  if (tid < JMAX) s_S[tid] = 0.f;
+  __syncthreads();
+  if (tid < JMAX) {
+    float m = s_red[0][tid];
+    for (int w = 1; w < 8; ++w) m = fmaxf(m, s_red[w][tid]);
+    s_mx[tid] = m;
+  }
+  __syncthreads();
+
+  // pass B: S_j = sum exp(d_j - mx_j),  T[j][i] = sum exp(d_j - mx_j) d_i   (this thread: i in its quarter)
+  float S[JMAX];
+  float T[JMAX][JMAX / 4];
+#pragma unroll
+  for (int j = 0; j < JMAX; ++j) {
+    S[j] = 0.f;
+#pragma unroll
+    for (int i = 0; i < JMAX / 4; ++i) T[j][i] = 0.f;
+  }
+  for (int p = lane64; p < HW; p += 64) {
+    if (t[p] == l) {
+      float d[JMAX];
+      const float4* o4 = reinterpret_cast<const float4*>(ob + (size_t)p * JMAX);
+#pragma unroll
+      for (int v = 0; v < JMAX / 4; ++v) {
+        const float4 x = o4[v];
+        d[4 * v] = x.x; d[4 * v + 1] = x.y; d[4 * v + 2] = x.z; d[4 * v + 3] = x.w;
+      }
+      const float4 dq4 = o4[q];                       // this thread's quarter of the second index
+      const float dq[4] = {dq4.x, dq4.y, dq4.z, dq4.w};
+      static_assert(JMAX / 4 == 4, "quarter layout assumes JMAX == 16");
+#pragma unroll
+      for (int j = 0; j < JMAX; ++j) {
+        if (j < J) {
+          const float e = __expf(d[j] - s_mx[j]);
+          S[j] += e;
+#pragma unroll
+          for (int i = 0; i < JMAX / 4; ++i) T[j][i] = fmaf(e, dq[i], T[j][i]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < JMAX; ++j) {
+    S[j] = warp_sum(S[j]);
+#pragma unroll
+    for (int i = 0; i < JMAX / 4; ++i) T[j][i] = warp_sum(T[j][i]);
+  }
+  if ((tid & 31) == 0) {
+#pragma unroll
+    for (int j = 0; j < JMAX; ++j) {
+      if (q == 0) atomicAdd(&s_S[j], S[j]);
+#pragma unroll
+      for (int i = 0; i < JMAX / 4; ++i) atomicAdd(&s_T[j][q * (JMAX / 4) + i], T[j][i]);
+    }
+  }
+  __syncthreads();
+  // A[j][i] = T[j][i] / S[j]  (in place)
+  {
+    const int j = tid / JMAX, i = tid % JMAX;    // 256 threads == JMAX*JMAX
+    if (j < J && i < J) s_T[j][i] = s_T[j][i] / s_S[j];
+  }
+  __syncthreads();
+  const float n_terms = (float)counts[1];
+  float esum = 0.f;
+  {
+    const int a = tid / JMAX, c = tid % JMAX;
+    float cv = 0.f;
+    if (a < J && c < J && a != c) {
+      const float kld = 0.5f * (s_T[a][a] - s_T[a][c] - s_T[c][a] + s_T[c][c]);
+      const float e = __expf(-kld);
+      if (a < c) esum = e;
+      cv = -0.5f * coef * e / n_terms;
+    }
+    s_kl[a][c] = cv;
+    gt[GT_C + a * JMAX + c] = cv;
+  }
+  esum = warp_sum(esum);
+  if ((tid & 31) == 0 && esum != 0.f) atomicAdd(&accum[2], (double)esum);
+  __syncthreads();
+  if (tid < JMAX) {
+    const int a = tid;
+    float cs = 0.f, r = 0.f;
+    if (a < J) {
+      for (int c = 0; c < J; ++c) {
+        cs += s_kl[a][c];
+        r = fmaf(s_kl[a][c], s_T[a][a] - s_T[a][c], r);
+      }
+    }
+    gt[GT_CSUM + a] = cs;
+    gt[GT_R + a] = r;
+    gt[GT_LSE + a] = (a < J) ? s_mx[a] + __logf(s_S[a]) : 0.f;
+  }
+  if (tid == 0) gt[GT_VALID] = (float)J;
+}
+
+// One thread per pixel: dL/d(own distances) from the KLD term.
+__global__ void k_kld_grad(const float* __restrict__ own, const int32_t* __restrict__ target,
+                           const float* __restrict__ gtab, int HW, int C, long long M,
+                           float* __restrict__ own_grad) {
+  const long long m = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= M) return;
+  const int b = (int)(m / HW);
+  const int l = target[m];
+  float4* out = reinterpret_cast<float4*>(own_grad + m * JMAX);
+  int J = 0;
+  const float* gt = nullptr;
+  if (l >= 0 && l < C) {
+    gt = gtab + ((size_t)b * C + l) * GT_SIZE;
+    J = (int)gt[GT_VALID];
+  }
+  if (J < 2) {
+#pragma unroll
+    for (int v = 0; v < JMAX / 4; ++v) out[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+    return;
+  }
+  float d[JMAX], qv[JMAX], g[JMAX];
+  const float4* o4 = reinterpret_cast<const float4*>(own + m * JMAX);
+#pragma unroll
+  for (int v = 0; v < JMAX / 4; ++v) {
+    const float4 x = o4[v];
+    d[4 * v] = x.x; d[4 * v + 1] = x.y; d[4 * v + 2] = x.z; d[4 * v + 3] = x.w;
+  }
+#pragma unroll
+  for (int a = 0; a < JMAX; ++a) qv[a] = (a < J) ? __expf(d[a] - gt[GT_LSE + a]) : 0.f;
+#pragma unroll
+  for (int a = 0; a < JMAX; ++a) {
+    float ga = 0.f;
+    if (a < J) {
+      float cd = 0.f, cq = 0.f;
+#pragma unroll
+      for (int c = 0; c < JMAX; ++c) {
+        if (c < J) {
+          const float cc = gt[GT_C + a * JMAX + c];
+          cd = fmaf(cc, d[c], cd);
+          cq = fmaf(cc, qv[c], cq);
+        }
+      }
+      const float cs = gt[GT_CSUM + a];
+      ga = qv[a] * (d[a] * cs - cd - gt[GT_R + a]) + qv[a] * cs - cq;
+    }
+    g[a] = ga;
+  }
+#pragma unroll
+  for (int v = 0; v < JMAX / 4; ++v) out[v] = make_float4(g[4 * v], g[4 * v + 1], g[4 * v + 2], g[4 * v + 3]);
+}
+
+// l1 = |W * (1 - identity^T)|_1 (module.py:213-218), dW += w_l1 * sign(W) * mask, final scalars.
+__global__ void k_finalize(const float* __restrict__ W, const int32_t* __restrict__ proto_class, int C, int N,
+                           float w_ce, float w_kld, float w_l1, float grad_scale,
+                           const int* __restrict__ counts, const double* __restrict__ accum,
+                           float* __restrict__ dW, double* __restrict__ scalars) {
+  __shared__ float s_part[32];
+  float l1 = 0.f;
+  for (int i = threadIdx.x; i < C * N; i += blockDim.x) {
+    const int c = i / N, n = i - c * N;
+    if (proto_class[n] != c) {
+      const float w = W[i];
+      l1 += fabsf(w);
+      if (dW) dW[i] += w_l1 * grad_scale * ((w > 0.f) ? 1.f : ((w < 0.f) ? -1.f : 0.f));
+    }
+  }
+  l1 = warp_sum(l1);
+  if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = l1;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double tot = 0.0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) tot += (double)s_part[w];
+    const double n_valid = (double)counts[0], n_terms = (double)counts[1];
+    const double ce = n_valid > 0 ? accum[0] / n_valid
+                                   : __longlong_as_double(0x7ff8000000000000LL);  // empty mean = NaN, as torch
+    const double kld = n_terms > 0 ? accum[2] / n_terms : 0.0;
+    scalars[0] = (double)w_ce * ce + (double)w_kld * kld + (double)w_l1 * tot;
+    scalars[1] = ce;
+    scalars[2] = kld;
+    scalars[3] = tot;
+    scalars[4] = accum[1];
+    scalars[5] = n_valid;
+    scalars[6] = n_terms;
+    scalars[7] = 0.0;
+  }
+}
+
+__global__ void k_proto_rank(const int32_t* __restrict__ proto_class, int N, int32_t* __restrict__ rank) {
+  // rank of prototype n among the prototypes of its class (N is small; quadratic scan is fine)
+  for (int n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x) {
+    const int c = proto_class[n];
+    int r = 0;
+    for (int i = 0; i < n; ++i) r += (proto_class[i] == c);
+    rank[n] = r;
+  }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------- host side
+struct StepWorkspace {  // carved out of the caller's workspace buffer
+  float* logits;     // [M, C]
+  float* dlogits;    // [M, C]
+  float* own;        // [M, JMAX]
+  float* own_grad;   // [M, JMAX]
+  float* gtab;       // [B*C, GT_SIZE]
+  int* hist;         // [B, C+1]
+  int* cls_count;    // [C]
+  int* counts;       // [2]
+  int32_t* rank;     // [N]
+  double* accum;     // [4]
+  size_t bytes;
+};
+
+StepWorkspace carve_step_workspace(void* base, int B, int HW, int N, int C) {
+  StepWorkspace w;
+  const size_t M = (size_t)B * HW;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { void* p = base ? (char*)base + off : nullptr; off += align_up(bytes, 256); return p; };
+  w.logits = (float*)take(M * C * sizeof(float));
+  w.dlogits = (float*)take(M * C * sizeof(float));
+  w.own = (float*)take(M * JMAX * sizeof(float));
+  w.own_grad = (float*)take(M * JMAX * sizeof(float));
+  w.gtab = (float*)take((size_t)B * C * GT_SIZE * sizeof(float));
+  w.hist = (int*)take((size_t)B * (C + 1) * sizeof(int));
+  w.cls_count = (int*)take((size_t)C * sizeof(int));
+  w.counts = (int*)take(2 * sizeof(int));
+  w.rank = (int32_t*)take((size_t)N * sizeof(int32_t));
+  w.accum = (double*)take(4 * sizeof(double));
+  w.bytes = off;
+  return w;
+}
+
+size_t step_workspace_bytes(int B, int HW, int N, int C) {
+  return carve_step_workspace(nullptr, B, HW, N, C).bytes;
+}
+
+int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
+                      const int32_t* target, const int32_t* proto_class, int ignore_void,
+                      float w_ce, float w_kld, float w_l1, float grad_scale, const int32_t* global_counts,
+                      float* logits_out, int32_t* argmax_out, float* dz, float* dP, float* dW,
+                      double* scalars, void* workspace, cudaStream_t st) {
+  const int B = s.B, HW = s.HW, N = s.N, C = s.C;
+  const long long M = (long long)B * HW;
+  StepWorkspace ws = carve_step_workspace(workspace, B, HW, N, C);
+  const bool want_grad = (dz != nullptr) || (dP != nullptr) || (dW != nullptr);
+  float* logits = logits_out ? logits_out : ws.logits;
+
+  ADLM_CUDA(cudaMemsetAsync(ws.hist, 0, sizeof(int) * (size_t)B * (C + 1), st));
+  {
+    dim3 grid(min(cdiv(HW, 256), 64), B);
+    k_label_hist<<<grid, 256, sizeof(int) * (C + 1), st>>>(target, HW, C, ws.hist);
+    ADLM_LAUNCH_CHECK();
+  }
+  k_loss_prepare<<<1, 256, 0, st>>>(ws.hist, proto_class, B, C, N, ignore_void, ws.cls_count, ws.counts, ws.accum);
+  ADLM_LAUNCH_CHECK();
+  k_proto_rank<<<cdiv(N, 128), 128, 0, st>>>(proto_class, N, ws.rank);
+  ADLM_LAUNCH_CHECK();
+  const int* counts = global_counts ? global_counts : ws.counts;
+  // own-class distances of pixels whose label has no prototypes are never written: clear the buffer
+  ADLM_CUDA(cudaMemsetAsync(ws.own, 0, sizeof(float) * (size_t)M * JMAX, st));
+
+  StepExtras ex;
+  ex.target = target;
+  ex.proto_class = proto_class;
+  ex.proto_rank = ws.rank;
+  ex.own_dist = ws.own;
+  int rc;
+  if ((rc = head_fwd_dispatch(s, prec_mode, z, P, W, logits, nullptr, nullptr, argmax_out, ex, st)) != ADLM_OK)
+    return rc;
+
+  k_ce<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(logits, target, M, C, ignore_void, w_ce * grad_scale,
+                                                    counts, want_grad ? ws.dlogits : nullptr, ws.accum);
+  ADLM_LAUNCH_CHECK();
+  {
+    dim3 grid(C, B);
+    k_kld_stats<<<grid, 256, 0, st>>>(ws.own, target, ws.hist, ws.cls_count, counts, HW, C,
+                                      w_kld * grad_scale, ws.gtab, ws.accum);
+    ADLM_LAUNCH_CHECK();
+  }
+  if (want_grad) {
+    k_kld_grad<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(ws.own, target, ws.gtab, HW, C, M, ws.own_grad);
+    ADLM_LAUNCH_CHECK();
+    StepExtras exb = ex;
+    exb.own_dist = nullptr;
+    exb.own_grad = ws.own_grad;
+    if ((rc = head_bwd_dispatch(s, prec_mode, z, P, W, ws.dlogits, nullptr, nullptr, dz, dP, dW, exb, st)) != ADLM_OK)
+      return rc;
+  }
+  k_finalize<<<1, 256, 0, st>>>(W, proto_class, C, N, w_ce, w_kld, w_l1, grad_scale, counts, ws.accum,
+                                dW, scalars);
+  ADLM_LAUNCH_CHECK();
+  return ADLM_OK;
+}
+
+int step_counts_impl(const int32_t* target, int B, int HW, const int32_t* proto_class, int N, int C,
+                     int ignore_void, int32_t* counts_out, void* workspace, cudaStream_t st) {
+  StepWorkspace ws = carve_step_workspace(workspace, B, HW, N, C);
+  ADLM_CUDA(cudaMemsetAsync(ws.hist, 0, sizeof(int) * (size_t)B * (C + 1), st));
+  dim3 grid(min(cdiv(HW, 256), 64), B);
+  k_label_hist<<<grid, 256, sizeof(int) * (C + 1), st>>>(target, HW, C, ws.hist);
+  ADLM_LAUNCH_CHECK();
+  k_loss_prepare<<<1, 256, 0, st>>>(ws.hist, proto_class, B, C, N, ignore_void, ws.cls_count, counts_out, ws.accum);
+  ADLM_LAUNCH_CHECK();
+  return ADLM_OK;
+}
+
+}  // namespace adlm

@@ -1,0 +1,205 @@
+// Push: nearest-patch search of segmentation/push.py as streaming kernels.
+//
+//   k_patch_class_mask  push.py:201-230  full-resolution labels -> per-patch class bitmask
+//   k_simt_push_scan    push.py:249-280  class-filtered per-prototype argmin, fp32 arithmetic
+//   k_push_gather       push.py:268-280, :142-145  winners' feature vectors
+//
+// The reference copies the (h,w,N) distance map and the features of every image to the host and
+// searches them in Python; here the distance never leaves the SM: each CTA keeps a running
+// (distance bits << 32 | global patch id) minimum per prototype in shared memory and folds it into
+// the global array with one 64-bit atomicMin per prototype.
+#include "common.cuh"
+
+namespace adlm {
+
+namespace {
+
+// One CTA per (patch row, image): OR the class bits of every label pixel whose row maps to this
+// patch row into a shared-memory row of w masks.  Label rows are read coalesced.
+__global__ void __launch_bounds__(256)
+k_patch_class_mask(const uint8_t* __restrict__ labels, int H, int Wimg, const int32_t* __restrict__ row_lut,
+                   const int32_t* __restrict__ col_lut, int h, int w, uint32_t* __restrict__ mask_out) {
+  extern __shared__ uint32_t smask[];
+  const int pi = blockIdx.x, img = blockIdx.y;
+  for (int j = threadIdx.x; j < w; j += blockDim.x) smask[j] = 0u;
+  __syncthreads();
+  // rows mapped to patch row pi: the LUT is monotone, find the range by scanning from an estimate
+  // (kept simple: every thread tests the row it strides over)
+  const uint8_t* lab = labels + (size_t)img * H * Wimg;
+  // first/last row of this patch row (binary search on the monotone LUT)
+  int lo = 0, hi = H;
+  while (lo < hi) { const int mid = (lo + hi) >> 1; if (row_lut[mid] < pi) lo = mid + 1; else hi = mid; }
+  const int r0 = lo;
+  hi = H;
+  while (lo < hi) { const int mid = (lo + hi) >> 1; if (row_lut[mid] <= pi) lo = mid + 1; else hi = mid; }
+  const int r1 = lo;
+  const int n = (r1 - r0) * Wimg;
+  for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
+    const int r = r0 + idx / Wimg, j = idx - (idx / Wimg) * Wimg;
+    const unsigned l = lab[(size_t)r * Wimg + j];
+    if (l > 0u && l <= 32u) {
+      const uint32_t bit = 1u << (l - 1u);
+      const int pj = col_lut[j];
+      // neighbouring lanes usually hit the same patch with the same class: skip redundant atomics
+      if ((smask[pj] & bit) == 0u) atomicOr(&smask[pj], bit);
+    }
+  }
+  __syncthreads();
+  uint32_t* out = mask_out + ((size_t)img * h + pi) * w;
+  for (int j = threadIdx.x; j < w; j += blockDim.x) out[j] = smask[j];
+}
+
+constexpr int TM = 64, TN = 64, NT = 256, PS = TN + 4;
+
+// Same tiling as simt_head.cu's forward; the epilogue is the masked running minimum.
+__global__ void __launch_bounds__(NT)
+k_simt_push_scan(const float* __restrict__ z, int K, int HW, const uint32_t* __restrict__ mask,
+                 const float* __restrict__ P, int N, const int32_t* __restrict__ proto_class,
+                 unsigned long long patch_base, unsigned long long* __restrict__ packed_min,
+                 int tiles_per_img) {
+  extern __shared__ __align__(16) float smem[];
+  const int Kq = (K + 63) & ~63;
+  float* zs = smem;
+  float* ps = zs + Kq * TM;
+  float* x2s = ps + Kq * PS;
+  float* p2s = x2s + TM;
+  unsigned long long* best = reinterpret_cast<unsigned long long*>(p2s + TN);   // [TN]
+  uint32_t* ms = reinterpret_cast<uint32_t*>(best + TN);                        // [TM]
+  int* pcs = reinterpret_cast<int*>(ms + TM);                                   // [TN]
+
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int img = blockIdx.x / tiles_per_img, p0 = (blockIdx.x % tiles_per_img) * TM;
+  const float* zb = z + (size_t)img * K * HW;
+  for (int idx = tid; idx < Kq * TM; idx += NT) {
+    const int k = idx >> 6, px = idx & 63, p = p0 + px;
+    zs[idx] = (k < K && p < HW) ? __ldg(zb + (size_t)k * HW + p) : 0.f;
+  }
+  if (tid < TM) ms[tid] = (p0 + tid < HW) ? mask[(size_t)img * HW + p0 + tid] : 0u;
+  __syncthreads();
+  if (tid < TM) {
+    float a = 0.f;
+    for (int k = 0; k < K; ++k) { const float v = zs[k * TM + tid]; a = fmaf(v, v, a); }
+    x2s[tid] = a;
+  }
+  uint32_t any = 0u;
+  for (int i = 0; i < TM; ++i) any |= ms[i];
+  if (any == 0u) return;   // no labelled pixel in this tile (uniform across the CTA)
+
+  for (int n0 = 0; n0 < N; n0 += TN) {
+    __syncthreads();
+    const int kblocks = Kq >> 3;
+    for (int idx = tid; idx < TN * Kq; idx += NT) {
+      const int kk = idx & 7, nn = (idx >> 3) & 3, rest = idx >> 5;
+      const int kb = rest % kblocks, nb = rest / kblocks;
+      const int n = nb * 4 + nn, k = kb * 8 + kk;
+      ps[k * PS + n] = (n0 + n < N && k < K) ? __ldg(P + (size_t)(n0 + n) * K + k) : 0.f;
+    }
+    if (tid < TN) {
+      best[tid] = ADLM_PUSH_NONE;
+      pcs[tid] = (n0 + tid < N) ? proto_class[n0 + tid] : -1;
+    }
+    __syncthreads();
+    if (tid >= 64 && tid < 128) {
+      const int n = tid - 64;
+      float a = 0.f;
+      for (int k = 0; k < K; ++k) { const float v = ps[k * PS + n]; a = fmaf(v, v, a); }
+      p2s[n] = a;
+    }
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+#pragma unroll 4
+    for (int k = 0; k < K; ++k) {
+      float a[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = zs[k * TM + tx + 16 * i];
+      const float4 b4 = *reinterpret_cast<const float4*>(ps + k * PS + ty * 4);
+      const float b[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int nl = ty * 4 + j;
+      const int pc = pcs[nl];
+      unsigned long long key = ADLM_PUSH_NONE;
+      if (pc >= 0 && pc < 32) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int px = tx + 16 * i;
+          if ((ms[px] >> pc) & 1u) {
+            const float d = fmaxf(x2s[px] + fmaf(-2.f, acc[i][j], p2s[nl]), 0.f);
+            const unsigned long long kk =
+                ((unsigned long long)__float_as_uint(d) << 32) |
+                (patch_base + (unsigned long long)img * HW + (unsigned long long)(p0 + px));
+            key = kk < key ? kk : key;
+          }
+        }
+      }
+      // the 16 lanes sharing ty hold the same prototype: shuffle-min across them
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+        key = other < key ? other : key;
+      }
+      if (tx == 0 && key != ADLM_PUSH_NONE) best[nl] = key;   // one writer per prototype
+    }
+    __syncthreads();
+    if (tid < TN && n0 + tid < N && best[tid] != ADLM_PUSH_NONE) atomicMin(packed_min + n0 + tid, best[tid]);
+  }
+}
+
+__global__ void k_push_gather(const float* __restrict__ z, int n_img, int K, int HW,
+                              unsigned long long patch_base, const unsigned long long* __restrict__ packed,
+                              int N, float* __restrict__ out) {
+  const int n = blockIdx.x;
+  const unsigned long long key = packed[n];
+  if (key == ADLM_PUSH_NONE) return;
+  const unsigned long long id = key & 0xffffffffULL;
+  if (id < patch_base || id >= patch_base + (unsigned long long)n_img * HW) return;
+  const unsigned long long local = id - patch_base;
+  const size_t img = local / HW, p = local % HW;
+  for (int k = threadIdx.x; k < K; k += blockDim.x) out[(size_t)n * K + k] = z[(img * K + k) * HW + p];
+}
+
+}  // namespace
+
+int patch_class_mask_impl(const uint8_t* labels, int n_img, int H, int Wimg, const int32_t* row_lut,
+                          const int32_t* col_lut, int h, int w, uint32_t* mask_out, cudaStream_t st) {
+  dim3 grid(h, n_img);
+  KernelTimer timer(ADLM_K_PATCH_MASK, st);
+  k_patch_class_mask<<<grid, 256, sizeof(uint32_t) * w, st>>>(labels, H, Wimg, row_lut, col_lut, h, w, mask_out);
+  ADLM_LAUNCH_CHECK();
+  return ADLM_OK;
+}
+
+int simt_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mask, const float* P, int N,
+                   const int32_t* proto_class, long long patch_base, unsigned long long* packed_min,
+                   cudaStream_t st) {
+  const int Kq = (K + 63) & ~63;
+  const int tiles_per_img = cdiv(HW, TM);
+  const long long grid = (long long)n_img * tiles_per_img;
+  ADLM_CHECK_SUPPORTED(grid < (1ll << 31), "too many pixel tiles");
+  const size_t bytes = sizeof(float) * ((size_t)Kq * TM + (size_t)Kq * PS + TM + TN) +
+                       sizeof(unsigned long long) * TN + sizeof(uint32_t) * TM + sizeof(int) * TN;
+  ADLM_CUDA(cudaFuncSetAttribute(k_simt_push_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  KernelTimer timer(ADLM_K_PUSH_SCAN, st);
+  k_simt_push_scan<<<(unsigned)grid, NT, bytes, st>>>(z, K, HW, mask, P, N, proto_class,
+                                                      (unsigned long long)patch_base, packed_min, tiles_per_img);
+  ADLM_LAUNCH_CHECK();
+  return ADLM_OK;
+}
+
+int push_gather_impl(const float* z, int n_img, int K, int HW, long long patch_base,
+                     const unsigned long long* packed_min, int N, float* proto_out, cudaStream_t st) {
+  k_push_gather<<<N, 64, 0, st>>>(z, n_img, K, HW, (unsigned long long)patch_base, packed_min, N, proto_out);
+  ADLM_LAUNCH_CHECK();
+  return ADLM_OK;
+}
+
+}  // namespace adlm

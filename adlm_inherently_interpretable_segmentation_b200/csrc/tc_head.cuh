@@ -1,0 +1,17 @@
+// tcgen05 (5th-gen tensor core) kernels of the prototype head: ADLM_PREC_TF32 / ADLM_PREC_TF32X3.
+#pragma once
+#include "common.cuh"
+
+namespace adlm {
+
+int tc_head_fwd(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
+                float* logits, float* dist, float* sim, int32_t* argmax, const StepExtras& ex,
+                cudaStream_t st);
+int tc_head_bwd(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
+                const float* dlogits, const float* ddist, const float* dsim, float* dz, float* dP,
+                float* dW, const StepExtras& ex, cudaStream_t st);
+int tc_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mask, const float* P, int N,
+                 const int32_t* proto_class, long long patch_base, int prec_mode,
+                 unsigned long long* packed_min, cudaStream_t st);
+
+}  // namespace adlm

@@ -1,0 +1,409 @@
+#!/usr/bin/env python
+"""Benchmark of the ProtoSeg prototype-head hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--precision fp32|tf32|tf32x3]
+
+One "step" = one fused training step of the head (forward + CE + KLD + masked L1 + backward,
+segmentation/module.py:137-222,236) over one synthetic batch of BASELINE configs[1]'s head shape:
+16 images of 64 x 65 x 65 DeepLab features (513x513 crops), 190 prototypes x 64-d, 19 classes.  The
+DeepLabv2/ResNet-101 backbone is out of scope (BASELINE north_star) and is not timed.
+
+Prints ONE JSON line (rank 0):
+  value      Mpixels/s over all ranks, inputs resident in HBM, CUDA-event timed, max over ranks
+  e2e        same metric through the public C-ABI-backed API with HOST buffers: pinned H2D of the step's
+             features + labels and D2H of its results (loss scalars, dz, dP, dW) inside the timed region
+  roofline   dominant kernel's achieved HBM GB/s (algorithmic bytes / CUDA-event launch time) vs MEASURED_PEAKS
+  cpu_baseline  the reference's operator sequence (oracle/torch_port.py) on this box's host cores
+  push       secondary metric of BASELINE.json: push imgs/s over a resident synthetic shard
+
+--impl reference times the CPU port alone on the same config (bounded sample per step).
+Under torchrun (N > 1): batch-sharded weak scaling, one all-reduce of the loss normalisers and one of
+[dP | dW | scalars] per step (parallel.dp_fused_step).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CFG = dict(B=16, K=64, h=65, w=65, N=190, C=19)          # BASELINE configs[1], head only
+WEIGHTS = (1.0, 0.25, 1e-4)                              # cityscapes_kld_imnet.gin:35,38-39
+BYTES_FWD = lambda K, C: 4 * K + 4 * C                   # z in, logits out
+BYTES_BWD = lambda K, C: 4 * K + 4 * C + 4 * K           # z + dlogits in, dz out
+PUSH_CFG = dict(n_img=64, K=64, h=129, w=257, H=1024, W=2048, N=190, C=19)   # configs[2] per-GPU slice
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default=None)
+    ap.add_argument("--no-push", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return dict(hbm=float(p["hbm_gbs"]), source="measured (MEASURED_PEAKS.json)")
+    return dict(hbm=6650.0, source="fallback (B200_PROFILING.md)")
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """samples SM clock + throttle reasons with NVML while the timed region runs"""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self):
+        nv = self.nv
+        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40,
+                 "sw_thermal_slowdown": 0x20, "hw_power_brake": 0x80, "sync_boost": 0x10,
+                 "applications_clocks_setting": 0x2}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._thread = threading.Thread(target=self._loop, daemon=True)
+            self._thread.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join()
+        return False
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["nvml unavailable"]}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU leg
+def cpu_step_fn(n_images):
+    """the reference's operator sequence on host cores (oracle/torch_port.py), n_images of the workload"""
+    import torch
+    from oracle import torch_port as tp
+    from adlm_inherently_interpretable_segmentation_b200 import synth
+    c = CFG
+    z, P, W = synth.head_inputs(n_images, c["K"], c["h"], c["w"], c["N"], c["C"], w_noise=0.1, seed=synth.BASE_SEED)
+    target = torch.from_numpy(synth.block_labels(n_images, c["h"], c["w"], c["C"], block=8,
+                                                 seed=synth.BASE_SEED).astype(np.int64))
+    ident = tp.class_identity(c["N"], c["C"])
+    zt = torch.from_numpy(z).requires_grad_(True)
+    P4 = torch.from_numpy(P).reshape(c["N"], c["K"], 1, 1).requires_grad_(True)
+    Wt = torch.from_numpy(W).requires_grad_(True)
+
+    def step():
+        for t in (zt, P4, Wt):
+            t.grad = None
+        return tp.step(zt, P4, Wt, target, ident, ignore_void=True, weights=WEIGHTS)
+    return step, n_images * c["h"] * c["w"]
+
+
+def cpu_baseline(budget_s=12.0):
+    import torch
+    step, pixels = cpu_step_fn(2)                      # the reference's own batch size (gin: batch_size 2)
+    step()
+    t0 = time.perf_counter()
+    n = 0
+    while n < 3 or time.perf_counter() - t0 < budget_s:
+        step()
+        n += 1
+    dt = time.perf_counter() - t0
+    return {"value": pixels * n / dt / 1e6, "unit": "Mpixels/s", "cores": torch.get_num_threads(),
+            "kind": "port",
+            "sample": f"{n} steps of batch 2 (2x64x65x65, 190x64, C=19) of oracle/torch_port.step "
+                      f"(reference op sequence incl. KLD loops + autograd), {dt:.1f} s, torch {torch.__version__}"}
+
+
+def run_reference(args):
+    """--impl reference: the CPU port on the same config; every step is a bounded sample of the batch"""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    c = CFG
+    n_img = 2
+    step, pixels = cpu_step_fn(n_img)
+    t0 = time.perf_counter()
+    step()
+    t1 = time.perf_counter() - t0
+    if t1 * (args.steps + args.warmup) > 150.0:        # keep the whole run within a few minutes
+        n_img = 1
+        step, pixels = cpu_step_fn(n_img)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    val = pixels * args.steps / dt / 1e6
+    line = {
+        "impl": "reference", "metric": "proto_head_fwd_bwd_mpixels_per_s", "value": val, "unit": "Mpixels/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": config_dict("fp32", None),
+        "cpu_baseline": {"value": val, "unit": "Mpixels/s", "cores": torch.get_num_threads(), "kind": "port",
+                         "sample": f"each step = {n_img} of the 16 images (oracle/torch_port.step on host cores)"},
+        "e2e": {"value": val, "unit": "Mpixels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def config_dict(prec, ring):
+    c = CFG
+    return {"workload": "configs[1] head: fused prototype-head training step (fwd + CE + KLD + L1 + bwd), "
+                        "batch 16 of 64x65x65 features (513x513 crops), 190 prototypes x 64-d, 19 classes; "
+                        "backbone out of scope",
+            "global_batch_per_gpu": c["B"], "pixels_per_step_per_gpu": c["B"] * c["h"] * c["w"],
+            "precision": prec, "parallelism": "dp (batch-sharded, prototype-gradient all-reduce)",
+            "l2_policy": (f"ring of {ring} distinct resident batches ({ring * c['B'] * c['K'] * c['h'] * c['w'] * 4 / 2**20:.0f} MiB "
+                          "> 2x L2) so every step reads inputs evicted from L2") if ring else "n/a"}
+
+
+# ------------------------------------------------------------------------------------------------ GPU leg
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from adlm_inherently_interpretable_segmentation_b200 import _lib, head, parallel, push, synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    prec = args.precision or head.DEFAULT_PRECISION
+    c = CFG
+    B, K, h, w, N, C = c["B"], c["K"], c["h"], c["w"], c["N"], c["C"]
+    M = B * h * w
+    K_steps, W_steps = args.steps, max(args.warmup, 3)
+
+    # ---- synthetic, seeded inputs: a ring of distinct batches larger than L2
+    ring = 16
+    g = torch.Generator(device=dev).manual_seed(synth.BASE_SEED + rank)
+    zs = [torch.sigmoid(torch.randn(B, K, h, w, device=dev, generator=g)) for _ in range(ring)]
+    labs = synth.block_labels(ring * B, h, w, C, block=8, seed=synth.BASE_SEED + rank).astype(np.int32)
+    tgts = [torch.from_numpy(labs[i * B:(i + 1) * B]).to(dev) for i in range(ring)]
+    _, Pn, Wn = synth.head_inputs(1, K, 2, 2, N, C, w_noise=0.1, seed=synth.BASE_SEED)
+    P = torch.from_numpy(Pn).to(dev)
+    Wt = torch.from_numpy(Wn).to(dev)
+    pc = torch.arange(N, dtype=torch.int32, device=dev) // (N // C)
+    ws = torch.empty(int(_lib.load().adlm_step_workspace_bytes(B, K, h * w, N, C)), device=dev, dtype=torch.uint8)
+
+    def step(i):
+        j = i % ring
+        if world > 1:
+            return parallel.dp_fused_step((P, Wt), zs[j], tgts[j], pc, weights=WEIGHTS, precision=prec, workspace=ws)
+        return head.fused_step(zs[j], P, Wt, tgts[j], pc, weights=WEIGHTS, precision=prec, workspace=ws)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, n, sampler=None):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        ctx = sampler if sampler is not None else _Null()
+        with ctx:
+            e0.record()
+            for i in range(n):
+                fn(i)
+            e1.record()
+            barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t)
+        return ms
+
+    for i in range(W_steps):
+        step(i)
+    sampler = ClockSampler(local)
+    l0 = _lib.launch_count()
+    ms = timed(step, K_steps, sampler)
+    launches = _lib.launch_count() - l0
+    value = world * M * K_steps / (ms * 1e-3) / 1e6
+
+    # ---- roofline leg: per-launch CUDA events around the two head kernels, same loop
+    pk = peaks()
+    roof = None
+    kern = {}
+    for tag, name, nbytes in ((_lib.K_HEAD_BWD, "head_bwd", BYTES_BWD(K, C) * M), (_lib.K_HEAD_FWD, "head_fwd", BYTES_FWD(K, C) * M)):
+        with _lib.kernel_timing(tag, K_steps) as t:
+            timed(step, K_steps)
+        if t.ms:
+            avg = float(np.mean(t.ms))
+            kern[name] = {"avg_ms": avg, "launches": len(t.ms), "algorithmic_bytes": nbytes,
+                          "achieved_gbs": nbytes / (avg * 1e-3) / 1e9}
+    if kern:
+        dom = max(kern, key=lambda k: kern[k]["avg_ms"])
+        roof = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["achieved_gbs"], "peak": pk["hbm"],
+                "unit": "GB/s", "frac": kern[dom]["achieved_gbs"] / pk["hbm"], "traffic": None,
+                "peak_source": pk["source"], "kernels": kern,
+                "share_of_step": kern[dom]["avg_ms"] / (ms / K_steps)}
+
+    # ---- e2e leg: host buffers in, host buffers out, through the public API
+    n_host = 4
+    hz = [zs[i].cpu().pin_memory() for i in range(n_host)]
+    ht = [tgts[i].cpu().pin_memory() for i in range(n_host)]
+    dz_h = torch.empty((B, K, h, w), dtype=torch.float32).pin_memory()
+    dP_h = torch.empty((N, K), dtype=torch.float32).pin_memory()
+    dW_h = torch.empty((C, N), dtype=torch.float32).pin_memory()
+    sc_h = torch.empty(_lib.STEP_NSCALARS, dtype=torch.float64).pin_memory()
+    z_d = torch.empty((B, K, h, w), device=dev, dtype=torch.float32)
+    t_d = torch.empty((B, h, w), device=dev, dtype=torch.int32)
+    h2d = hz[0].numel() * 4 + ht[0].numel() * 4
+    d2h = dz_h.numel() * 4 + dP_h.numel() * 4 + dW_h.numel() * 4 + sc_h.numel() * 8
+
+    def e2e_step(i):
+        j = i % n_host
+        z_d.copy_(hz[j], non_blocking=True)
+        t_d.copy_(ht[j], non_blocking=True)
+        if world > 1:
+            r = parallel.dp_fused_step((P, Wt), z_d, t_d, pc, weights=WEIGHTS, precision=prec, workspace=ws)
+        else:
+            r = head.fused_step(z_d, P, Wt, t_d, pc, weights=WEIGHTS, precision=prec, workspace=ws)
+        dz_h.copy_(r.dz, non_blocking=True)
+        dP_h.copy_(r.dP.reshape(N, K), non_blocking=True)
+        dW_h.copy_(r.dW, non_blocking=True)
+        sc_h.copy_(r.scalars, non_blocking=True)
+        torch.cuda.current_stream().synchronize()      # the caller holds the step's results on the host
+
+    for i in range(3):
+        e2e_step(i)
+    ms_e2e = timed(e2e_step, K_steps)
+    e2e = {"value": world * M * K_steps / (ms_e2e * 1e-3) / 1e6, "unit": "Mpixels/s",
+           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / K_steps}
+
+    # ---- secondary metric: push imgs/s over a resident synthetic shard (configs[2] per-GPU slice)
+    push_res = None
+    if not args.no_push:
+        push_res = bench_push(torch, dist, push, synth, dev, rank, world, prec, pk)
+
+    cpu = None
+    if rank == 0 and not args.no_cpu:
+        cpu = cpu_baseline()
+
+    if rank == 0:
+        line = {
+            "metric": "proto_head_fwd_bwd_mpixels_per_s", "value": value, "unit": "Mpixels/s", "n_gpus": world,
+            "steps": K_steps, "warmup": W_steps, "ms_per_step": ms / K_steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": {"fp32": "f32", "tf32": "tf32", "tf32x3": "tf32x3"}[prec],
+            "data": "synthetic", "config": config_dict(prec, ring), "clocks": sampler.summary(), "e2e": e2e,
+            "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu, "push": push_res,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+class _Null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+
+def bench_push(torch, dist, push, synth, dev, rank, world, prec, pk):
+    """push search over n_img resident images per GPU: labels -> class mask -> scan -> reduce -> gather"""
+    from adlm_inherently_interpretable_segmentation_b200 import _lib
+    c = PUSH_CFG
+    n, K, h, w, H, W, N, C = c["n_img"], c["K"], c["h"], c["w"], c["H"], c["W"], c["N"], c["C"]
+    g = torch.Generator(device=dev).manual_seed(synth.BASE_SEED + 100 + rank)
+    z = torch.sigmoid(torch.randn(n, K, h, w, device=dev, generator=g))
+    lab1 = synth.block_labels(8, H, W, C, block=32, seed=synth.BASE_SEED + rank)
+    labels = torch.from_numpy(lab1).to(dev).repeat(n // 8, 1, 1).contiguous()
+    P = torch.rand(N, K, device=dev, generator=g)
+    pc = torch.arange(N, dtype=torch.int32, device=dev) // (N // C)
+    chunk = 32
+
+    def one_pass():
+        s = push.PushSearch(P, pc, precision=prec)
+        for i in range(0, n, chunk):
+            s.scan(z[i:i + chunk], labels[i:i + chunk], rank * n + i)
+        s.reduce()
+        out = torch.zeros((N, K), device=dev)
+        for i in range(0, n, chunk):
+            s.gather(z[i:i + chunk], rank * n + i, out)
+        if world > 1:
+            dist.all_reduce(out)
+        return out
+
+    one_pass()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        dist.barrier()
+    reps = 3
+    e0.record()
+    for _ in range(reps):
+        one_pass()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t)
+    with _lib.kernel_timing(_lib.K_PUSH_SCAN, 64) as t:
+        one_pass()
+        torch.cuda.synchronize()
+    scan_ms = float(np.sum(t.ms)) if t.ms else None
+    bytes_scan = n * h * w * (4 * K + 4)
+    return {"metric": "push_imgs_per_s", "value": world * n / (ms * 1e-3), "unit": "imgs/s",
+            "images_per_gpu": n, "ms_per_pass": ms, "precision": prec,
+            "workload": "configs[2] slice: 1024x2048 labels, 64x129x257 features, 190 prototypes; labels->mask, "
+                        "scan, packed-min reduce, gather (features resident; backbone out of scope)",
+            "scan_kernel": None if scan_ms is None else {
+                "ms_per_pass": scan_ms, "achieved_gbs": bytes_scan / (scan_ms * 1e-3) / 1e9,
+                "frac_of_hbm_peak": bytes_scan / (scan_ms * 1e-3) / 1e9 / pk["hbm"]}}
+
+
+if __name__ == "__main__":
+    main()

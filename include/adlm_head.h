@@ -1,0 +1,190 @@
+/*
+ * adlm_head.h — C ABI of the B200-native ProtoSeg prototype head + push search.
+ *
+ * One shared library (libadlm_head.so, built from
+ * adlm_inherently_interpretable_segmentation_b200/csrc/ by nvcc for sm_100a) exports exactly
+ * the symbols declared here.  Plain C: pointers + sizes, no torch types.  Every pointer is a
+ * DEVICE pointer unless it says "host"; every buffer is allocated and owned by the caller
+ * (torch, in the Python host); nothing is allocated inside except lazily created TMA
+ * descriptors.  Every call is asynchronous on `stream` (a cudaStream_t passed as void*).
+ * Return value: 0 on success, negative ADLM_E_* on failure, message via adlm_last_error().
+ * There is no CPU fallback and no fallback to a library GEMM: unsupported shapes return
+ * ADLM_E_UNSUPPORTED.
+ *
+ * Reference interface replaced (file:line into the reference repo):
+ *   adlm_head_fwd          model.py:203-221 (_l2_convolution), :231-237 (distance_2_similarity),
+ *                          :161-162 (run_last_layer), :259-283 (forward_from_conv_features)
+ *   adlm_head_bwd          autograd backward of the above, invoked at segmentation/module.py:236
+ *   adlm_step_fwd_bwd      segmentation/module.py:137-222 + :236 (forward, CE on non-void patches,
+ *                          KLD prototype-diversity loss on distances, masked L1, backward)
+ *   adlm_patch_class_mask  segmentation/push.py:201-230 (pixel -> patch class sets)
+ *   adlm_push_scan         segmentation/push.py:249-280 (class-filtered per-prototype argmin,
+ *                          strict '<' against the global minimum)
+ *   adlm_push_gather       segmentation/push.py:268-280, :142-145 (winner feature vectors)
+ */
+#ifndef ADLM_HEAD_H
+#define ADLM_HEAD_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ADLM_ABI_VERSION 3
+
+#if defined(__GNUC__)
+#define ADLM_API __attribute__((visibility("default")))
+#else
+#define ADLM_API
+#endif
+
+/* error codes */
+#define ADLM_OK 0
+#define ADLM_E_INVALID (-1)     /* bad argument (null pointer, non-positive size, misaligned) */
+#define ADLM_E_UNSUPPORTED (-2) /* shape / mode outside what the kernels implement */
+#define ADLM_E_CUDA (-3)        /* a CUDA runtime call failed; message holds cudaGetErrorString */
+#define ADLM_E_WORKSPACE (-4)   /* workspace too small */
+
+/* prototype_activation_function (model.py:231-237) */
+#define ADLM_ACT_LOG 0    /* s = log((d + 1) / (d + eps)) */
+#define ADLM_ACT_LINEAR 1 /* s = -d */
+
+/* arithmetic of the z.p contraction */
+#define ADLM_PREC_FP32 0   /* CUDA-core fp32 FMA — the reference's arithmetic class */
+#define ADLM_PREC_TF32 1   /* tcgen05 kind::tf32, operands centred and rounded to nearest */
+#define ADLM_PREC_TF32X3 2 /* tcgen05 3xTF32 (hi*hi + hi*lo + lo*hi): fp32-class accuracy */
+
+/* limits of this build (checked at run time, ADLM_E_UNSUPPORTED beyond them) */
+#define ADLM_MAX_K 256            /* prototype depth */
+#define ADLM_MAX_C 128            /* classes */
+#define ADLM_MAX_PROTOS_PER_CLASS 16
+#define ADLM_MAX_PUSH_CLASSES 32  /* patch class mask is one uint32 per patch */
+
+/* number of doubles adlm_step_fwd_bwd writes to `scalars` */
+#define ADLM_STEP_NSCALARS 8
+/* scalars[0] loss  [1] cross_entropy  [2] kld_loss  [3] l1  [4] n_correct  [5] n_patches (non-void)
+ * [6] n_kld_terms  [7] reserved */
+
+ADLM_API const char* adlm_last_error(void);
+ADLM_API int adlm_abi_version(void);
+/* number of kernel launches issued by this library since load (bench.py's gpu_launches) */
+ADLM_API unsigned long long adlm_launch_count(void);
+
+/*
+ * Measurement aid (bench.py's roofline leg): between adlm_timing_begin(tag, max) and adlm_timing_end the
+ * library brackets every launch of the tagged kernel with CUDA events on the launching stream.
+ * adlm_timing_end synchronises those events and writes the per-launch durations (milliseconds) to the
+ * HOST array ms_out (capacity given to begin); returns the number of launches recorded or a negative code.
+ */
+#define ADLM_K_HEAD_FWD 1
+#define ADLM_K_HEAD_BWD 2
+#define ADLM_K_PUSH_SCAN 3
+#define ADLM_K_PATCH_MASK 4
+ADLM_API int adlm_timing_begin(int kernel_tag, int max_samples);
+ADLM_API int adlm_timing_end(float* ms_out);
+
+/*
+ * Head forward.  z [B,K,HW] fp32 (NCHW features flattened over h*w, contiguous),
+ * P [N,K] prototypes, W [C,N] last layer (no bias).
+ * Outputs (each may be NULL = not wanted, except logits):
+ *   logits [B,HW,C]   (= reference (B,h,w,C))
+ *   dist   [B,N,HW]   (= reference (B,N,h,w)); the M x N map touches HBM only if requested
+ *   sim    [B*HW,N]   (= reference prototype_activations)
+ *   argmax [B,HW]     int32 per-pixel argmax over classes (first maximum, as torch.argmax)
+ */
+ADLM_API int adlm_head_fwd(const float* z, int B, int K, int HW,
+                  const float* P, const float* W, int N, int C,
+                  float eps, int act_mode, int prec_mode,
+                  float* logits, float* dist, float* sim, int32_t* argmax,
+                  void* stream);
+
+/*
+ * Head backward for arbitrary upstream gradients (autograd drop-in).
+ *   dlogits [B,HW,C] | NULL, ddist [B,N,HW] | NULL, dsim [B*HW,N] | NULL
+ *   dz [B,K,HW] | NULL, dP [N,K] | NULL, dW [C,N] | NULL  (dP/dW are overwritten, not accumulated)
+ * Distances are recomputed from z and P (never read back from HBM).
+ */
+ADLM_API int adlm_head_bwd(const float* z, int B, int K, int HW,
+                  const float* P, const float* W, int N, int C,
+                  float eps, int act_mode, int prec_mode,
+                  const float* dlogits, const float* ddist, const float* dsim,
+                  float* dz, float* dP, float* dW,
+                  void* stream);
+
+/*
+ * Fused training / validation step of the head ('log' activation):
+ *   forward -> CE over non-void patches -> KLD over same-class prototype pairs (on distances,
+ *   groups keyed by the UN-shifted label, module.py:150,170-178) -> masked L1 on W -> backward.
+ *   target [B,HW] int32: labels already resized to the feature map (dataset.py:23-31);
+ *     ignore_void != 0: label 0 is void, class = label-1 (module.py:156-160)
+ *   proto_class [N] int32: class of each prototype (argmax of prototype_class_identity row)
+ *   grad_scale: multiplies every gradient (1/iter_size, module.py:236)
+ *   dz/dP/dW: NULL, NULL, NULL = loss/metrics only (validation step).  dP/dW overwritten.
+ *   logits_out [B,HW,C] | NULL, argmax_out [B,HW] | NULL.
+ *   scalars: ADLM_STEP_NSCALARS doubles (device).
+ *   workspace: adlm_step_workspace_bytes(...) bytes (device, 256-byte aligned).
+ */
+ADLM_API size_t adlm_step_workspace_bytes(int B, int K, int HW, int N, int C);
+ADLM_API int adlm_step_fwd_bwd(const float* z, int B, int K, int HW,
+                      const float* P, const float* W, int N, int C,
+                      float eps, int prec_mode,
+                      const int32_t* target, const int32_t* proto_class, int ignore_void,
+                      float w_ce, float w_kld, float w_l1, float grad_scale,
+                      const int32_t* global_counts,
+                      float* logits_out, int32_t* argmax_out,
+                      float* dz, float* dP, float* dW,
+                      double* scalars, void* workspace, size_t workspace_bytes,
+                      void* stream);
+
+/*
+ * Loss normalisers of a batch shard: counts_out[0] = number of CE patches (module.py:156-165),
+ * counts_out[1] = number of KLD terms (module.py:186-206).  Data-parallel training sums these over
+ * ranks and passes the sums back as `global_counts` (device, 2 x int32; NULL = use the shard's own),
+ * so that the summed shard gradients equal the single-GPU gradient of the whole batch.
+ */
+ADLM_API int adlm_step_counts(const int32_t* target, int B, int HW,
+                     const int32_t* proto_class, int N, int C, int ignore_void,
+                     int32_t* counts_out, void* workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * Push, step 1: per-patch class bitmask from full-resolution labels.
+ *   labels [n_img,H,Wimg] uint8 (0 = void, class c = label-1);
+ *   row_lut [H], col_lut [Wimg] int32: pixel -> patch index, computed on the host with the
+ *   reference's float expression int(pixel / (H / h)) (push.py:201-202,217,219);
+ *   mask_out [n_img,h*w] uint32, bit c set iff >= 1 pixel of class c falls in the patch.
+ */
+ADLM_API int adlm_patch_class_mask(const uint8_t* labels, int n_img, int H, int Wimg,
+                          const int32_t* row_lut, const int32_t* col_lut, int h, int w,
+                          uint32_t* mask_out, void* stream);
+
+/*
+ * Push, step 2: streaming class-filtered nearest-patch search.
+ *   z [n_img,K,HW], mask [n_img,HW], P [N,K], proto_class [N].
+ *   packed_min [N] uint64, updated in place with
+ *       min(packed_min[j], (float_bits(d) << 32) | (patch_base + img*HW + patch))
+ *   over patches whose mask has bit proto_class[j].  d >= 0, so the IEEE bits order like the
+ *   values; ties resolve to the lowest global patch id (= earliest image, push.py:265).
+ *   Initialise with ADLM_PUSH_NONE.  patch_base + n_img*HW must be < 2^32.
+ */
+#define ADLM_PUSH_NONE 0x7fffffffffffffffULL
+ADLM_API int adlm_push_scan(const float* z, int n_img, int K, int HW,
+                   const uint32_t* mask, const float* P, int N, const int32_t* proto_class,
+                   long long patch_base, int prec_mode,
+                   unsigned long long* packed_min, void* stream);
+
+/*
+ * Push, step 3: fetch the winners that live in this shard.
+ *   For each prototype j whose packed id falls in [patch_base, patch_base + n_img*HW):
+ *   proto_out[j,:] = z[img,:,patch]; otherwise the row is left untouched (caller zero-fills:
+ *   prototypes with no candidate keep the zero vector, push.py:57-61).
+ */
+ADLM_API int adlm_push_gather(const float* z, int n_img, int K, int HW, long long patch_base,
+                     const unsigned long long* packed_min, int N,
+                     float* proto_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ADLM_HEAD_H */

@@ -77,11 +77,14 @@ def kld_groups(target_img, C):
 
 
 def step_loss(z, P, W, target, ignore_void=True, weights=(1.0, 0.25, 1e-4), ident=None,
-              dtype=np.float64, want_grads=True):
+              dtype=np.float64, want_grads=True, norm=None):
     """fwd + CE + KLD + L1 (+ analytic backward).  target (B,h,w) int, already resized.
 
     Returns dict(loss, cross_entropy, kld_loss, l1, n_correct, n_patches, [dz, dP, dW]).
     module.py:143-222; the backward is what loss.backward() (module.py:236) yields.
+    norm=(n_patches, n_kld_terms) replaces the two mean normalisers by given (whole-batch) counts: a
+    batch shard evaluated that way contributes its additive share of the whole-batch loss / gradients
+    (used to check the data-parallel split; not a reference code path).
     """
     w_ce, w_kld, w_l1 = weights
     z = z.astype(dtype)
@@ -108,7 +111,8 @@ def step_loss(z, P, W, target, ignore_void=True, weights=(1.0, 0.25, 1e-4), iden
         tt = tflat
     lg = logits[keep]
     lse = _logsumexp(lg, 1)
-    ce = float((lse - lg[np.arange(len(keep)), tt]).mean())
+    n_ce = len(keep) if norm is None else norm[0]
+    ce = float((lse - lg[np.arange(len(keep)), tt]).sum() / n_ce)
     n_correct = int((lg.argmax(1) == tt).sum())
 
     # KLD over distances (module.py:167-208)
@@ -128,14 +132,15 @@ def step_loss(z, P, W, target, ignore_void=True, weights=(1.0, 0.25, 1e-4), iden
                 terms.append((b, protos, pix, i, j, (kld1 + kld2) / 2.0, q, a))
     if terms:
         kvals = np.array([t[5] for t in terms])
-        kld_loss = float(np.exp(-kvals).mean())
+        n_terms = len(terms) if norm is None else norm[1]
+        kld_loss = float(np.exp(-kvals).sum() / n_terms)
     else:
         kld_loss = 0.0
     l1_mask = 1 - ident.T
     l1 = float(np.abs(W * l1_mask).sum())
     loss = w_ce * ce + w_kld * kld_loss + w_l1 * l1
     out = dict(loss=loss, cross_entropy=ce, kld_loss=kld_loss, l1=l1, n_correct=n_correct,
-               n_patches=int(len(keep)), logits=logits.reshape(B, h, w, C),
+               n_patches=int(len(keep)), n_kld_terms=len(terms), logits=logits.reshape(B, h, w, C),
                dist=d.reshape(B, hw, N).transpose(0, 2, 1).reshape(B, N, h, w))
     if not want_grads:
         return out
@@ -144,11 +149,11 @@ def step_loss(z, P, W, target, ignore_void=True, weights=(1.0, 0.25, 1e-4), iden
     dlogits = np.zeros((M, C), dtype=dtype)
     sm = np.exp(lg - lse[:, None])
     sm[np.arange(len(keep)), tt] -= 1
-    dlogits[keep] = sm * (w_ce / len(keep))
+    dlogits[keep] = sm * (w_ce / n_ce)
     dW = dlogits.T @ s + w_l1 * np.sign(W) * l1_mask
     Gd = (dlogits @ W) * (1 / (d + 1) - 1 / (d + EPS))
     if terms:
-        T = len(terms)
+        T = n_terms
         Gk = np.zeros((B, hw, N), dtype=dtype)
         for (b, protos, pix, i, j, kld, q, a) in terms:
             c = w_kld * (-np.exp(-kld)) / T

@@ -51,3 +51,38 @@ def argmax_agreement(logits, logits_ref, tol):
         if gap > t:
             unexplained += 1
     return 1.0 - len(bad) / len(am), unexplained
+
+
+def torch_head_reference(z, P, W, dlogits=None, ddist=None, dsim=None, activation='log', dtype=None):
+    """Plain torch restatement of model.py:203-283 on CPU (float64 by default) with autograd, for upstream
+    gradients the oracle's analytic step does not cover.  Returns dict(logits, dist, sim, dz, dP, dW)."""
+    import torch
+    import torch.nn.functional as F
+    dtype = dtype or torch.float64
+    zt = torch.tensor(z, dtype=dtype, requires_grad=True)
+    Pt = torch.tensor(P, dtype=dtype, requires_grad=True)
+    Wt = torch.tensor(W, dtype=dtype, requires_grad=True)
+    N, K = Pt.shape
+    x2 = F.conv2d(zt ** 2, torch.ones(N, K, 1, 1, dtype=dtype))
+    xp = F.conv2d(zt, Pt.reshape(N, K, 1, 1))
+    dist = F.relu(x2 + (-2 * xp + (Pt ** 2).sum(1).view(-1, 1, 1)))
+    dv = dist.permute(0, 2, 3, 1).reshape(-1, N)
+    sim = torch.log((dv + 1) / (dv + EPS)) if activation == 'log' else -dv
+    logits = (sim @ Wt.t()).reshape(z.shape[0], z.shape[2], z.shape[3], -1)
+    out = dict(logits=logits.detach().numpy(), dist=dist.detach().numpy(), sim=sim.detach().numpy())
+    tot = None
+    for t, g in ((logits, dlogits), (dist, ddist), (sim, dsim)):
+        if g is not None:
+            term = (t * torch.tensor(g, dtype=dtype).reshape(t.shape)).sum()
+            tot = term if tot is None else tot + term
+    if tot is not None:
+        tot.backward()
+        out.update(dz=zt.grad.numpy(), dP=Pt.grad.numpy(), dW=None if Wt.grad is None else Wt.grad.numpy())
+    return out
+
+
+def rel_err(a, b):
+    """max |a-b| / max |b|"""
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-300))

@@ -1,0 +1,178 @@
+"""GPU parity of the head forward / backward through the C ABI (adlm_head_fwd / adlm_head_bwd) against
+the reference-generated golden vectors, the oracle and a float64 torch restatement.
+
+Tolerances (BASELINE.json): similarities / logits within 1e-3 relative (1e-5 for fp32 and 3xTF32) on top
+of the bound the reference's own fp32 distance error propagates to (tests/parity.py); argmax bit-exact
+except near-ties inside that bound (counted and asserted to be explained)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import head_oracle as orc
+import parity
+from adlm_inherently_interpretable_segmentation_b200 import head, synth
+
+pytestmark = pytest.mark.gpu
+
+FWD = ["head_fwd_small_A", "head_fwd_small_B", "head_fwd_mds", "head_fwd_k32"]
+# precision -> (distance abs tolerance in units of K*2^-21, relative tolerance on sims/logits)
+PRECISIONS = {"fp32": (4.0, 1e-5), "tf32x3": (6.0, 1e-5), "tf32": (None, 1e-3)}
+
+
+def available(prec):
+    """tcgen05 modes are skipped only while the library reports them as not built (ADLM_E_UNSUPPORTED)"""
+    z = torch.rand(1, 8, 4, 4, device="cuda")
+    P = torch.rand(8, 8, device="cuda")
+    W = torch.rand(2, 8, device="cuda")
+    try:
+        head.head_forward(z, P, W, precision=prec)
+        return True
+    except NotImplementedError:
+        return False
+
+
+def cuda(*arrs):
+    return [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in arrs]
+
+
+def dist_delta(prec, K, z=None, P=None):
+    ulps, _ = PRECISIONS[prec]
+    if ulps is not None:
+        return ulps * K * 2.0 ** -21
+    # 1xTF32 on centred operands: |z-0.5|,|p-0.5| <= 0.5 rounded to 11 bits -> K * 2 * 0.25 * 2^-11 worst case
+    return K * 0.5 * 2.0 ** -11
+
+
+@pytest.mark.parametrize("prec", list(PRECISIONS))
+@pytest.mark.parametrize("name", FWD)
+def test_forward_matches_reference_golden(golden, name, prec):
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    g = golden(name)
+    z, P, W = cuda(g["z"], g["P"], g["W"])
+    out = head.head_forward(z, P, W, precision=prec, want_dist=True, want_sim=True, want_argmax=True)
+    B, K, h, w = g["z"].shape
+    N, C = g["P"].shape[0], g["W"].shape[0]
+    dist, sim = out["dist"].cpu().numpy(), out["sim"].cpu().numpy()
+    logits, amax = out["logits"].cpu().numpy(), out["argmax"].cpu().numpy()
+    assert dist.shape == g["dist"].shape and logits.shape == g["logits"].shape and sim.shape == g["act"].shape
+    delta = dist_delta(prec, K)
+    rel = PRECISIONS[prec][1]
+    assert dist.min() >= 0
+    assert np.abs(dist - g["dist"]).max() <= delta
+    dref = parity.dist_MN(g["dist"])
+    assert np.all(np.abs(sim - g["act"]) <= parity.sim_tol(dref, delta, rel) + 1e-6)
+    tol = parity.logit_tol(dref, g["W"], delta, rel)
+    assert np.all(np.abs(logits.reshape(-1, C) - g["logits"].reshape(-1, C)) <= tol + 1e-5)
+    # logits must be the last layer applied to the similarities this kernel produced
+    assert np.allclose(logits.reshape(-1, C), sim.astype(np.float64) @ g["W"].astype(np.float64).T,
+                       rtol=2e-3 if prec == "tf32" else 1e-5, atol=1e-3 if prec == "tf32" else 2e-4)
+    assert np.array_equal(amax.reshape(-1), logits.reshape(-1, C).argmax(1))
+    agree, unexplained = parity.argmax_agreement(logits, g["logits"], tol)
+    assert unexplained == 0 and agree > (0.97 if prec == "tf32" else 0.99)
+
+
+@pytest.mark.parametrize("prec", list(PRECISIONS))
+def test_forward_cfg1_full_size(golden, prec):
+    """BASELINE configs[0]: 2x64x65x65 features, 190 prototypes x 64-d, fp32 forward + last layer"""
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    g = golden("head_fwd_cfg1")
+    B, K, h, w, N, C, seed = [int(v) for v in g["meta"]]
+    zn, Pn, Wn = synth.head_inputs(B, K, h, w, N, C, regime="A", w_noise=0.0, seed=seed)
+    z, P, W = cuda(zn, Pn, Wn)
+    out = head.head_forward(z, P, W, precision=prec, want_dist=True, want_argmax=True)
+    dist = out["dist"].cpu().numpy().reshape(B, N, h * w)
+    assert np.abs(dist[:, ::7, ::13] - g["dist_sample"]).max() <= dist_delta(prec, K)
+    logits = out["logits"].cpu().numpy()
+    rel = 1e-3 if prec == "tf32" else 1e-4
+    assert np.allclose(logits, g["logits"], rtol=rel, atol=rel * np.abs(g["logits"]).max())
+    assert (logits.argmax(-1) == g["logits"].argmax(-1)).mean() > (0.999 if prec == "tf32" else 0.9999)
+    # outputs that were not requested are not needed for the same logits
+    only = head.head_forward(z, P, W, precision=prec, want_dist=False)
+    assert only["dist"] is None and torch.equal(only["logits"], out["logits"])
+
+
+@pytest.mark.parametrize("prec", list(PRECISIONS))
+def test_linear_activation_and_odd_shapes(prec):
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    for (B, K, h, w, N, C) in [(1, 24, 3, 5, 7, 2), (3, 64, 11, 13, 70, 7), (2, 128, 9, 9, 130, 13)]:
+        zn = synth.features(B, K, h, w, 5)
+        Pn = np.random.default_rng(6).random((N, K)).astype(np.float32)
+        Wn = np.random.default_rng(7).standard_normal((C, N)).astype(np.float32)
+        ref = parity.torch_head_reference(zn, Pn, Wn, activation='linear')
+        z, P, W = cuda(zn, Pn, Wn)
+        out = head.head_forward(z, P, W, activation="linear", precision=prec, want_sim=True)
+        tol = dist_delta(prec, K) * 2
+        assert np.abs(out["dist"].cpu().numpy() - ref["dist"]).max() <= tol
+        assert np.abs(out["sim"].cpu().numpy() - ref["sim"]).max() <= tol
+        lt = tol * np.abs(Wn).sum(1).max() + 1e-3 * np.abs(ref["logits"]).max() * (prec == "tf32") + 1e-4
+        assert np.abs(out["logits"].cpu().numpy() - ref["logits"]).max() <= lt
+
+
+@pytest.mark.parametrize("prec", list(PRECISIONS))
+@pytest.mark.parametrize("case", ["logits", "dist", "sim", "all"])
+def test_backward_matches_float64_autograd(prec, case):
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    B, K, h, w, N, C = 2, 64, 9, 11, 190, 19
+    zn, Pn, Wn = synth.head_inputs(B, K, h, w, N, C, regime="A", w_noise=0.1, seed=77)
+    rng = np.random.default_rng(3)
+    M = B * h * w
+    dl = (rng.standard_normal((B, h, w, C)) / M).astype(np.float32) if case in ("logits", "all") else None
+    dd = (rng.standard_normal((B, N, h, w)) / M).astype(np.float32) if case in ("dist", "all") else None
+    ds = (rng.standard_normal((M, N)) / M).astype(np.float32) if case in ("sim", "all") else None
+    ref = parity.torch_head_reference(zn, Pn, Wn, dl, dd, ds)
+    z, P, W = cuda(zn, Pn, Wn)
+    g = [None if a is None else torch.from_numpy(a).cuda() for a in (dl, dd, ds)]
+    dz, dP, dW = head.head_backward(z, P, W, g[0], g[1], g[2], precision=prec)
+    tol = 2e-3 if prec == "tf32" else 2e-5
+    assert parity.rel_err(dz.cpu().numpy(), ref["dz"]) <= tol
+    assert parity.rel_err(dP.cpu().numpy(), ref["dP"]) <= tol
+    if case in ("logits", "all"):
+        assert parity.rel_err(dW.cpu().numpy(), ref["dW"]) <= tol
+    else:
+        assert float(dW.abs().max()) == 0.0
+
+
+def test_backward_only_what_is_needed():
+    B, K, h, w, N, C = 1, 32, 5, 6, 20, 4
+    zn, Pn, Wn = synth.head_inputs(B, K, h, w, N, C, seed=8)
+    z, P, W = cuda(zn, Pn, Wn)
+    dl = torch.randn(B, h, w, C, device="cuda")
+    full = head.head_backward(z, P, W, dl)
+    only_w = head.head_backward(z, P, W, dl, need_dz=False, need_dP=False)
+    assert only_w[0] is None and only_w[1] is None and torch.allclose(only_w[2], full[2], rtol=1e-5, atol=1e-6)
+    only_z = head.head_backward(z, P, W, dl, need_dP=False, need_dW=False)
+    assert torch.allclose(only_z[0], full[0], rtol=1e-5, atol=1e-6) and only_z[2] is None
+
+
+@pytest.mark.parametrize("prec", list(PRECISIONS))
+def test_properties_at_benchmark_size(prec):
+    """size-independent properties at BASELINE configs[1]'s head size (16 x 64 x 65 x 65, 190 x 64):
+    d >= 0; a prototype copied from a pixel has d ~ 0 there and s ~ log(1/eps); permuting prototypes
+    permutes distance planes and leaves logits unchanged when W is permuted alike; batch shards agree."""
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    B, K, h, w, N, C = 16, 64, 65, 65, 190, 19
+    zn, Pn, Wn = synth.head_inputs(B, K, h, w, N, C, regime="B", w_noise=0.1, seed=123)
+    z, P, W = cuda(zn, Pn, Wn)
+    out = head.head_forward(z, P, W, precision=prec, want_dist=True, want_argmax=True)
+    dist = out["dist"]
+    assert float(dist.min()) >= 0.0 and bool(torch.isfinite(out["logits"]).all())
+    zf = z.permute(0, 2, 3, 1).reshape(-1, K)
+    # prototypes that sit on a pixel: their minimum distance is ~0
+    on_pixel = (torch.cdist(P, zf).min(dim=1).values < 1e-5).nonzero().flatten()
+    assert on_pixel.numel() > 50
+    dmin = dist.permute(1, 0, 2, 3).reshape(N, -1).min(dim=1).values
+    delta = dist_delta(prec, K)
+    assert bool((dmin[on_pixel] <= delta).all())
+    perm = torch.randperm(N, device="cuda", generator=torch.Generator(device="cuda").manual_seed(1))
+    outp = head.head_forward(z, P[perm].contiguous(), W[:, perm].contiguous(), precision=prec, want_dist=True)
+    assert torch.equal(outp["dist"], dist[:, perm])
+    ltol = (1e-3 if prec == "tf32" else 2e-5) * float(out["logits"].abs().max())
+    assert float((outp["logits"] - out["logits"]).abs().max()) <= ltol
+    # batch shards (the multi-GPU split) give bit-identical rows
+    half = head.head_forward(z[8:], P, W, precision=prec, want_dist=False, want_argmax=True)
+    assert torch.equal(half["logits"], out["logits"][8:]) and torch.equal(half["argmax"], out["argmax"][8:])

@@ -1,0 +1,154 @@
+"""GPU parity of the fused training step (adlm_step_fwd_bwd: forward + CE + KLD + masked L1 + backward,
+segmentation/module.py:137-222,236) against fixtures produced by the reference's own _step and against the
+oracle, plus the data-parallel split on one device."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import head_oracle as orc
+import parity
+from adlm_inherently_interpretable_segmentation_b200 import head, parallel, synth
+from test_gpu_head import available, cuda
+
+pytestmark = pytest.mark.gpu
+
+# (loss tolerance, gradient tolerance) per fixture: regime B sits prototypes ON pixels (d == 0), where the
+# reference's own fp32 distances carry ~2.5e-5 noise against ds/dd = -1e4 (tests/test_oracle_golden.py)
+STEP_TOL = {"step_small_A": (2e-5, 2e-4), "step_novoid": (2e-5, 2e-4), "step_small_B": (2e-3, 0.15)}
+PREC_SCALE = {"fp32": 1.0, "tf32x3": 1.0, "tf32": 50.0}
+
+
+def run_step(g, prec, **kw):
+    z, P, W = cuda(g["z"], g["P"], g["W"])
+    target = torch.from_numpy(g["target"].astype(np.int32)).cuda()
+    N, C = g["P"].shape[0], g["W"].shape[0]
+    pc = torch.arange(N, dtype=torch.int32, device="cuda") // (N // C)
+    return head.fused_step(z, P, W, target, pc, ignore_void=bool(g["ignore_void"]),
+                           weights=tuple(float(x) for x in g["weights"]), precision=prec, **kw)
+
+
+@pytest.mark.parametrize("prec", list(PREC_SCALE))
+@pytest.mark.parametrize("name", list(STEP_TOL))
+def test_step_matches_reference_step(golden, name, prec):
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    g = golden(name)
+    ltol, gtol = (t * PREC_SCALE[prec] for t in STEP_TOL[name])
+    res = run_step(g, prec, want_logits=True, want_argmax=True)
+    sc = res.scalars.cpu().numpy()
+    assert int(sc[5]) == int(g["n_patches"])
+    assert sc[1] == pytest.approx(float(g["cross_entropy"]), rel=ltol)
+    assert sc[2] == pytest.approx(float(g["kld_loss"]), rel=max(ltol, 2e-5))
+    assert sc[0] == pytest.approx(float(g["loss"]), rel=ltol)
+    assert abs(int(sc[4]) - int(g["n_correct"])) <= (1 if prec != "tf32" else 3)
+    for key, got in (("dz", res.dz), ("dP", res.dP.reshape(g["dP"].shape)), ("dW", res.dW)):
+        assert parity.rel_err(got.cpu().numpy(), g[key]) <= gtol, key
+    # the oracle (float64 restatement, pinned to the same fixtures) agrees on the pieces the fixture lacks
+    o = orc.step_loss(g["z"], g["P"], g["W"], g["target"], ignore_void=bool(g["ignore_void"]),
+                      weights=tuple(g["weights"]), want_grads=False)
+    assert sc[3] == pytest.approx(o["l1"], rel=1e-5) and int(sc[6]) == o["n_kld_terms"]
+
+
+@pytest.mark.parametrize("prec", list(PREC_SCALE))
+def test_step_loss_only_and_grad_scale(golden, prec):
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    g = golden("step_small_A")
+    full = run_step(g, prec)
+    val = run_step(g, prec, need_grads=False)          # validation step: no gradients requested
+    assert val.dz is None and val.dP is None and val.dW is None
+    assert torch.allclose(val.scalars, full.scalars, rtol=1e-6)
+    fifth = run_step(g, prec, grad_scale=0.2)          # module.py:236 divides the loss by iter_size
+    for a, b in ((fifth.dz, full.dz), (fifth.dP, full.dP), (fifth.dW, full.dW)):
+        assert parity.rel_err(a.cpu().numpy(), 0.2 * b.cpu().numpy()) <= 1e-4
+    assert torch.allclose(fifth.scalars[:4], full.scalars[:4], rtol=1e-6)
+
+
+def test_step_edge_cases():
+    """all-void image, a label value with a single pixel, label == C (skipped by the KLD bound check),
+    and a prototype class that never appears"""
+    B, K, h, w, N, C = 3, 32, 6, 7, 20, 4
+    zn, Pn, Wn = synth.head_inputs(B, K, h, w, N, C, w_noise=0.1, seed=31)
+    target = synth.block_labels(B, h, w, C, block=2, seed=32).astype(np.int64)
+    target[0] = 0                      # void-only image: contributes a KLD group for class 0 (the quirk)
+    target[1][target[1] == 3] = 1      # class 3 absent from image 1
+    target[1, 0, 0] = 3                # ... except one pixel: group skipped (< 2 pixels)
+    target[2, :2] = C                  # label C: valid CE class C-1, no KLD group
+    o = orc.step_loss(zn, Pn, Wn, target)
+    z, P, W = cuda(zn, Pn, Wn)
+    pc = torch.arange(N, dtype=torch.int32, device="cuda") // (N // C)
+    res = head.fused_step(z, P, W, torch.from_numpy(target).cuda(), pc)
+    sc = res.scalars.cpu().numpy()
+    assert int(sc[5]) == o["n_patches"] and int(sc[6]) == o["n_kld_terms"]
+    assert sc[0] == pytest.approx(o["loss"], rel=2e-5) and sc[2] == pytest.approx(o["kld_loss"], rel=2e-5)
+    assert parity.rel_err(res.dz.cpu().numpy(), o["dz"]) <= 2e-4
+    assert parity.rel_err(res.dP.cpu().numpy().reshape(N, K), o["dP"]) <= 2e-4
+    assert parity.rel_err(res.dW.cpu().numpy(), o["dW"]) <= 2e-4
+    # no KLD term at all -> kld_loss == 0.0 (module.py:207-208)
+    r1 = head.fused_step(z[:1], P, W, torch.from_numpy(np.full((1, h, w), C)).cuda(), pc)
+    assert float(r1.scalars[2]) == 0.0 and int(r1.scalars[6]) == 0
+
+
+@pytest.mark.parametrize("prec", list(PREC_SCALE))
+def test_step_at_benchmark_size_matches_oracle(prec):
+    """BASELINE configs[1] head size would take the float64 oracle minutes; B=4 of the same 65x65x190x64
+    shape runs in seconds and exercises tail tiles (4225 = 33*128 + 1) and every class."""
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    B, K, h, w, N, C = 4, 64, 65, 65, 190, 19
+    zn, Pn, Wn = synth.head_inputs(B, K, h, w, N, C, regime="A", w_noise=0.1, seed=41)
+    target = synth.block_labels(B, h, w, C, block=8, seed=42).astype(np.int64)
+    o = orc.step_loss(zn, Pn, Wn, target)
+    z, P, W = cuda(zn, Pn, Wn)
+    pc = torch.arange(N, dtype=torch.int32, device="cuda") // (N // C)
+    res = head.fused_step(z, P, W, torch.from_numpy(target).cuda(), pc, precision=prec)
+    sc = res.scalars.cpu().numpy()
+    s = PREC_SCALE[prec]
+    assert sc[0] == pytest.approx(o["loss"], rel=2e-5 * s) and sc[1] == pytest.approx(o["cross_entropy"], rel=2e-5 * s)
+    assert sc[2] == pytest.approx(o["kld_loss"], rel=2e-5 * s)
+    assert abs(int(sc[4]) - o["n_correct"]) <= 2
+    assert parity.rel_err(res.dz.cpu().numpy(), o["dz"]) <= 2e-4 * s
+    assert parity.rel_err(res.dP.cpu().numpy().reshape(N, K), o["dP"]) <= 2e-4 * s
+    assert parity.rel_err(res.dW.cpu().numpy(), o["dW"]) <= 2e-4 * s
+
+
+def test_data_parallel_split_on_one_device():
+    """two shards evaluated with the whole batch's normalisers sum to the whole-batch step (the N>1 path of
+    parallel.dp_fused_step, run sequentially on one GPU)"""
+    B, K, h, w, N, C = 4, 64, 13, 17, 190, 19
+    zn, Pn, Wn = synth.head_inputs(B, K, h, w, N, C, w_noise=0.1, seed=51)
+    target = torch.from_numpy(synth.block_labels(B, h, w, C, block=3, seed=52).astype(np.int32)).cuda()
+    z, P, W = cuda(zn, Pn, Wn)
+    pc = torch.arange(N, dtype=torch.int32, device="cuda") // (N // C)
+    wts = (1.0, 0.25, 1e-4)
+    full = head.fused_step(z, P, W, target, pc, weights=wts)
+    counts = sum(head.step_counts(target[lo:hi], pc, C) for lo, hi in ((0, 2), (2, 4)))
+    assert counts.cpu().tolist() == [int(full.scalars[5]), int(full.scalars[6])]
+    parts = [head.fused_step(z[lo:hi], P, W, target[lo:hi], pc, weights=(wts[0], wts[1], wts[2] / 2),
+                             global_counts=counts.to(torch.int32)) for lo, hi in ((0, 2), (2, 4))]
+    assert parity.rel_err((parts[0].dP + parts[1].dP).cpu().numpy(), full.dP.cpu().numpy()) <= 1e-5
+    assert parity.rel_err((parts[0].dW + parts[1].dW).cpu().numpy(), full.dW.cpu().numpy()) <= 1e-5
+    assert parity.rel_err(torch.cat([parts[0].dz, parts[1].dz]).cpu().numpy(), full.dz.cpu().numpy()) <= 1e-5
+    assert float(parts[0].scalars[0] + parts[1].scalars[0]) == pytest.approx(float(full.scalars[0]), rel=1e-6)
+    # single-process world: dp_fused_step degenerates to the plain step
+    one = parallel.dp_fused_step((P, W), z, target, pc, weights=wts)
+    assert torch.allclose(one.scalars, full.scalars, rtol=1e-6)
+
+
+def test_autograd_function_continues_into_the_features():
+    B, K, h, w, N, C = 2, 32, 5, 6, 20, 4
+    zn, Pn, Wn = synth.head_inputs(B, K, h, w, N, C, w_noise=0.1, seed=61)
+    target = torch.from_numpy(synth.block_labels(B, h, w, C, block=2, seed=62).astype(np.int32)).cuda()
+    pre = torch.randn(B, K, h, w, device="cuda", requires_grad=True)
+    P = torch.from_numpy(Pn).cuda().requires_grad_(True)
+    W = torch.from_numpy(Wn).cuda().requires_grad_(True)
+    pc = torch.arange(N, dtype=torch.int32, device="cuda") // (N // C)
+    cfg = dict(ignore_void=True, weights=(1.0, 0.25, 1e-4), grad_scale=1.0, eps=1e-4, precision=None)
+    z = torch.sigmoid(pre)
+    loss, scalars = head.FusedStepFunction.apply(z, P, W, target, pc, cfg)
+    (loss / 5).backward()
+    res = head.fused_step(z.detach(), P.detach(), W.detach(), target, pc)
+    assert torch.allclose(P.grad, res.dP / 5, rtol=1e-5, atol=1e-8)
+    assert torch.allclose(W.grad, res.dW / 5, rtol=1e-5, atol=1e-8)
+    zd = z.detach()
+    assert torch.allclose(pre.grad, res.dz / 5 * zd * (1 - zd), rtol=1e-4, atol=1e-9)

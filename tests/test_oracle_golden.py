@@ -102,3 +102,39 @@ def test_patch_mask_matches_python_loop():
     for c in range(19):
         got = {(int(a), int(b)) for a, b in zip(*np.nonzero((mask >> np.uint32(c)) & np.uint32(1)))}
         assert got == sets[c]
+
+
+# ---- the torch-CPU port (oracle/torch_port.py: the reference's own operator sequence, used as the timed CPU
+# baseline on the GPU box) is pinned to the same reference-generated fixtures
+@pytest.mark.parametrize("name", ["step_small_A", "step_small_B", "step_novoid"])
+def test_torch_port_step_matches_reference(golden, name):
+    import torch
+    from oracle import torch_port as tp
+    g = golden(name)
+    N, K = g["P"].shape
+    C = g["W"].shape[0]
+    z = torch.from_numpy(g["z"]).requires_grad_(True)
+    P4 = torch.from_numpy(g["P"]).reshape(N, K, 1, 1).requires_grad_(True)
+    W = torch.from_numpy(g["W"]).requires_grad_(True)
+    r = tp.step(z, P4, W, torch.from_numpy(g["target"].astype(np.int64)), tp.class_identity(N, C),
+                ignore_void=bool(g["ignore_void"]), weights=tuple(float(v) for v in g["weights"]))
+    # same ops, same order, same library: agreement to fp32 rounding of the thread-count-dependent reductions
+    assert r["loss"] == pytest.approx(float(g["loss"]), rel=1e-5)
+    assert r["kld_loss"] == pytest.approx(float(g["kld_loss"]), rel=1e-5)
+    assert r["n_patches"] == int(g["n_patches"]) and abs(r["n_correct"] - int(g["n_correct"])) <= 1
+    for got, key in ((z.grad, "dz"), (P4.grad.reshape(N, K), "dP"), (W.grad, "dW")):
+        assert parity.rel_err(got.numpy(), g[key]) <= (0.05 if name == "step_small_B" else 1e-4), key
+
+
+def test_torch_port_push_matches_reference(golden):
+    import torch
+    from oracle import torch_port as tp
+    g = golden("push_mds")
+    n_img, K, h, w, N, C, H, Wimg, seed = [int(v) for v in g["meta"]]
+    gmin = np.full(N, np.inf)
+    gpatch = np.zeros((N, K))
+    P4 = torch.from_numpy(g["P"]).reshape(N, K, 1, 1)
+    for i in range(n_img):
+        tp.push_image(torch.from_numpy(g["z"][i:i + 1]), P4, g["labels"][i], C, gmin, gpatch, i)
+    assert np.allclose(gmin, g["gmin"], atol=1e-6)
+    assert (np.all(gpatch == g["gpatch"], axis=1)).mean() >= 0.95   # set-order ties (push.py:230) may differ
