@@ -161,7 +161,8 @@ def test_push_prototypes_end_to_end(tmp_path):
     push.push_prototypes(ds, net, root_dir_for_saving_prototypes=out_dir, epoch_number=7,
                          proto_bound_boxes_filename_prefix="bb", log=logs.append)
     ui, dup = orc.push_finalize(opatch)
-    assert net.num_prototypes == len(ui) == N - len(dup) and len(dup) == 9   # 10 zero vectors collapse to 1
+    # 10 zero vectors (absent class) collapse to 1; same-class prototypes that picked the same patch collapse too
+    assert net.num_prototypes == len(ui) == N - len(dup) and len(dup) >= 9
     got = net.prototype_vectors.detach().cpu().numpy().reshape(-1, K)
     assert np.allclose(got, opatch[ui].astype(np.float32), atol=0)
     assert json.load(open(os.path.join(out_dir, "unique_prototypes.json"))) == [int(i) for i in ui]
@@ -175,4 +176,6 @@ def test_push_prototypes_end_to_end(tmp_path):
     # the pushed prototypes now sit on feature pixels: distance ~0 at the winner patch
     with torch.no_grad():
         d = net._l2_convolution(torch.from_numpy(feats).cuda())
-    assert float(d.flatten(2).min(dim=2).values.min(dim=0).values[:len(ui) - 1].max()) <= 16 * 2.0 ** -19
+    dmin = d.flatten(2).min(dim=2).values.min(dim=0).values.cpu().numpy()
+    pushed = np.abs(got).sum(1) > 0
+    assert pushed.sum() == len(ui) - 1 and dmin[pushed].max() <= 16 * 2.0 ** -19
