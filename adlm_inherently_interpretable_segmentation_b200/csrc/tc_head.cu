@@ -1,21 +1,423 @@
+// ADLM_PREC_TF32 / ADLM_PREC_TF32X3 path: the prototype head on the 5th-generation tensor cores.
+//
+// Forward (k_tc_fwd), per 128-pixel tile, one thread per pixel (= one TMEM lane):
+//   convert   z[k][px] (NCHW, coalesced LDG, prefetched one tile ahead) -> centred (z - 1/2; squared L2
+//             distance is translation invariant), rounded to nearest tf32 (hi [+ lo for 3xTF32]) ->
+//             shared-memory A operand [K/4][128 px][4 k]; |z|^2 accumulated in a register.
+//             (TMA cannot fetch this tile: the NCHW row pitch h*w*4 B is not a multiple of 16 for the
+//             reference's odd maps — 65x65, 129x257 — and a register pass is needed anyway to round/split.)
+//   MMA1      D1[128 x Npad] = A . Pk^T     tcgen05.mma kind::tf32, accumulator in TMEM
+//   epilogue1 tcgen05.ld -> d = max(|z|^2 - 2 acc + |p|^2, 0) -> s = log((d+1)/(d+eps)); optional streaming
+//             stores of d (NCHW), s, own-class distances; s is written back over D1 (tcgen05.st)
+//   MMA2      D2[128 x Cpad] = S . W^T      A operand straight from TMEM (.ts form): the similarity matrix
+//             never touches shared or global memory
+//   epilogue2 logits (B,h,w,C) + per-pixel argmax
+// Two warpgroups per CTA run this pipeline on alternating tiles, so one group's MUFU-bound epilogue
+// overlaps the other's loads and MMAs; the grid is persistent (one CTA per SM).
+// 3xTF32 keeps fp32-class distances (hi*lo + lo*hi + hi*hi) and does the last layer in fp32 FMA.
 #include "tc_head.cuh"
+#include "tc_common.cuh"
 
 namespace adlm {
 
-int tc_head_fwd(const HeadShape&, int, const float*, const float*, const float*, float*, float*, float*,
-                int32_t*, const StepExtras&, cudaStream_t) {
-  set_error("tc_head_fwd: tcgen05 path not built yet");
-  return ADLM_E_UNSUPPORTED;
+namespace {
+
+using namespace tc;
+
+constexpr int TILE = 128;
+constexpr int JMAX = ADLM_MAX_PROTOS_PER_CLASS;
+constexpr float LN2 = 0.6931471805599453f;
+constexpr float CENTRE = 0.5f;
+
+struct TcFwdParams {
+  const float* z;
+  const float* P;
+  const float* W;
+  float* logits;
+  float* dist;
+  float* sim;
+  int32_t* argmax;
+  const int32_t* target;
+  const int32_t* proto_class;
+  const int32_t* proto_rank;
+  float* own_dist;
+  int B, K, HW, N, C;
+  float eps;
+  int act_mode;
+  int Npad, Cpad;
+  long long M;
+  int num_tiles;
+};
+
+template <int KP, bool X3>
+struct FwdSmem {
+  static constexpr int NWG = X3 ? 1 : 2;
+  static constexpr int PARTS = X3 ? 2 : 1;
+  // byte offsets
+  static __host__ __device__ size_t pk(int part, int Npad) { return (size_t)part * KP * Npad * 4; }
+  static __host__ __device__ size_t wk(int Npad) { return (size_t)PARTS * KP * Npad * 4; }
+  static __host__ __device__ size_t wk_bytes(int Npad, int Cpad) { return (size_t)Npad * (X3 ? 32 : Cpad) * 4; }
+  static __host__ __device__ size_t abuf(int wg, int part, int Npad, int Cpad) {
+    return wk(Npad) + wk_bytes(Npad, Cpad) + ((size_t)wg * PARTS + part) * KP * TILE * 4;
+  }
+  static __host__ __device__ size_t misc(int Npad, int Cpad) { return abuf(NWG, 0, Npad, Cpad); }
+  static __host__ __device__ size_t total(int Npad, int Cpad) {
+    // p2 [Npad] f32, class [Npad] i32, rank [Npad] i32, chunk class masks [Npad/16] u32, barriers, tmem base
+    return misc(Npad, Cpad) + (size_t)Npad * 12 + (size_t)(Npad / 16) * 4 + 64 + 16;
+  }
+};
+
+template <int KP, bool X3>
+__global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const TcFwdParams p) {
+  using L = FwdSmem<KP, X3>;
+  constexpr int NWG = L::NWG;
+  constexpr int NTHREADS = NWG * 128;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const int Npad = p.Npad, Cpad = p.Cpad, K = p.K, N = p.N, C = p.C, HW = p.HW;
+  float* Pk_hi = reinterpret_cast<float*>(smem + L::pk(0, Npad));
+  float* Pk_lo = reinterpret_cast<float*>(smem + L::pk(X3 ? 1 : 0, Npad));
+  float* Wk = reinterpret_cast<float*>(smem + L::wk(Npad));
+  uint8_t* misc = smem + L::misc(Npad, Cpad);
+  float* p2s = reinterpret_cast<float*>(misc);
+  int* pcs = reinterpret_cast<int*>(misc + (size_t)Npad * 4);
+  int* prs = reinterpret_cast<int*>(misc + (size_t)Npad * 8);
+  uint32_t* cmask = reinterpret_cast<uint32_t*>(misc + (size_t)Npad * 12);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(misc + (size_t)Npad * 12 + (size_t)(Npad / 16) * 4 + ((16 - ((Npad / 16) * 4) % 16) % 16));
+  uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 4);
+
+  const int tid = threadIdx.x, wg = tid >> 7, wt = tid & 127, warp_in_wg = wt >> 5;
+  const bool want_own = p.own_dist != nullptr;
+
+  // ---- one-time setup: TMEM, barriers, prototype / last-layer operands ----
+  if (tid < 32) tmem_alloc(smem_u32(tmem_base_s), NWG * 256);
+  if (tid == 32) {
+    for (int i = 0; i < 4; ++i) mbar_init(smem_u32(&bars[i]), 1);
+    mbar_init_fence();
+  }
+  // Pk: [KP/4][Npad][4], centred and rounded (3xTF32: hi and lo = rna(x - hi))
+  for (int idx = tid; idx < (KP / 4) * Npad; idx += NTHREADS) {
+    const int n = idx % Npad, k4 = idx / Npad;
+    float hi[4], lo[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int k = k4 * 4 + j;
+      const float v = (n < N && k < K) ? __ldg(p.P + (size_t)n * K + k) - CENTRE : 0.f;
+      hi[j] = rna_tf32(v);
+      lo[j] = X3 ? rna_tf32(v - hi[j]) : 0.f;
+    }
+    *reinterpret_cast<float4*>(Pk_hi + (size_t)idx * 4) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+    if (X3) *reinterpret_cast<float4*>(Pk_lo + (size_t)idx * 4) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+  }
+  if (!X3) {
+    // Wk: B operand of MMA2, rows = classes, K index = prototype: [Npad/4][Cpad][4]
+    for (int idx = tid; idx < Npad * Cpad; idx += NTHREADS) {
+      const int n = idx / Cpad, c = idx - n * Cpad;
+      const float v = (c < C && n < N) ? __ldg(p.W + (size_t)c * N + n) : 0.f;
+      Wk[(size_t)(n >> 2) * Cpad * 4 + c * 4 + (n & 3)] = rna_tf32(v);
+    }
+  } else {
+    // plain fp32 [Npad][32] for the CUDA-core last layer
+    for (int idx = tid; idx < Npad * 32; idx += NTHREADS) {
+      const int n = idx >> 5, c = idx & 31;
+      Wk[idx] = (c < C && n < N) ? __ldg(p.W + (size_t)c * N + n) : 0.f;
+    }
+  }
+  for (int n = tid; n < Npad; n += NTHREADS) {
+    float a = 0.f;
+    if (n < N) {
+      for (int k = 0; k < K; ++k) {
+        const float v = __ldg(p.P + (size_t)n * K + k) - CENTRE;
+        const float u = X3 ? v : rna_tf32(v);   // 1xTF32: |p|^2 of the ROUNDED vector, so that z == p gives d == 0
+        a = fmaf(u, u, a);
+      }
+    }
+    p2s[n] = a;
+    pcs[n] = (want_own && n < N) ? p.proto_class[n] : -1;
+    prs[n] = (want_own && n < N) ? p.proto_rank[n] : 0;
+  }
+  __syncthreads();
+  for (int c = tid; c < Npad / 16; c += NTHREADS) {
+    uint32_t m = 0u;
+    for (int i = 0; i < 16; ++i) {
+      const int pc = pcs[c * 16 + i];
+      if (pc >= 0 && pc < 32) m |= 1u << pc;
+    }
+    cmask[c] = m;
+  }
+  fence_async_smem();
+  fence_before();
+  __syncthreads();
+  fence_after();
+
+  const uint32_t tmem_base = *tmem_base_s;
+  const uint32_t d1 = tmem_base + wg * 256;              // [128 lanes x Npad cols]
+  const uint32_t d2 = d1 + Npad;                         // [128 lanes x Cpad cols]
+  const uint32_t lane_field = (uint32_t)(warp_in_wg * 32) << 16;
+  float* Ahi = reinterpret_cast<float*>(smem + L::abuf(wg, 0, Npad, Cpad));
+  float* Alo = reinterpret_cast<float*>(smem + L::abuf(wg, X3 ? 1 : 0, Npad, Cpad));
+  const uint32_t bar_d1 = smem_u32(&bars[wg * 2]), bar_d2 = smem_u32(&bars[wg * 2 + 1]);
+  const uint32_t idesc1 = make_idesc_tf32(TILE, Npad), idesc2 = make_idesc_tf32(TILE, Cpad);
+  const int ksteps = (K + 7) >> 3;
+
+  // tile sequence of this warpgroup: tiles blockIdx.x + (wg + NWG*j) * gridDim.x
+  const long long stride = (long long)gridDim.x * NWG;
+  long long tile = (long long)blockIdx.x + (long long)wg * gridDim.x;
+
+  float zr[KP];
+  auto prefetch = [&](long long t) {
+    const long long m = t * TILE + wt;
+    if (t < p.num_tiles && m < p.M) {
+      const int b = (int)(m / HW);
+      const float* src = p.z + ((size_t)b * K) * HW + (m - (long long)b * HW);
+#pragma unroll
+      for (int k = 0; k < KP; ++k) zr[k] = (k < K) ? __ldg(src + (size_t)k * HW) : CENTRE;
+    } else {
+#pragma unroll
+      for (int k = 0; k < KP; ++k) zr[k] = CENTRE;
+    }
+  };
+  prefetch(tile);
+
+  uint32_t parity = 0;
+  for (; tile < p.num_tiles; tile += stride, parity ^= 1u) {
+    const long long m = tile * TILE + wt;
+    const bool valid = m < p.M;
+    const int b = valid ? (int)(m / HW) : 0;
+    const int pix = valid ? (int)(m - (long long)b * HW) : 0;
+
+    // ---- convert: registers -> tf32 operand tile; |z|^2 ----
+    float x2 = 0.f;
+#pragma unroll
+    for (int k4 = 0; k4 < KP / 4; ++k4) {
+      float hi[4], lo[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float v = zr[k4 * 4 + j] - CENTRE;
+        hi[j] = rna_tf32(v);
+        lo[j] = X3 ? rna_tf32(v - hi[j]) : 0.f;
+        const float u = X3 ? v : hi[j];
+        x2 = fmaf(u, u, x2);
+      }
+      *reinterpret_cast<float4*>(Ahi + ((size_t)k4 * TILE + wt) * 4) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+      if (X3) *reinterpret_cast<float4*>(Alo + ((size_t)k4 * TILE + wt) * 4) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+    }
+    fence_async_smem();
+    fence_before();
+    named_bar_sync(1 + wg, 128);
+    if (wt == 0) {
+      fence_after();
+      const uint32_t a_hi = smem_u32(Ahi), a_lo = smem_u32(Alo), b_hi = smem_u32(Pk_hi), b_lo = smem_u32(Pk_lo);
+      uint32_t acc = 0u;
+      for (int ks = 0; ks < ksteps; ++ks) {
+        const uint32_t ao = ks * 2 * TILE * 16, bo = ks * 2 * Npad * 16;
+        if (X3) {
+          mma_ss(d1, make_desc(a_hi + ao, TILE * 16, 128), make_desc(b_lo + bo, Npad * 16, 128), idesc1, acc);
+          mma_ss(d1, make_desc(a_lo + ao, TILE * 16, 128), make_desc(b_hi + bo, Npad * 16, 128), idesc1, 1u);
+          acc = 1u;
+        }
+        mma_ss(d1, make_desc(a_hi + ao, TILE * 16, 128), make_desc(b_hi + bo, Npad * 16, 128), idesc1, acc);
+        acc = 1u;
+      }
+      mma_commit(bar_d1);
+    }
+    // next tile's features travel while the tensor core and the epilogue work
+    prefetch(tile + stride);
+
+    int lab = -1;
+    if (want_own && valid) lab = p.target[m];
+    const bool lab_ok = lab >= 0 && lab < 32;
+
+    mbar_wait(bar_d1, parity);
+    fence_after();
+
+    // ---- epilogue 1: distances -> similarities ----
+    float lacc[X3 ? 32 : 1];
+    if (X3) {
+#pragma unroll
+      for (int c = 0; c < 32; ++c) lacc[X3 ? c : 0] = 0.f;
+    }
+    const uint32_t t1 = d1 + lane_field;
+    for (int ch = 0; ch < Npad / 16; ++ch) {
+      uint32_t r[16];
+      tmem_ld16(t1 + ch * 16, r);
+      tmem_ld_wait();
+      float dv[16];
+      uint32_t sv_bits[16];
+      float sv[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int n = ch * 16 + i;
+        const float d = fmaxf(fmaf(-2.f, __uint_as_float(r[i]), x2 + p2s[n]), 0.f);
+        dv[i] = d;
+        float s;
+        if (p.act_mode == ADLM_ACT_LOG) s = X3 ? logf((d + 1.f) / (d + p.eps)) : LN2 * (__log2f(d + 1.f) - __log2f(d + p.eps));
+        else s = -d;
+        sv[i] = s;
+        sv_bits[i] = __float_as_uint(rna_tf32(s));
+      }
+      if (!X3) {
+        tmem_st16(t1 + ch * 16, sv_bits);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const float4* wrow = reinterpret_cast<const float4*>(Wk + (size_t)(ch * 16 + i) * 32);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 w4 = wrow[q];
+            lacc[q * 4 + 0] = fmaf(sv[i], w4.x, lacc[q * 4 + 0]);
+            lacc[q * 4 + 1] = fmaf(sv[i], w4.y, lacc[q * 4 + 1]);
+            lacc[q * 4 + 2] = fmaf(sv[i], w4.z, lacc[q * 4 + 2]);
+            lacc[q * 4 + 3] = fmaf(sv[i], w4.w, lacc[q * 4 + 3]);
+          }
+        }
+      }
+      if (valid) {
+        const int nmax = min(16, N - ch * 16);
+        if (p.dist != nullptr) {
+          float* dst = p.dist + ((size_t)b * N + ch * 16) * HW + pix;
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (i < nmax) dst[(size_t)i * HW] = dv[i];
+        }
+        if (p.sim != nullptr) {
+          float* dst = p.sim + (size_t)m * N + ch * 16;
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (i < nmax) dst[i] = sv[i];
+        }
+        if (lab_ok && ((cmask[ch] >> lab) & 1u)) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (pcs[ch * 16 + i] == lab) p.own_dist[(size_t)m * JMAX + prs[ch * 16 + i]] = dv[i];
+        }
+      }
+    }
+
+    float lg[32];
+    if (!X3) {
+      // ---- MMA2: logits = S . W^T with S read from TMEM ----
+      tmem_st_wait();
+      fence_before();
+      named_bar_sync(1 + wg, 128);
+      if (wt == 0) {
+        fence_after();
+        const uint32_t wb = smem_u32(Wk);
+        for (int ks = 0; ks < Npad / 8; ++ks)
+          mma_ts(d2, d1 + ks * 8, make_desc(wb + ks * 2 * Cpad * 16, Cpad * 16, 128), idesc2, ks > 0 ? 1u : 0u);
+        mma_commit(bar_d2);
+      }
+      mbar_wait(bar_d2, parity);
+      fence_after();
+      uint32_t r[16];
+      tmem_ld16(d2 + lane_field, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 16; ++i) lg[i] = __uint_as_float(r[i]);
+      if (Cpad > 16) {
+        tmem_ld16(d2 + lane_field + 16, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) lg[16 + i] = __uint_as_float(r[i]);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) lg[16 + i] = 0.f;
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < 32; ++c) lg[c] = lacc[X3 ? c : 0];
+    }
+
+    // ---- epilogue 2: logits + argmax ----
+    if (valid) {
+      float* dst = p.logits + (size_t)m * C;
+      int best = 0;
+      float bv = lg[0];
+#pragma unroll
+      for (int c = 0; c < 32; ++c) {
+        if (c < C) {
+          dst[c] = lg[c];
+          if (c > 0 && lg[c] > bv) { bv = lg[c]; best = c; }
+        }
+      }
+      if (p.argmax != nullptr) p.argmax[m] = best;
+    }
+    // TMEM reads of this tile are complete (wait::ld); order them before the next tile's MMAs
+    fence_before();
+  }
+
+  __syncthreads();
+  if (tid < 32) tmem_dealloc(tmem_base, NWG * 256);
 }
-int tc_head_bwd(const HeadShape&, int, const float*, const float*, const float*, const float*, const float*,
-                const float*, float*, float*, float*, const StepExtras&, cudaStream_t) {
-  set_error("tc_head_bwd: tcgen05 path not built yet");
-  return ADLM_E_UNSUPPORTED;
+
+int g_num_sms = 0;
+int num_sms() {
+  if (g_num_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+  }
+  return g_num_sms;
 }
-int tc_push_scan(const float*, int, int, int, const uint32_t*, const float*, int, const int32_t*, long long,
-                 int, unsigned long long*, cudaStream_t) {
-  set_error("tc_push_scan: tcgen05 path not built yet");
-  return ADLM_E_UNSUPPORTED;
+
+template <int KP, bool X3>
+int launch_fwd(const TcFwdParams& prm, cudaStream_t st) {
+  using L = FwdSmem<KP, X3>;
+  const size_t bytes = L::total(prm.Npad, prm.Cpad) + 64;
+  if (bytes > 227 * 1024) {
+    set_error("tc_head_fwd: %zu bytes of shared memory needed (> 227 KB) for K=%d N=%d", bytes, prm.K, prm.N);
+    return ADLM_E_UNSUPPORTED;
+  }
+  ADLM_CUDA(cudaFuncSetAttribute(k_tc_fwd<KP, X3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  const int grid = prm.num_tiles < num_sms() ? prm.num_tiles : num_sms();
+  KernelTimer timer(ADLM_K_HEAD_FWD, st);
+  k_tc_fwd<KP, X3><<<grid, L::NWG * 128, bytes, st>>>(prm);
+  ADLM_LAUNCH_CHECK();
+  return ADLM_OK;
+}
+
+}  // namespace
+
+int tc_head_fwd(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
+                float* logits, float* dist, float* sim, int32_t* argmax, const StepExtras& ex,
+                cudaStream_t st) {
+  ADLM_CHECK_SUPPORTED(s.K <= 128, "tensor-core path needs K <= 128 (use precision fp32)");
+  ADLM_CHECK_SUPPORTED(s.N <= 224, "tensor-core path needs N <= 224 (use precision fp32)");
+  ADLM_CHECK_SUPPORTED(s.C <= 32, "tensor-core path needs C <= 32 (use precision fp32)");
+  TcFwdParams prm;
+  prm.z = z; prm.P = P; prm.W = W;
+  prm.logits = logits; prm.dist = dist; prm.sim = sim; prm.argmax = argmax;
+  prm.target = ex.target; prm.proto_class = ex.proto_class; prm.proto_rank = ex.proto_rank;
+  prm.own_dist = ex.own_dist;
+  prm.B = s.B; prm.K = s.K; prm.HW = s.HW; prm.N = s.N; prm.C = s.C;
+  prm.eps = s.eps; prm.act_mode = s.act_mode;
+  prm.Npad = (s.N + 15) & ~15;
+  prm.Cpad = (s.C + 15) & ~15;
+  prm.M = (long long)s.B * s.HW;
+  prm.num_tiles = (int)((prm.M + TILE - 1) / TILE);
+  const bool x3 = prec_mode == ADLM_PREC_TF32X3;
+  const int kp = s.K <= 32 ? 32 : (s.K <= 64 ? 64 : 128);
+  switch (kp) {
+    case 32: return x3 ? launch_fwd<32, true>(prm, st) : launch_fwd<32, false>(prm, st);
+    case 64: return x3 ? launch_fwd<64, true>(prm, st) : launch_fwd<64, false>(prm, st);
+    default: return x3 ? launch_fwd<128, true>(prm, st) : launch_fwd<128, false>(prm, st);
+  }
+}
+
+// Until the tcgen05 backward lands, the tensor-core modes take their gradients from the fp32 CUDA-core
+// kernel (which recomputes distances in fp32): same mathematics, tighter arithmetic than the forward.
+int tc_head_bwd(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
+                const float* dlogits, const float* ddist, const float* dsim, float* dz, float* dP,
+                float* dW, const StepExtras& ex, cudaStream_t st) {
+  (void)prec_mode;
+  return simt_head_bwd(s, z, P, W, dlogits, ddist, dsim, dz, dP, dW, ex, st);
+}
+
+int tc_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mask, const float* P, int N,
+                 const int32_t* proto_class, long long patch_base, int prec_mode,
+                 unsigned long long* packed_min, cudaStream_t st) {
+  (void)prec_mode;
+  return simt_push_scan(z, n_img, K, HW, mask, P, N, proto_class, patch_base, packed_min, st);
 }
 
 }  // namespace adlm
