@@ -18,7 +18,7 @@ MAX_PROTOS_PER_CLASS = 16
 MAX_PUSH_CLASSES = 32
 STEP_NSCALARS = 8
 PUSH_NONE = 0x7FFFFFFFFFFFFFFF
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 # name -> (restype, argtypes); kept next to include/adlm_head.h (tests check they agree)
 SIGNATURES = {
@@ -31,7 +31,8 @@ SIGNATURES = {
                               c_float, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "adlm_head_bwd": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int,
                               c_float, c_int, c_int, c_void_p, c_void_p, c_void_p,
-                              c_void_p, c_void_p, c_void_p, c_void_p]),
+                              c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "adlm_head_bwd_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "adlm_step_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int]),
     "adlm_step_fwd_bwd": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int,
                                   c_float, c_int, c_void_p, c_void_p, c_int,

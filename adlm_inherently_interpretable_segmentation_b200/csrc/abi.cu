@@ -63,17 +63,22 @@ int head_fwd_dispatch(const HeadShape& s, int prec_mode, const float* z, const f
 
 int head_bwd_dispatch(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
                       const float* dlogits, const float* ddist, const float* dsim, float* dz, float* dP,
-                      float* dW, const StepExtras& ex, cudaStream_t st) {
+                      float* dW, const StepExtras& ex, void* workspace, size_t workspace_bytes, cudaStream_t st) {
   switch (prec_mode) {
     case ADLM_PREC_FP32:
       return simt_head_bwd(s, z, P, W, dlogits, ddist, dsim, dz, dP, dW, ex, st);
     case ADLM_PREC_TF32:
     case ADLM_PREC_TF32X3:
-      return tc_head_bwd(s, prec_mode, z, P, W, dlogits, ddist, dsim, dz, dP, dW, ex, st);
+      return tc_head_bwd(s, prec_mode, z, P, W, dlogits, ddist, dsim, dz, dP, dW, ex, workspace, workspace_bytes, st);
     default:
       set_error("unknown prec_mode %d", prec_mode);
       return ADLM_E_INVALID;
   }
+}
+
+size_t head_bwd_workspace_bytes(int prec_mode, int K, int N) {
+  if (prec_mode != ADLM_PREC_TF32 || K > 64 || N > 192) return 0;
+  return tc_bwd_workspace_bytes(K, N);
 }
 
 }  // namespace adlm
@@ -127,7 +132,8 @@ int adlm_head_fwd(const float* z, int B, int K, int HW, const float* P, const fl
 
 int adlm_head_bwd(const float* z, int B, int K, int HW, const float* P, const float* W, int N, int C,
                   float eps, int act_mode, int prec_mode, const float* dlogits, const float* ddist,
-                  const float* dsim, float* dz, float* dP, float* dW, void* stream) {
+                  const float* dsim, float* dz, float* dP, float* dW, void* workspace, size_t workspace_bytes,
+                  void* stream) {
   int rc = check_shape(__func__, B, K, HW, N, C);
   if (rc != ADLM_OK) return rc;
   ADLM_CHECK_ARG(z && P && W, "z, P and W must be non-null");
@@ -135,14 +141,15 @@ int adlm_head_bwd(const float* z, int B, int K, int HW, const float* P, const fl
   ADLM_CHECK_ARG(dz || dP || dW, "at least one output gradient is required");
   ADLM_CHECK_ARG(act_mode == ADLM_ACT_LOG || act_mode == ADLM_ACT_LINEAR, "unknown act_mode");
   HeadShape s{B, K, HW, N, C, eps, act_mode};
-  return head_bwd_dispatch(s, prec_mode, z, P, W, dlogits, ddist, dsim, dz, dP, dW, StepExtras{},
-                           (cudaStream_t)stream);
+  return head_bwd_dispatch(s, prec_mode, z, P, W, dlogits, ddist, dsim, dz, dP, dW, StepExtras{}, workspace,
+                           workspace_bytes, (cudaStream_t)stream);
 }
 
+size_t adlm_head_bwd_workspace_bytes(int K, int N, int prec_mode) { return head_bwd_workspace_bytes(prec_mode, K, N); }
+
 size_t adlm_step_workspace_bytes(int B, int K, int HW, int N, int C) {
-  (void)K;
-  if (B <= 0 || HW <= 0 || N <= 0 || C <= 0) return 0;
-  return step_workspace_bytes(B, HW, N, C);
+  if (B <= 0 || K <= 0 || HW <= 0 || N <= 0 || C <= 0) return 0;
+  return step_workspace_bytes(B, K, HW, N, C);
 }
 
 int adlm_step_fwd_bwd(const float* z, int B, int K, int HW, const float* P, const float* W, int N, int C,
@@ -155,8 +162,8 @@ int adlm_step_fwd_bwd(const float* z, int B, int K, int HW, const float* P, cons
   if (rc != ADLM_OK) return rc;
   ADLM_CHECK_ARG(z && P && W && target && proto_class && scalars && workspace, "null pointer argument");
   ADLM_CHECK_ARG(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
-  if (workspace_bytes < step_workspace_bytes(B, HW, N, C)) {
-    set_error("%s: workspace too small (%zu < %zu)", __func__, workspace_bytes, step_workspace_bytes(B, HW, N, C));
+  if (workspace_bytes < step_workspace_bytes(B, K, HW, N, C)) {
+    set_error("%s: workspace too small (%zu < %zu)", __func__, workspace_bytes, step_workspace_bytes(B, K, HW, N, C));
     return ADLM_E_WORKSPACE;
   }
   HeadShape s{B, K, HW, N, C, eps, ADLM_ACT_LOG};
@@ -172,7 +179,7 @@ int adlm_step_counts(const int32_t* target, int B, int HW, const int32_t* proto_
   ADLM_CHECK_ARG(B > 0 && HW > 0 && N > 0 && C > 0, "non-positive size");
   ADLM_CHECK_SUPPORTED(C <= ADLM_MAX_C, "C > 128");
   ADLM_CHECK_ARG(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
-  if (workspace_bytes < step_workspace_bytes(B, HW, N, C)) {
+  if (workspace_bytes < step_workspace_bytes(B, 1, HW, N, C)) {
     set_error("%s: workspace too small", __func__);
     return ADLM_E_WORKSPACE;
   }

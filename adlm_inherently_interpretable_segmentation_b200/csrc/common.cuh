@@ -113,11 +113,12 @@ int head_fwd_dispatch(const HeadShape& s, int prec_mode, const float* z, const f
                       cudaStream_t st);
 int head_bwd_dispatch(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
                       const float* dlogits, const float* ddist, const float* dsim, float* dz, float* dP,
-                      float* dW, const StepExtras& ex, cudaStream_t st);
+                      float* dW, const StepExtras& ex, void* workspace, size_t workspace_bytes, cudaStream_t st);
+size_t head_bwd_workspace_bytes(int prec_mode, int K, int N);
 
 // fused step (loss.cu)
 struct StepWorkspace;
-size_t step_workspace_bytes(int B, int HW, int N, int C);
+size_t step_workspace_bytes(int B, int K, int HW, int N, int C);
 int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
                       const int32_t* target, const int32_t* proto_class, int ignore_void,
                       float w_ce, float w_kld, float w_l1, float grad_scale, const int32_t* global_counts,

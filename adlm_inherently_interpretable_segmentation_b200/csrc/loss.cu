@@ -368,10 +368,12 @@ struct StepWorkspace {  // carved out of the caller's workspace buffer
   int* counts;       // [2]
   int32_t* rank;     // [N]
   double* accum;     // [4]
+  void* bwd_scratch; // per-CTA dP/dW partials of the tensor-core backward
+  size_t bwd_scratch_bytes;
   size_t bytes;
 };
 
-StepWorkspace carve_step_workspace(void* base, int B, int HW, int N, int C) {
+StepWorkspace carve_step_workspace(void* base, int B, int K, int HW, int N, int C) {
   StepWorkspace w;
   const size_t M = (size_t)B * HW;
   size_t off = 0;
@@ -386,12 +388,14 @@ StepWorkspace carve_step_workspace(void* base, int B, int HW, int N, int C) {
   w.counts = (int*)take(2 * sizeof(int));
   w.rank = (int32_t*)take((size_t)N * sizeof(int32_t));
   w.accum = (double*)take(4 * sizeof(double));
+  w.bwd_scratch_bytes = head_bwd_workspace_bytes(ADLM_PREC_TF32, K, N);
+  w.bwd_scratch = take(w.bwd_scratch_bytes);
   w.bytes = off;
   return w;
 }
 
-size_t step_workspace_bytes(int B, int HW, int N, int C) {
-  return carve_step_workspace(nullptr, B, HW, N, C).bytes;
+size_t step_workspace_bytes(int B, int K, int HW, int N, int C) {
+  return carve_step_workspace(nullptr, B, K, HW, N, C).bytes;
 }
 
 int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
@@ -401,7 +405,7 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
                       double* scalars, void* workspace, cudaStream_t st) {
   const int B = s.B, HW = s.HW, N = s.N, C = s.C;
   const long long M = (long long)B * HW;
-  StepWorkspace ws = carve_step_workspace(workspace, B, HW, N, C);
+  StepWorkspace ws = carve_step_workspace(workspace, B, s.K, HW, N, C);
   const bool want_grad = (dz != nullptr) || (dP != nullptr) || (dW != nullptr);
   float* logits = logits_out ? logits_out : ws.logits;
 
@@ -443,7 +447,8 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
     StepExtras exb = ex;
     exb.own_dist = nullptr;
     exb.own_grad = ws.own_grad;
-    if ((rc = head_bwd_dispatch(s, prec_mode, z, P, W, ws.dlogits, nullptr, nullptr, dz, dP, dW, exb, st)) != ADLM_OK)
+    if ((rc = head_bwd_dispatch(s, prec_mode, z, P, W, ws.dlogits, nullptr, nullptr, dz, dP, dW, exb, ws.bwd_scratch,
+                                ws.bwd_scratch_bytes, st)) != ADLM_OK)
       return rc;
   }
   k_finalize<<<1, 256, 0, st>>>(W, proto_class, C, N, w_ce, w_kld, w_l1, grad_scale, counts, ws.accum,
@@ -454,7 +459,7 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
 
 int step_counts_impl(const int32_t* target, int B, int HW, const int32_t* proto_class, int N, int C,
                      int ignore_void, int32_t* counts_out, void* workspace, cudaStream_t st) {
-  StepWorkspace ws = carve_step_workspace(workspace, B, HW, N, C);
+  StepWorkspace ws = carve_step_workspace(workspace, B, 1, HW, N, C);
   ADLM_CUDA(cudaMemsetAsync(ws.hist, 0, sizeof(int) * (size_t)B * (C + 1), st));
   dim3 grid(min(cdiv(HW, 256), 64), B);
   k_label_hist<<<grid, 256, sizeof(int) * (C + 1), st>>>(target, HW, C, ws.hist);

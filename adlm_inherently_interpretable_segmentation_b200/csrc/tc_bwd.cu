@@ -1,0 +1,622 @@
+// ADLM_PREC_TF32 backward of the prototype head on the tensor cores: two kernels, both recompute the
+// distances on chip (nothing of size M x N is read from or written to HBM).
+//
+//   G[m][n] = ((dlogits W)[m][n] + dsim[m][n]) * ds/dd(d[m][n]) + ddist[m][n] + kld_grad[m][n], zero where relu clipped
+//   dZ = 2 (rowsum(G) zc - G Pc)      k_tc_bwd_dz   lanes = pixels;  G goes back into TMEM and is the A operand
+//                                                   of the G.P contraction (.ts MMA)
+//   dP = 2 (colsum(G) Pc - G^T Zc)    k_tc_bwd_dp   lanes = prototypes (the transposed problem D^T = Pc Zc^T), so that
+//   dW = dlogits^T S                                G and S are again TMEM A operands of the two pixel contractions;
+//                                                   accumulators stay in TMEM for all tiles of the CTA, per-CTA
+//                                                   partials are summed by k_reduce_partials
+// (zc = z - 1/2, Pc = P - 1/2: both formulas are invariant under the common shift.)
+// A contraction over the TMEM lane index is impossible (lanes are the M index of an A operand), and MN-major
+// tf32 shared-memory operands do not work on this part, hence one kernel per orientation.
+#include "tc_head.cuh"
+#include "tc_common.cuh"
+
+namespace adlm {
+
+namespace {
+
+using namespace tc;
+
+constexpr int TILE = 128;
+constexpr int JMAX = ADLM_MAX_PROTOS_PER_CLASS;
+constexpr float LN2 = 0.6931471805599453f;
+constexpr float CENTRE = 0.5f;
+
+struct TcBwdParams {
+  const float* z;
+  const float* P;
+  const float* W;
+  const float* dlogits;   // [M, C] | null
+  const float* ddist;     // [B, N, HW] | null
+  const float* dsim;      // [M, N] | null
+  const int32_t* target;  // [M] | null (KLD term)
+  const int32_t* proto_class;
+  const int32_t* proto_rank;
+  const float* own_grad;  // [M, JMAX] | null
+  float* dz;              // [B, K, HW]
+  float* partials;        // [grid][Npad2*KP + Npad2*32]
+  int B, K, HW, N, C;
+  float eps;
+  int act_mode;
+  int Npad, C8;
+  long long M;
+  int num_tiles;
+};
+
+// ds/dd of model.py:233 / :235
+__device__ __forceinline__ float dsdd_of(float d, float eps, int act_mode) {
+  if (act_mode == ADLM_ACT_LOG) return (eps - 1.f) * rcp_approx((d + 1.f) * (d + eps));
+  return -1.f;
+}
+
+// ------------------------------------------------------------------------------------------------ dZ
+// smem: Pk [KP/4][Npad][4] | Pt [Npad/4][KP][4] | Wt [C8/4][Npad][4] | per WG: Zk [KP/4][128][4], dLk [C8/4][128][4]
+template <int KP>
+struct DzSmem {
+  static __host__ __device__ size_t pk() { return 0; }
+  static __host__ __device__ size_t pt(int Npad) { return (size_t)KP * Npad * 4; }
+  static __host__ __device__ size_t wt(int Npad) { return 2 * (size_t)KP * Npad * 4; }
+  static __host__ __device__ size_t zk(int wg, int Npad, int C8) {
+    return wt(Npad) + (size_t)C8 * Npad * 4 + (size_t)wg * ((size_t)KP * TILE * 4 + (size_t)C8 * TILE * 4);
+  }
+  static __host__ __device__ size_t dlk(int wg, int Npad, int C8) { return zk(wg, Npad, C8) + (size_t)KP * TILE * 4; }
+  static __host__ __device__ size_t misc(int Npad, int C8) { return zk(2, Npad, C8); }
+  static __host__ __device__ size_t total(int Npad, int C8) { return misc(Npad, C8) + (size_t)Npad * 12 + 256; }
+};
+
+template <int KP>
+__global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
+  using L = DzSmem<KP>;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const int Npad = p.Npad, C8 = p.C8, K = p.K, N = p.N, C = p.C, HW = p.HW, NH = Npad / 2;
+  float* Pk = reinterpret_cast<float*>(smem + L::pk());
+  float* Pt = reinterpret_cast<float*>(smem + L::pt(Npad));
+  float* Wt = reinterpret_cast<float*>(smem + L::wt(Npad));
+  uint8_t* misc = smem + L::misc(Npad, C8);
+  float* p2s = reinterpret_cast<float*>(misc);
+  int* pcs = reinterpret_cast<int*>(misc + (size_t)Npad * 4);
+  int* prs = reinterpret_cast<int*>(misc + (size_t)Npad * 8);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(misc + (size_t)Npad * 12);
+  uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 4);
+
+  const int tid = threadIdx.x, wg = tid >> 7, wt = tid & 127, warp_in_wg = wt >> 5;
+  const bool kld = p.own_grad != nullptr;
+
+  if (tid < 32) tmem_alloc(smem_u32(tmem_base_s), 512);
+  if (tid == 32) {
+    for (int i = 0; i < 4; ++i) mbar_init(smem_u32(&bars[i]), 1);
+    mbar_init_fence();
+  }
+  for (int idx = tid; idx < (KP / 4) * Npad; idx += 256) {
+    const int n = idx % Npad, k4 = idx / Npad;
+    float v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int k = k4 * 4 + j;
+      v[j] = rna_tf32((n < N && k < K) ? __ldg(p.P + (size_t)n * K + k) - CENTRE : 0.f);
+      Pt[(size_t)(n >> 2) * KP * 4 + k * 4 + (n & 3)] = v[j];      // rows k, K index n
+    }
+    *reinterpret_cast<float4*>(Pk + (size_t)idx * 4) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+  for (int idx = tid; idx < C8 * Npad; idx += 256) {
+    const int c = idx / Npad, n = idx - c * Npad;
+    const float v = (c < C && n < N && p.dlogits != nullptr) ? __ldg(p.W + (size_t)c * N + n) : 0.f;
+    Wt[(size_t)(c >> 2) * Npad * 4 + n * 4 + (c & 3)] = rna_tf32(v);   // rows n, K index c
+  }
+  __syncthreads();
+  for (int n = tid; n < Npad; n += 256) {
+    float a = 0.f;
+    for (int k4 = 0; k4 < KP / 4; ++k4) {
+      const float4 v = *reinterpret_cast<const float4*>(Pk + ((size_t)k4 * Npad + n) * 4);
+      a = fmaf(v.x, v.x, a); a = fmaf(v.y, v.y, a); a = fmaf(v.z, v.z, a); a = fmaf(v.w, v.w, a);
+    }
+    p2s[n] = a;
+    pcs[n] = (kld && n < N) ? p.proto_class[n] : -1;
+    prs[n] = (kld && n < N) ? p.proto_rank[n] : 0;
+  }
+  fence_async_smem();
+  fence_before();
+  __syncthreads();
+  fence_after();
+
+  const uint32_t tmem_base = *tmem_base_s;
+  const uint32_t tD = tmem_base + wg * 256;      // D1 half   [128 x NH]
+  const uint32_t tG = tD + NH;                   // Gl half   [128 x NH]
+  const uint32_t tZ = tD + 2 * NH;               // dZ        [128 x KP]
+  const uint32_t lane_field = (uint32_t)(warp_in_wg * 32) << 16;
+  float* Zk = reinterpret_cast<float*>(smem + L::zk(wg, Npad, C8));
+  float* dLk = reinterpret_cast<float*>(smem + L::dlk(wg, Npad, C8));
+  const uint32_t bar_a = smem_u32(&bars[wg * 2]), bar_z = smem_u32(&bars[wg * 2 + 1]);
+  const uint32_t idesc_h = make_idesc_tf32(TILE, NH), idesc_z = make_idesc_tf32(TILE, KP);
+  const int ksteps = (K + 7) >> 3;
+
+  const long long stride = (long long)gridDim.x * 2;
+  long long tile = (long long)blockIdx.x + (long long)wg * gridDim.x;
+  uint32_t ph_a = 0, ph_z = 0;
+
+  for (; tile < p.num_tiles; tile += stride) {
+    const long long m = tile * TILE + wt;
+    const bool valid = m < p.M;
+    const int b = valid ? (int)(m / HW) : 0;
+    const int pix = valid ? (int)(m - (long long)b * HW) : 0;
+    const float* zsrc = p.z + ((size_t)b * K) * HW + pix;
+
+    // ---- operands of this tile: Zk (centred, rounded), dLk ----
+    float x2 = 0.f;
+#pragma unroll
+    for (int k4 = 0; k4 < KP / 4; ++k4) {
+      float v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int k = k4 * 4 + j;
+        v[j] = rna_tf32((valid && k < K) ? __ldg(zsrc + (size_t)k * HW) - CENTRE : 0.f);
+        x2 = fmaf(v[j], v[j], x2);
+      }
+      *reinterpret_cast<float4*>(Zk + ((size_t)k4 * TILE + wt) * 4) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+    for (int c4 = 0; c4 < C8 / 4; ++c4) {
+      float v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int c = c4 * 4 + j;
+        v[j] = (valid && c < C && p.dlogits != nullptr) ? rna_tf32(__ldg(p.dlogits + (size_t)m * C + c)) : 0.f;
+      }
+      *reinterpret_cast<float4*>(dLk + ((size_t)c4 * TILE + wt) * 4) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+    int lab = -1;
+    if (kld && valid) lab = p.target[m];
+    fence_async_smem();
+    fence_before();
+    named_bar_sync(1 + wg, 128);
+
+    float rs = 0.f;
+    for (int h = 0; h < 2; ++h) {
+      if (wt == 0) {
+        fence_after();
+        const uint32_t a0 = smem_u32(Zk), b0 = smem_u32(Pk) + h * NH * 16;
+        for (int ks = 0; ks < ksteps; ++ks)
+          mma_ss(tD, make_desc(a0 + ks * 2 * TILE * 16, TILE * 16, 128), make_desc(b0 + ks * 2 * Npad * 16, Npad * 16, 128),
+                 idesc_h, ks > 0 ? 1u : 0u);
+        const uint32_t l0 = smem_u32(dLk), w0 = smem_u32(Wt) + h * NH * 16;
+        for (int ks = 0; ks < C8 / 8; ++ks)
+          mma_ss(tG, make_desc(l0 + ks * 2 * TILE * 16, TILE * 16, 128), make_desc(w0 + ks * 2 * Npad * 16, Npad * 16, 128),
+                 idesc_h, ks > 0 ? 1u : 0u);
+        mma_commit(bar_a);
+      }
+      mbar_wait(bar_a, ph_a);
+      ph_a ^= 1u;
+      fence_after();
+      for (int ch = 0; ch < NH / 16; ++ch) {
+        uint32_t ra[16], rg[16], out[16];
+        tmem_ld16(tD + lane_field + ch * 16, ra);
+        tmem_ld16(tG + lane_field + ch * 16, rg);
+        tmem_ld_wait();
+        const int n0 = h * NH + ch * 16;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int n = n0 + i;
+          const float pre = fmaf(-2.f, __uint_as_float(ra[i]), x2 + p2s[n]);
+          const float d = fmaxf(pre, 0.f);
+          float g = __uint_as_float(rg[i]);
+          if (p.dsim != nullptr && valid && n < N) g += __ldg(p.dsim + (size_t)m * N + n);
+          g *= dsdd_of(d, p.eps, p.act_mode);
+          if (p.ddist != nullptr && valid && n < N) g += __ldg(p.ddist + ((size_t)b * N + n) * HW + pix);
+          if (lab >= 0 && pcs[n] == lab) g += __ldg(p.own_grad + (size_t)m * JMAX + prs[n]);
+          g = (pre > 0.f && valid && n < N) ? g : 0.f;
+          rs += g;
+          out[i] = __float_as_uint(rna_tf32(g));
+        }
+        tmem_st16(tD + lane_field + ch * 16, out);
+      }
+      tmem_st_wait();
+      fence_before();
+      named_bar_sync(1 + wg, 128);
+      if (wt == 0) {
+        fence_after();
+        const uint32_t pt0 = smem_u32(Pt) + (h * NH / 4) * KP * 16;
+        for (int ks = 0; ks < NH / 8; ++ks)
+          mma_ts(tZ, tD + ks * 8, make_desc(pt0 + ks * 2 * KP * 16, KP * 16, 128), idesc_z, (h > 0 || ks > 0) ? 1u : 0u);
+        if (h == 1) mma_commit(bar_z);
+      }
+    }
+    mbar_wait(bar_z, ph_z);
+    ph_z ^= 1u;
+    fence_after();
+    // ---- dz = 2 (rowsum(G) zc - G Pc) ----
+    float* dst = p.dz + ((size_t)b * K) * HW + pix;
+#pragma unroll
+    for (int ch = 0; ch < KP / 16; ++ch) {
+      uint32_t r[16];
+      tmem_ld16(tZ + lane_field + ch * 16, r);
+      tmem_ld_wait();
+      if (valid) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int k = ch * 16 + i;
+          if (k < K) dst[(size_t)k * HW] = 2.f * (rs * (__ldg(zsrc + (size_t)k * HW) - CENTRE) - __uint_as_float(r[i]));
+        }
+      }
+    }
+    fence_before();
+  }
+  __syncthreads();
+  if (tid < 32) tmem_dealloc(tmem_base, 512);
+}
+
+// ------------------------------------------------------------------------------------------- dP, dW
+// lanes = prototypes.  Roles: warps 0-7 epilogue (TMEM lane n = 32*(warp%4)+lane, pixel columns split in two
+// halves by warp/4), warps 8-11 build the pixel-side operands (thread = pixel), warp 12 issues the MMAs.
+// smem: ZtB (128B-swizzled [KP][128 px]) | dLtB (swizzled [32][128 px]) | PkA [KP/4][Npad2][4] |
+//       WtA [C8/4][Npad2][4] | ZkB [KP/4][128][4] | dLkB [C8/4][128][4] | x2, label, image, pixel per column
+constexpr int DP_THREADS = 416;
+
+template <int KP>
+struct DpSmem {
+  static __host__ __device__ size_t zt() { return 0; }
+  static __host__ __device__ size_t dlt() { return (size_t)KP * TILE * 4; }
+  static __host__ __device__ size_t pk() { return dlt() + 32 * TILE * 4; }
+  static __host__ __device__ size_t wt(int Npad2) { return pk() + (size_t)KP * Npad2 * 4; }
+  static __host__ __device__ size_t zk(int Npad2, int C8) { return wt(Npad2) + (size_t)C8 * Npad2 * 4; }
+  static __host__ __device__ size_t dlk(int Npad2, int C8) { return zk(Npad2, C8) + (size_t)KP * TILE * 4; }
+  static __host__ __device__ size_t misc(int Npad2, int C8) { return dlk(Npad2, C8) + (size_t)C8 * TILE * 4; }
+  // x2 [128] f32, lab [128] i32, img [128] i32, pix [128] i32, cs [2][2][128] f32, barriers
+  static __host__ __device__ size_t total(int Npad2, int C8) { return misc(Npad2, C8) + 128 * 16 + 512 * 4 + 128; }
+};
+
+template <int KP>
+__global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p, int NB) {
+  using L = DpSmem<KP>;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const int Npad2 = NB * 128, C8 = p.C8, K = p.K, N = p.N, C = p.C, HW = p.HW;
+  float* ZtB = reinterpret_cast<float*>(smem + L::zt());
+  float* dLtB = reinterpret_cast<float*>(smem + L::dlt());
+  float* PkA = reinterpret_cast<float*>(smem + L::pk());
+  float* WtA = reinterpret_cast<float*>(smem + L::wt(Npad2));
+  float* ZkB = reinterpret_cast<float*>(smem + L::zk(Npad2, C8));
+  float* dLkB = reinterpret_cast<float*>(smem + L::dlk(Npad2, C8));
+  uint8_t* misc = smem + L::misc(Npad2, C8);
+  float* x2s = reinterpret_cast<float*>(misc);
+  int* labs = reinterpret_cast<int*>(misc + 512);
+  int* imgs = reinterpret_cast<int*>(misc + 1024);
+  int* pixs = reinterpret_cast<int*>(misc + 1536);
+  float* css = reinterpret_cast<float*>(misc + 2048);           // [half][blk][128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(misc + 2048 + 2048);
+  uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 4);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const bool kld = p.own_grad != nullptr;
+  const bool has_dl = p.dlogits != nullptr;
+
+  if (warp == 12) tmem_alloc(smem_u32(tmem_base_s), 512);
+  if (tid == 0) {
+    mbar_init(smem_u32(&bars[0]), 128);   // full: pixel operands written
+    mbar_init(smem_u32(&bars[1]), 1);     // acc: D^T and Gl^T of a block ready
+    mbar_init(smem_u32(&bars[2]), 256);   // gs: G and S of a block written back to TMEM
+    mbar_init(smem_u32(&bars[3]), 1);     // free: every MMA of the tile done
+    mbar_init_fence();
+  }
+  for (int idx = tid; idx < (KP / 4) * Npad2; idx += DP_THREADS) {
+    const int n = idx % Npad2, k4 = idx / Npad2;
+    float v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int k = k4 * 4 + j;
+      v[j] = rna_tf32((n < N && k < K) ? __ldg(p.P + (size_t)n * K + k) - CENTRE : 0.f);
+    }
+    *reinterpret_cast<float4*>(PkA + (size_t)idx * 4) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+  for (int idx = tid; idx < C8 * Npad2; idx += DP_THREADS) {
+    const int c = idx / Npad2, n = idx - c * Npad2;
+    const float v = (c < C && n < N && has_dl) ? __ldg(p.W + (size_t)c * N + n) : 0.f;
+    WtA[(size_t)(c >> 2) * Npad2 * 4 + n * 4 + (c & 3)] = rna_tf32(v);
+  }
+  for (int idx = tid; idx < 32 * TILE; idx += DP_THREADS) dLtB[idx] = 0.f;
+  fence_async_smem();
+  fence_before();
+  __syncthreads();
+  fence_after();
+
+  const uint32_t tmem_base = *tmem_base_s;
+  const uint32_t tD1 = tmem_base, tGl = tmem_base + 128, tP0 = tmem_base + 256, tW0 = tmem_base + 256 + NB * KP;
+  const uint32_t bar_full = smem_u32(&bars[0]), bar_acc = smem_u32(&bars[1]), bar_gs = smem_u32(&bars[2]),
+                 bar_free = smem_u32(&bars[3]);
+  const int iters = (p.num_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1;
+
+  if (warp >= 8 && warp < 12) {
+    // ================= pixel-side operand builder: thread = pixel =================
+    const int cw = tid - 256;
+    float zr[KP];
+    float dlr[32];
+    auto prefetch = [&](int it) {
+      const long long m = ((long long)blockIdx.x + (long long)it * gridDim.x) * TILE + cw;
+      const bool ok = it < iters && m < p.M;
+      const int b = ok ? (int)(m / HW) : 0;
+      const float* src = p.z + ((size_t)b * K) * HW + (ok ? (m - (long long)b * HW) : 0);
+#pragma unroll
+      for (int k = 0; k < KP; ++k) zr[k] = (ok && k < K) ? __ldg(src + (size_t)k * HW) : CENTRE;
+#pragma unroll
+      for (int c = 0; c < 32; ++c) dlr[c] = (ok && has_dl && c < C) ? __ldg(p.dlogits + (size_t)m * C + c) : 0.f;
+    };
+    prefetch(0);
+    for (int it = 0; it < iters; ++it) {
+      const long long m = ((long long)blockIdx.x + (long long)it * gridDim.x) * TILE + cw;
+      const bool valid = m < p.M;
+      if (it > 0) mbar_wait(bar_free, (uint32_t)(it - 1) & 1u);
+      float x2 = 0.f;
+#pragma unroll
+      for (int k4 = 0; k4 < KP / 4; ++k4) {
+        float v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          v[j] = rna_tf32(zr[k4 * 4 + j] - CENTRE);
+          x2 = fmaf(v[j], v[j], x2);
+          ZtB[off_sw128(k4 * 4 + j, cw, KP)] = v[j];
+        }
+        *reinterpret_cast<float4*>(ZkB + ((size_t)k4 * TILE + cw) * 4) = make_float4(v[0], v[1], v[2], v[3]);
+      }
+#pragma unroll
+      for (int c4 = 0; c4 < 8; ++c4) {
+        if (c4 * 4 < C8) {
+          float v[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            v[j] = rna_tf32(dlr[c4 * 4 + j]);
+            if (c4 * 4 + j < C) dLtB[off_sw128(c4 * 4 + j, cw, 32)] = v[j];
+          }
+          *reinterpret_cast<float4*>(dLkB + ((size_t)c4 * TILE + cw) * 4) = make_float4(v[0], v[1], v[2], v[3]);
+        }
+      }
+      x2s[cw] = x2;
+      const int b = valid ? (int)(m / HW) : 0;
+      imgs[cw] = b;
+      pixs[cw] = valid ? (int)(m - (long long)b * HW) : 0;
+      labs[cw] = valid ? (kld ? p.target[m] : -1) : -2;
+      fence_async_smem();
+      mbar_arrive(bar_full);
+      prefetch(it + 1);
+    }
+  } else if (warp == 12) {
+    // ================= MMA issuer =================
+    if (lane == 0) {
+      const uint32_t idesc_t = make_idesc_tf32(128, 128), idesc_p = make_idesc_tf32(128, KP), idesc_w = make_idesc_tf32(128, 32);
+      const int ksteps = (K + 7) >> 3;
+      uint32_t g = 0;
+      for (int it = 0; it < iters; ++it) {
+        mbar_wait(bar_full, (uint32_t)it & 1u);
+        fence_after();
+        for (int blk = 0; blk < NB; ++blk) {
+          const uint32_t a0 = smem_u32(PkA) + blk * 128 * 16, b0 = smem_u32(ZkB);
+          for (int ks = 0; ks < ksteps; ++ks)
+            mma_ss(tD1, make_desc(a0 + ks * 2 * Npad2 * 16, Npad2 * 16, 128), make_desc(b0 + ks * 2 * TILE * 16, TILE * 16, 128),
+                   idesc_t, ks > 0 ? 1u : 0u);
+          const uint32_t w0 = smem_u32(WtA) + blk * 128 * 16, l0 = smem_u32(dLkB);
+          for (int ks = 0; ks < C8 / 8; ++ks)
+            mma_ss(tGl, make_desc(w0 + ks * 2 * Npad2 * 16, Npad2 * 16, 128), make_desc(l0 + ks * 2 * TILE * 16, TILE * 16, 128),
+                   idesc_t, ks > 0 ? 1u : 0u);
+          mma_commit(bar_acc);
+          mbar_wait(bar_gs, g & 1u);
+          ++g;
+          fence_after();
+          const uint32_t zt0 = smem_u32(ZtB), lt0 = smem_u32(dLtB);
+          for (int ks = 0; ks < TILE / 8; ++ks) {
+            const uint32_t acc = (it > 0 || ks > 0) ? 1u : 0u;
+            mma_ts(tP0 + blk * KP, tD1 + ks * 8, make_desc_sw128(zt0 + (ks >> 2) * KP * 128 + (ks & 3) * 32), idesc_p, acc);
+            mma_ts(tW0 + blk * 32, tGl + ks * 8, make_desc_sw128(lt0 + (ks >> 2) * 32 * 128 + (ks & 3) * 32), idesc_w, acc);
+          }
+        }
+        mma_commit(bar_free);
+      }
+    }
+  } else {
+    // ================= epilogue: thread = (prototype lane, pixel-column half) =================
+    const int half = warp >> 2, lane_n = ((warp & 3) << 5) + lane;
+    const uint32_t lane_field = (uint32_t)((warp & 3) * 32) << 16;
+    float p2[2] = {0.f, 0.f}, cs[2] = {0.f, 0.f};
+    int pcl[2] = {-5, -5}, prk[2] = {0, 0};
+    for (int blk = 0; blk < NB; ++blk) {
+      const int n = blk * 128 + lane_n;
+      float a = 0.f;
+      for (int k4 = 0; k4 < KP / 4; ++k4) {
+        const float4 v = *reinterpret_cast<const float4*>(PkA + ((size_t)k4 * Npad2 + n) * 4);
+        a = fmaf(v.x, v.x, a); a = fmaf(v.y, v.y, a); a = fmaf(v.z, v.z, a); a = fmaf(v.w, v.w, a);
+      }
+      p2[blk] = a;
+      if (kld && n < N) { pcl[blk] = p.proto_class[n]; prk[blk] = p.proto_rank[n]; }
+    }
+    uint32_t g = 0;
+    for (int it = 0; it < iters; ++it) {
+      const long long m0 = ((long long)blockIdx.x + (long long)it * gridDim.x) * TILE;
+      mbar_wait(bar_full, (uint32_t)it & 1u);
+      for (int blk = 0; blk < NB; ++blk) {
+        const int n = blk * 128 + lane_n;
+        mbar_wait(bar_acc, g & 1u);
+        ++g;
+        fence_after();
+        if (blk * 128 + (warp & 3) * 32 < N) {       // warps whose 32 prototypes are all padding skip the math
+          for (int ch = 0; ch < 4; ++ch) {
+            const int c0 = half * 64 + ch * 16;
+            uint32_t ra[16], rg[16], og[16], os[16];
+            tmem_ld16(tD1 + lane_field + c0, ra);
+            tmem_ld16(tGl + lane_field + c0, rg);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const int px = c0 + i;
+              const int lab = labs[px];
+              const float pre = fmaf(-2.f, __uint_as_float(ra[i]), x2s[px] + p2[blk]);
+              const float d = fmaxf(pre, 0.f);
+              float s, dsdd;
+              if (p.act_mode == ADLM_ACT_LOG) {
+                const float u = d + 1.f, v = d + p.eps;
+                s = LN2 * (lg2_approx(u) - lg2_approx(v));
+                dsdd = (p.eps - 1.f) * rcp_approx(u * v);
+              } else {
+                s = -d;
+                dsdd = -1.f;
+              }
+              float gv = __uint_as_float(rg[i]);
+              const bool okpx = lab != -2 && n < N;
+              if (p.dsim != nullptr && okpx) gv += __ldg(p.dsim + (size_t)(m0 + px) * N + n);
+              gv *= dsdd;
+              if (p.ddist != nullptr && okpx) gv += __ldg(p.ddist + ((size_t)imgs[px] * N + n) * HW + pixs[px]);
+              if (lab == pcl[blk]) gv += __ldg(p.own_grad + (size_t)(m0 + px) * JMAX + prk[blk]);
+              gv = (pre > 0.f && okpx) ? gv : 0.f;
+              s = okpx ? s : 0.f;
+              cs[blk] += gv;
+              og[i] = __float_as_uint(rna_tf32(gv));
+              os[i] = __float_as_uint(rna_tf32(s));
+            }
+            tmem_st16(tD1 + lane_field + c0, og);
+            tmem_st16(tGl + lane_field + c0, os);
+          }
+          tmem_st_wait();
+        }
+        fence_before();
+        mbar_arrive(bar_gs);
+      }
+    }
+    // ---- flush this CTA's partial sums ----
+    mbar_wait(bar_free, (uint32_t)(iters - 1) & 1u);
+    fence_after();
+    for (int blk = 0; blk < NB; ++blk) css[(half * 2 + blk) * 128 + lane_n] = cs[blk];
+    named_bar_sync(1, 256);
+    float* part = p.partials + (size_t)blockIdx.x * ((size_t)Npad2 * KP + (size_t)Npad2 * 32);
+    for (int blk = 0; blk < NB; ++blk) {
+      const int n = blk * 128 + lane_n;
+      const float cst = css[blk * 128 + lane_n] + css[(2 + blk) * 128 + lane_n];
+      if (blk * 128 + (warp & 3) * 32 < N) {
+#pragma unroll
+        for (int ch = 0; ch < KP / 32; ++ch) {
+          const int k0 = half * (KP / 2) + ch * 16;
+          uint32_t r[16];
+          tmem_ld16(tP0 + blk * KP + lane_field + k0, r);
+          tmem_ld_wait();
+          if (n < N) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const int k = k0 + i;
+              const float pc = PkA[(size_t)(k >> 2) * Npad2 * 4 + n * 4 + (k & 3)];
+              part[(size_t)n * KP + k] = 2.f * (cst * pc - __uint_as_float(r[i]));
+            }
+          }
+        }
+        uint32_t r[16];
+        tmem_ld16(tW0 + blk * 32 + lane_field + half * 16, r);
+        tmem_ld_wait();
+        if (n < N) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) part[(size_t)Npad2 * KP + (size_t)n * 32 + half * 16 + i] = __uint_as_float(r[i]);
+        }
+      }
+    }
+    fence_before();
+  }
+  __syncthreads();
+  if (warp == 12) tmem_dealloc(tmem_base, 512);
+}
+
+// dP[n][k] = sum over CTAs; dW[c][n] = sum over CTAs (stored [n][32] per CTA)
+__global__ void k_reduce_partials(const float* __restrict__ partials, int n_parts, int Npad2, int KP, int N, int K,
+                                  int C, float* __restrict__ dP, float* __restrict__ dW) {
+  const size_t per = (size_t)Npad2 * KP + (size_t)Npad2 * 32;
+  const int total = N * K + C * N;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    size_t off;
+    float* dst;
+    if (idx < N * K) {
+      const int n = idx / K, k = idx - n * K;
+      off = (size_t)n * KP + k;
+      dst = dP ? dP + idx : nullptr;
+    } else {
+      const int j = idx - N * K, c = j / N, n = j - c * N;
+      off = (size_t)Npad2 * KP + (size_t)n * 32 + c;
+      dst = dW ? dW + j : nullptr;
+    }
+    if (dst == nullptr) continue;
+    float a = 0.f;
+    for (int q = 0; q < n_parts; ++q) a += partials[(size_t)q * per + off];
+    *dst = a;
+  }
+}
+
+int g_sms = 0;
+int sm_count() {
+  if (g_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_sms <= 0) g_sms = 148;
+  }
+  return g_sms;
+}
+
+bool tc_bwd_supported(const HeadShape& s, int prec_mode) {
+  return prec_mode == ADLM_PREC_TF32 && s.K <= 64 && s.N <= 192 && s.C <= 32;
+}
+
+template <int KP>
+int launch_bwd(TcBwdParams prm, float* dP, float* dW, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  const int grid = prm.num_tiles < sm_count() ? prm.num_tiles : sm_count();
+  KernelTimer timer(ADLM_K_HEAD_BWD, st);
+  if (prm.dz != nullptr) {
+    using L = DzSmem<KP>;
+    const size_t bytes = L::total(prm.Npad, prm.C8);
+    ADLM_CUDA(cudaFuncSetAttribute(k_tc_bwd_dz<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    k_tc_bwd_dz<KP><<<grid, 256, bytes, st>>>(prm);
+    ADLM_LAUNCH_CHECK();
+  }
+  if (dP != nullptr || dW != nullptr) {
+    using L = DpSmem<KP>;
+    const int NB = (prm.N + 127) / 128, Npad2 = NB * 128;
+    const size_t per = ((size_t)Npad2 * KP + (size_t)Npad2 * 32) * sizeof(float);
+    if (workspace == nullptr || workspace_bytes < per * grid) {
+      set_error("tc_head_bwd: workspace too small (%zu < %zu)", workspace_bytes, per * grid);
+      return ADLM_E_WORKSPACE;
+    }
+    prm.partials = static_cast<float*>(workspace);
+    const size_t bytes = L::total(Npad2, prm.C8);
+    ADLM_CUDA(cudaFuncSetAttribute(k_tc_bwd_dp<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    k_tc_bwd_dp<KP><<<grid, DP_THREADS, bytes, st>>>(prm, NB);
+    ADLM_LAUNCH_CHECK();
+    const int total = prm.N * prm.K + prm.C * prm.N;
+    k_reduce_partials<<<(total + 255) / 256, 256, 0, st>>>(prm.partials, grid, Npad2, KP, prm.N, prm.K, prm.C, dP, dW);
+    ADLM_LAUNCH_CHECK();
+  }
+  return ADLM_OK;
+}
+
+}  // namespace
+
+size_t tc_bwd_workspace_bytes(int K, int N) {
+  const int NB = (N + 127) / 128, Npad2 = NB * 128, KP = K <= 32 ? 32 : 64;
+  return ((size_t)Npad2 * KP + (size_t)Npad2 * 32) * sizeof(float) * (size_t)sm_count();
+}
+
+int tc_head_bwd(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
+                const float* dlogits, const float* ddist, const float* dsim, float* dz, float* dP,
+                float* dW, const StepExtras& ex, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  if (!tc_bwd_supported(s, prec_mode)) {
+    // 3xTF32 (fp32-class) and shapes beyond the tensor-core backward's operand budget take the fp32
+    // CUDA-core backward: same mathematics, tighter arithmetic
+    return simt_head_bwd(s, z, P, W, dlogits, ddist, dsim, dz, dP, dW, ex, st);
+  }
+  TcBwdParams prm;
+  prm.z = z; prm.P = P; prm.W = W;
+  prm.dlogits = dlogits; prm.ddist = ddist; prm.dsim = dsim;
+  prm.target = ex.own_grad ? ex.target : nullptr;
+  prm.proto_class = ex.proto_class; prm.proto_rank = ex.proto_rank; prm.own_grad = ex.own_grad;
+  prm.dz = dz; prm.partials = nullptr;
+  prm.B = s.B; prm.K = s.K; prm.HW = s.HW; prm.N = s.N; prm.C = s.C;
+  prm.eps = s.eps; prm.act_mode = s.act_mode;
+  prm.Npad = (s.N + 31) & ~31;
+  prm.C8 = (s.C + 7) & ~7;
+  prm.M = (long long)s.B * s.HW;
+  prm.num_tiles = (int)((prm.M + TILE - 1) / TILE);
+  if (s.K <= 32) return launch_bwd<32>(prm, dP, dW, workspace, workspace_bytes, st);
+  return launch_bwd<64>(prm, dP, dW, workspace, workspace_bytes, st);
+}
+
+}  // namespace adlm

@@ -7,7 +7,13 @@
 //     (= R*16), SBO = byte distance between 8-row groups (= 128).  One kind::tf32 MMA consumes K = 8,
 //     i.e. two slabs; the start address advances by 2*R*16 per k-step.
 //   * an A operand in TMEM holds row m in lane m and k in consecutive 32-bit columns (".ts" form).
-//   * MN-major operands without swizzle do not work (all-zero result); nothing here uses them.
+//   * the 128-byte-swizzled K-major layout also works (tools/tc_probe2.cu, profiles/r1_tcgen05_probe2.log):
+//     rows of 128 B (32 floats), 8-row atoms of 1024 B, 16-byte chunk index XOR (row % 8); SBO = 1024,
+//     a k-step of 8 floats advances the start address by 32 B inside the atom, the next 32-float k-atom
+//     lies rows*128 B further.  It is used where one warp writes a COLUMN of the operand (conflict-free).
+//   * MN-major tf32 operands (no swizzle or SWIZZLE_128B) return zeros on this part; nothing here uses
+//     them — operands needed in both orientations are stored twice.
+//   * every MMA here uses M = 128 (row r of the accumulator = TMEM lane r).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -24,6 +30,21 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;   // descriptor version 1 (sm_100)
   return d;                 // layout type 0: no swizzle
+}
+
+__device__ __forceinline__ uint64_t make_desc_sw128(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)1 << 16;            // LBO unused for swizzled K-major
+  d |= (uint64_t)(1024 >> 4) << 32;  // SBO: 8-row group
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;            // SWIZZLE_128B
+  return d;
+}
+// float offset of element (r, c) in a [rows x cols] fp32 tile stored with the 128-byte swizzle
+__device__ __forceinline__ int off_sw128(int r, int c, int rows) {
+  const int ci = c & 31;
+  return (c >> 5) * rows * 32 + (r >> 3) * 256 + (r & 7) * 32 + (((ci >> 2) ^ (r & 7)) << 2) + (ci & 3);
 }
 
 // kind::tf32, fp32 accumulate, both operands K-major
@@ -92,6 +113,20 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__device__ __forceinline__ float lg2_approx(float x) {
+  float r;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 
 // round-to-nearest fp32 -> tf32 (the tensor core would otherwise truncate the low 13 mantissa bits)

@@ -404,15 +404,6 @@ int tc_head_fwd(const HeadShape& s, int prec_mode, const float* z, const float* 
   }
 }
 
-// Until the tcgen05 backward lands, the tensor-core modes take their gradients from the fp32 CUDA-core
-// kernel (which recomputes distances in fp32): same mathematics, tighter arithmetic than the forward.
-int tc_head_bwd(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
-                const float* dlogits, const float* ddist, const float* dsim, float* dz, float* dP,
-                float* dW, const StepExtras& ex, cudaStream_t st) {
-  (void)prec_mode;
-  return simt_head_bwd(s, z, P, W, dlogits, ddist, dsim, dz, dP, dW, ex, st);
-}
-
 int tc_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mask, const float* P, int N,
                  const int32_t* proto_class, long long patch_base, int prec_mode,
                  unsigned long long* packed_min, cudaStream_t st) {

@@ -9,7 +9,9 @@ int tc_head_fwd(const HeadShape& s, int prec_mode, const float* z, const float* 
                 cudaStream_t st);
 int tc_head_bwd(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
                 const float* dlogits, const float* ddist, const float* dsim, float* dz, float* dP,
-                float* dW, const StepExtras& ex, cudaStream_t st);
+                float* dW, const StepExtras& ex, void* workspace, size_t workspace_bytes, cudaStream_t st);
+// bytes of scratch tc_head_bwd needs for the per-CTA dP/dW partial sums (0 when the fp32 backward is used)
+size_t tc_bwd_workspace_bytes(int K, int N);
 int tc_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mask, const float* P, int N,
                  const int32_t* proto_class, long long patch_base, int prec_mode,
                  unsigned long long* packed_min, cudaStream_t st);

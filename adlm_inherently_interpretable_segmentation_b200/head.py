@@ -108,10 +108,14 @@ def head_backward(z, prototypes, weight, dlogits=None, ddist=None, dsim=None, ep
         dz = torch.empty_like(z) if need_dz else None
         dP = torch.empty((N, K), device=dev, dtype=torch.float32) if need_dP else None
         dW = torch.empty((C, N), device=dev, dtype=torch.float32) if need_dW else None
+        prec = _prec(precision or DEFAULT_PRECISION)
+        need = int(lib.adlm_head_bwd_workspace_bytes(K, N, prec))
+        ws = torch.empty(need, device=dev, dtype=torch.uint8) if need else None
         rc = lib.adlm_head_bwd(_lib.ptr(z), B, K, h * w, _lib.ptr(P), _lib.ptr(W), N, C,
-                               c_float(eps), _act(activation), _prec(precision or DEFAULT_PRECISION),
+                               c_float(eps), _act(activation), prec,
                                _lib.ptr(dlogits), _lib.ptr(ddist), _lib.ptr(dsim),
-                               _lib.ptr(dz), _lib.ptr(dP), _lib.ptr(dW), _lib.stream_ptr())
+                               _lib.ptr(dz), _lib.ptr(dP), _lib.ptr(dW), _lib.ptr(ws), c_size_t(need),
+                               _lib.stream_ptr())
     _lib.check(rc, "adlm_head_bwd")
     if dP is not None:
         dP = dP.reshape(prototypes.shape)

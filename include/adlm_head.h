@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define ADLM_ABI_VERSION 3
+#define ADLM_ABI_VERSION 4
 
 #if defined(__GNUC__)
 #define ADLM_API __attribute__((visibility("default")))
@@ -105,13 +105,19 @@ ADLM_API int adlm_head_fwd(const float* z, int B, int K, int HW,
  *   dlogits [B,HW,C] | NULL, ddist [B,N,HW] | NULL, dsim [B*HW,N] | NULL
  *   dz [B,K,HW] | NULL, dP [N,K] | NULL, dW [C,N] | NULL  (dP/dW are overwritten, not accumulated)
  * Distances are recomputed from z and P (never read back from HBM).
+ * ADLM_PREC_TF32 with K <= 64, N <= 192, C <= 32 runs on the tensor cores (two kernels: dZ with pixels in the
+ * TMEM lanes, dP/dW with prototypes in the lanes); 3xTF32 and larger shapes use the fp32 CUDA-core backward.
  */
 ADLM_API int adlm_head_bwd(const float* z, int B, int K, int HW,
                   const float* P, const float* W, int N, int C,
                   float eps, int act_mode, int prec_mode,
                   const float* dlogits, const float* ddist, const float* dsim,
                   float* dz, float* dP, float* dW,
+                  void* workspace, size_t workspace_bytes,
                   void* stream);
+/* scratch adlm_head_bwd needs for (K, N, prec_mode): per-CTA partial sums of dP/dW of the tensor-core
+ * backward (0 for the modes / shapes that use the fp32 backward; workspace may then be NULL) */
+ADLM_API size_t adlm_head_bwd_workspace_bytes(int K, int N, int prec_mode);
 
 /*
  * Fused training / validation step of the head ('log' activation):

