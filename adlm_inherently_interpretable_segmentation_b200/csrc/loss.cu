@@ -116,52 +116,71 @@ __global__ void k_ce(const float* __restrict__ logits, const int32_t* __restrict
   }
 }
 
-// One CTA per (label l = blockIdx.x, image b = blockIdx.y).  256 threads = 64 pixel lanes x 4 quarters of
-// the second prototype index.
+// One CTA per (label l = blockIdx.x, image b = blockIdx.y): the group's pixels are first compacted into a
+// shared-memory index list (a group is ~1/C of the image, so scanning with divergent lanes would waste ~C x
+// the work), then: per-prototype max, the J x J matrix A[a][b] = E_a[d_b], the pair terms, and — same CTA,
+// which owns exactly these pixels — dL/d(own distances) for the backward kernels.
 __global__ void __launch_bounds__(256)
-k_kld_stats(const float* __restrict__ own, const int32_t* __restrict__ target, const int* __restrict__ hist,
-            const int* __restrict__ cls_count, const int* __restrict__ counts, int HW, int C,
-            float coef /* w_kld * grad_scale */, float* __restrict__ gtab, double* __restrict__ accum) {
+k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const int* __restrict__ hist,
+      const int* __restrict__ cls_count, const int* __restrict__ counts, int HW, int C,
+      float coef /* w_kld * grad_scale */, float* __restrict__ own_grad, double* __restrict__ accum) {
+  extern __shared__ int s_list[];                 // [cnt] pixel indices of this group
   const int l = blockIdx.x, b = blockIdx.y;
-  float* gt = gtab + ((size_t)b * C + l) * GT_SIZE;
   const int J = min(cls_count[l], JMAX);
   const int cnt = hist[b * (C + 1) + l];
-  const int tid = threadIdx.x;
-  if (J < 2 || cnt < 2) {
-    if (tid == 0) gt[GT_VALID] = 0.f;
-    return;
-  }
-  __shared__ float s_mx[JMAX];
-  __shared__ float s_S[JMAX];
+  const int tid = threadIdx.x, lane = tid & 31;
+  if (cnt == 0) return;
+  __shared__ int s_n;
+  __shared__ float s_mx[JMAX], s_S[JMAX], s_lse[JMAX], s_cs[JMAX], s_r[JMAX];
   __shared__ float s_T[JMAX][JMAX];
   __shared__ float s_red[8][JMAX];
   __shared__ float s_kl[JMAX][JMAX];
-  const int lane64 = tid & 63, q = tid >> 6;
   const int32_t* t = target + (size_t)b * HW;
   const float* ob = own + (size_t)b * HW * JMAX;
-
-  // pass A: per-prototype max over the group's pixels
+  if (tid == 0) s_n = 0;
+  __syncthreads();
+  for (int p0 = 0; p0 < HW; p0 += 256) {
+    const int p = p0 + tid;
+    const bool hit = p < HW && t[p] == l;
+    const unsigned bal = __ballot_sync(0xffffffffu, hit);
+    int base = 0;
+    if (lane == 0 && bal) base = atomicAdd(&s_n, __popc(bal));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (hit) s_list[base + __popc(bal & ((1u << lane) - 1u))] = p;
+  }
+  __syncthreads();
+  const int n = s_n;                              // == cnt
+  const bool valid_group = J >= 2 && n >= 2;
+  float4* og = own_grad ? reinterpret_cast<float4*>(own_grad + (size_t)b * HW * JMAX) : nullptr;
+  if (!valid_group) {
+    if (og)
+      for (int i = tid; i < n; i += 256) {
+        float4* o = og + (size_t)s_list[i] * (JMAX / 4);
+#pragma unroll
+        for (int v = 0; v < JMAX / 4; ++v) o[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    return;
+  }
+  // pass A: per-prototype max
   float mx[JMAX];
 #pragma unroll
   for (int j = 0; j < JMAX; ++j) mx[j] = -INFINITY;
-  for (int p = tid; p < HW; p += 256) {
-    if (t[p] == l) {
-      const float4* o4 = reinterpret_cast<const float4*>(ob + (size_t)p * JMAX);
+  for (int i = tid; i < n; i += 256) {
+    const float4* o4 = reinterpret_cast<const float4*>(ob + (size_t)s_list[i] * JMAX);
 #pragma unroll
-      for (int v = 0; v < JMAX / 4; ++v) {
-        const float4 x = o4[v];
-        mx[4 * v] = fmaxf(mx[4 * v], x.x); mx[4 * v + 1] = fmaxf(mx[4 * v + 1], x.y);
-        mx[4 * v + 2] = fmaxf(mx[4 * v + 2], x.z); mx[4 * v + 3] = fmaxf(mx[4 * v + 3], x.w);
-      }
+    for (int v = 0; v < JMAX / 4; ++v) {
+      const float4 x = o4[v];
+      mx[4 * v] = fmaxf(mx[4 * v], x.x); mx[4 * v + 1] = fmaxf(mx[4 * v + 1], x.y);
+      mx[4 * v + 2] = fmaxf(mx[4 * v + 2], x.z); mx[4 * v + 3] = fmaxf(mx[4 * v + 3], x.w);
     }
   }
 #pragma unroll
   for (int j = 0; j < JMAX; ++j) mx[j] = warp_max(mx[j]);
-  if ((tid & 31) == 0) {
+  if (lane == 0) {
 #pragma unroll
     for (int j = 0; j < JMAX; ++j) s_red[tid >> 5][j] = mx[j];
   }
-  for (int i = tid; i < JMAX * JMAX; i += 256) (&s_T[0][0])[i] = 0.f;
+  (&s_T[0][0])[tid] = 0.f;                        // 256 threads == JMAX*JMAX
   if (tid < JMAX) s_S[tid] = 0.f;
   __syncthreads();
   if (tid < JMAX) {
@@ -170,8 +189,8 @@ k_kld_stats(const float* __restrict__ own, const int32_t* __restrict__ target, c
     s_mx[tid] = m;
   }
   __syncthreads();
-
-  // pass B: S_j = sum exp(d_j - mx_j),  T[j][i] = sum exp(d_j - mx_j) d_i   (this thread: i in its quarter)
+  // pass B: S_j = sum exp(d_j - mx_j), T[j][i] = sum exp(d_j - mx_j) d_i; thread = (pixel lane, quarter of i)
+  const int lane64 = tid & 63, q = tid >> 6;
   float S[JMAX];
   float T[JMAX][JMAX / 4];
 #pragma unroll
@@ -180,26 +199,24 @@ k_kld_stats(const float* __restrict__ own, const int32_t* __restrict__ target, c
 #pragma unroll
     for (int i = 0; i < JMAX / 4; ++i) T[j][i] = 0.f;
   }
-  for (int p = lane64; p < HW; p += 64) {
-    if (t[p] == l) {
-      float d[JMAX];
-      const float4* o4 = reinterpret_cast<const float4*>(ob + (size_t)p * JMAX);
+  static_assert(JMAX / 4 == 4, "quarter layout assumes JMAX == 16");
+  for (int it = lane64; it < n; it += 64) {
+    const float4* o4 = reinterpret_cast<const float4*>(ob + (size_t)s_list[it] * JMAX);
+    float d[JMAX];
 #pragma unroll
-      for (int v = 0; v < JMAX / 4; ++v) {
-        const float4 x = o4[v];
-        d[4 * v] = x.x; d[4 * v + 1] = x.y; d[4 * v + 2] = x.z; d[4 * v + 3] = x.w;
-      }
-      const float4 dq4 = o4[q];                       // this thread's quarter of the second index
-      const float dq[4] = {dq4.x, dq4.y, dq4.z, dq4.w};
-      static_assert(JMAX / 4 == 4, "quarter layout assumes JMAX == 16");
+    for (int v = 0; v < JMAX / 4; ++v) {
+      const float4 x = o4[v];
+      d[4 * v] = x.x; d[4 * v + 1] = x.y; d[4 * v + 2] = x.z; d[4 * v + 3] = x.w;
+    }
+    const float4 dq4 = o4[q];
+    const float dq[4] = {dq4.x, dq4.y, dq4.z, dq4.w};
 #pragma unroll
-      for (int j = 0; j < JMAX; ++j) {
-        if (j < J) {
-          const float e = __expf(d[j] - s_mx[j]);
-          S[j] += e;
+    for (int j = 0; j < JMAX; ++j) {
+      if (j < J) {
+        const float e = __expf(d[j] - s_mx[j]);
+        S[j] += e;
 #pragma unroll
-          for (int i = 0; i < JMAX / 4; ++i) T[j][i] = fmaf(e, dq[i], T[j][i]);
-        }
+        for (int i = 0; i < 4; ++i) T[j][i] = fmaf(e, dq[i], T[j][i]);
       }
     }
   }
@@ -207,21 +224,20 @@ k_kld_stats(const float* __restrict__ own, const int32_t* __restrict__ target, c
   for (int j = 0; j < JMAX; ++j) {
     S[j] = warp_sum(S[j]);
 #pragma unroll
-    for (int i = 0; i < JMAX / 4; ++i) T[j][i] = warp_sum(T[j][i]);
+    for (int i = 0; i < 4; ++i) T[j][i] = warp_sum(T[j][i]);
   }
-  if ((tid & 31) == 0) {
+  if (lane == 0) {
 #pragma unroll
     for (int j = 0; j < JMAX; ++j) {
       if (q == 0) atomicAdd(&s_S[j], S[j]);
 #pragma unroll
-      for (int i = 0; i < JMAX / 4; ++i) atomicAdd(&s_T[j][q * (JMAX / 4) + i], T[j][i]);
+      for (int i = 0; i < 4; ++i) atomicAdd(&s_T[j][q * 4 + i], T[j][i]);
     }
   }
   __syncthreads();
-  // A[j][i] = T[j][i] / S[j]  (in place)
   {
-    const int j = tid / JMAX, i = tid % JMAX;    // 256 threads == JMAX*JMAX
-    if (j < J && i < J) s_T[j][i] = s_T[j][i] / s_S[j];
+    const int j = tid / JMAX, i = tid % JMAX;
+    if (j < J && i < J) s_T[j][i] = s_T[j][i] / s_S[j];     // A[j][i] = E_j[d_i]
   }
   __syncthreads();
   const float n_terms = (float)counts[1];
@@ -236,10 +252,9 @@ k_kld_stats(const float* __restrict__ own, const int32_t* __restrict__ target, c
       cv = -0.5f * coef * e / n_terms;
     }
     s_kl[a][c] = cv;
-    gt[GT_C + a * JMAX + c] = cv;
   }
   esum = warp_sum(esum);
-  if ((tid & 31) == 0 && esum != 0.f) atomicAdd(&accum[2], (double)esum);
+  if (lane == 0 && esum != 0.f) atomicAdd(&accum[2], (double)esum);
   __syncthreads();
   if (tid < JMAX) {
     const int a = tid;
@@ -250,62 +265,86 @@ k_kld_stats(const float* __restrict__ own, const int32_t* __restrict__ target, c
         r = fmaf(s_kl[a][c], s_T[a][a] - s_T[a][c], r);
       }
     }
-    gt[GT_CSUM + a] = cs;
-    gt[GT_R + a] = r;
-    gt[GT_LSE + a] = (a < J) ? s_mx[a] + __logf(s_S[a]) : 0.f;
+    s_cs[a] = cs;
+    s_r[a] = r;
+    s_lse[a] = (a < J) ? s_mx[a] + __logf(s_S[a]) : 0.f;
   }
-  if (tid == 0) gt[GT_VALID] = (float)J;
-}
-
-// One thread per pixel: dL/d(own distances) from the KLD term.
-__global__ void k_kld_grad(const float* __restrict__ own, const int32_t* __restrict__ target,
-                           const float* __restrict__ gtab, int HW, int C, long long M,
-                           float* __restrict__ own_grad) {
-  const long long m = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (m >= M) return;
-  const int b = (int)(m / HW);
-  const int l = target[m];
-  float4* out = reinterpret_cast<float4*>(own_grad + m * JMAX);
-  int J = 0;
-  const float* gt = nullptr;
-  if (l >= 0 && l < C) {
-    gt = gtab + ((size_t)b * C + l) * GT_SIZE;
-    J = (int)gt[GT_VALID];
-  }
-  if (J < 2) {
+  __syncthreads();
+  if (og == nullptr) return;
+  // gradient wrt the own-class distances of every pixel of the group
+  for (int it = tid; it < n; it += 256) {
+    const int p = s_list[it];
+    const float4* o4 = reinterpret_cast<const float4*>(ob + (size_t)p * JMAX);
+    float d[JMAX], qv[JMAX], g[JMAX];
 #pragma unroll
-    for (int v = 0; v < JMAX / 4; ++v) out[v] = make_float4(0.f, 0.f, 0.f, 0.f);
-    return;
-  }
-  float d[JMAX], qv[JMAX], g[JMAX];
-  const float4* o4 = reinterpret_cast<const float4*>(own + m * JMAX);
-#pragma unroll
-  for (int v = 0; v < JMAX / 4; ++v) {
-    const float4 x = o4[v];
-    d[4 * v] = x.x; d[4 * v + 1] = x.y; d[4 * v + 2] = x.z; d[4 * v + 3] = x.w;
-  }
-#pragma unroll
-  for (int a = 0; a < JMAX; ++a) qv[a] = (a < J) ? __expf(d[a] - gt[GT_LSE + a]) : 0.f;
-#pragma unroll
-  for (int a = 0; a < JMAX; ++a) {
-    float ga = 0.f;
-    if (a < J) {
-      float cd = 0.f, cq = 0.f;
-#pragma unroll
-      for (int c = 0; c < JMAX; ++c) {
-        if (c < J) {
-          const float cc = gt[GT_C + a * JMAX + c];
-          cd = fmaf(cc, d[c], cd);
-          cq = fmaf(cc, qv[c], cq);
-        }
-      }
-      const float cs = gt[GT_CSUM + a];
-      ga = qv[a] * (d[a] * cs - cd - gt[GT_R + a]) + qv[a] * cs - cq;
+    for (int v = 0; v < JMAX / 4; ++v) {
+      const float4 x = o4[v];
+      d[4 * v] = x.x; d[4 * v + 1] = x.y; d[4 * v + 2] = x.z; d[4 * v + 3] = x.w;
     }
-    g[a] = ga;
-  }
 #pragma unroll
-  for (int v = 0; v < JMAX / 4; ++v) out[v] = make_float4(g[4 * v], g[4 * v + 1], g[4 * v + 2], g[4 * v + 3]);
+    for (int a = 0; a < JMAX; ++a) qv[a] = (a < J) ? __expf(d[a] - s_lse[a]) : 0.f;
+#pragma unroll
+    for (int a = 0; a < JMAX; ++a) {
+      float ga = 0.f;
+      if (a < J) {
+        float cd = 0.f, cq = 0.f;
+#pragma unroll
+        for (int c = 0; c < JMAX; ++c) {
+          if (c < J) {
+            const float cc = s_kl[a][c];
+            cd = fmaf(cc, d[c], cd);
+            cq = fmaf(cc, qv[c], cq);
+          }
+        }
+        ga = qv[a] * (d[a] * s_cs[a] - cd - s_r[a]) + qv[a] * s_cs[a] - cq;
+      }
+      g[a] = ga;
+    }
+    float4* o = og + (size_t)p * (JMAX / 4);
+#pragma unroll
+    for (int v = 0; v < JMAX / 4; ++v) o[v] = make_float4(g[4 * v], g[4 * v + 1], g[4 * v + 2], g[4 * v + 3]);
+  }
+}
+// Single-CTA prologue of the step (small batches): label histogram per image, class sizes, the two loss
+// normalisers, prototype ranks, cleared accumulators — one launch instead of a memset and three kernels.
+__global__ void __launch_bounds__(1024)
+k_step_prepare(const int32_t* __restrict__ target, const int32_t* __restrict__ proto_class, int B, int HW, int C,
+               int N, int ignore_void, int* __restrict__ hist, int* __restrict__ cls_count,
+               int* __restrict__ counts, int32_t* __restrict__ rank, double* __restrict__ accum) {
+  extern __shared__ int sh[];                       // [B][C+1] histogram, then [C] class sizes
+  int* s_cls = sh + B * (C + 1);
+  __shared__ int s_valid, s_terms;
+  const int tid = threadIdx.x;
+  for (int i = tid; i < B * (C + 1) + C; i += 1024) sh[i] = 0;
+  if (tid == 0) { s_valid = 0; s_terms = 0; }
+  __syncthreads();
+  const long long M = (long long)B * HW;
+  for (long long m = tid; m < M; m += 1024) {
+    const int l = target[m];
+    if (l >= 0 && l <= C) atomicAdd(&sh[(int)(m / HW) * (C + 1) + l], 1);
+  }
+  for (int n = tid; n < N; n += 1024) {
+    const int c = proto_class[n];
+    if (c >= 0 && c < C) atomicAdd(&s_cls[c], 1);
+    int r = 0;
+    for (int i = 0; i < n; ++i) r += (proto_class[i] == c);
+    rank[n] = r;
+  }
+  __syncthreads();
+  int valid = 0, terms = 0;
+  for (int i = tid; i < B * (C + 1); i += 1024) {
+    const int l = i % (C + 1), cnt = sh[i];
+    hist[i] = cnt;
+    if (ignore_void) { if (l >= 1) valid += cnt; }
+    else             { if (l < C) valid += cnt; }
+    if (l < C && cnt >= 2 && s_cls[l] >= 2) terms += s_cls[l] * (s_cls[l] - 1) / 2;
+  }
+  if (valid) atomicAdd(&s_valid, valid);
+  if (terms) atomicAdd(&s_terms, terms);
+  __syncthreads();
+  for (int c = tid; c < C; c += 1024) cls_count[c] = s_cls[c];
+  if (tid == 0) { counts[0] = s_valid; counts[1] = s_terms; }
+  if (tid < 4) accum[tid] = 0.0;
 }
 
 // l1 = |W * (1 - identity^T)|_1 (module.py:213-218), dW += w_l1 * sign(W) * mask, final scalars.
@@ -409,19 +448,22 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
   const bool want_grad = (dz != nullptr) || (dP != nullptr) || (dW != nullptr);
   float* logits = logits_out ? logits_out : ws.logits;
 
-  ADLM_CUDA(cudaMemsetAsync(ws.hist, 0, sizeof(int) * (size_t)B * (C + 1), st));
-  {
+  const size_t prep_smem = sizeof(int) * ((size_t)B * (C + 1) + C);
+  if (prep_smem <= 48 * 1024 && M <= (1ll << 21)) {
+    k_step_prepare<<<1, 1024, prep_smem, st>>>(target, proto_class, B, HW, C, N, ignore_void, ws.hist, ws.cls_count,
+                                               ws.counts, ws.rank, ws.accum);
+    ADLM_LAUNCH_CHECK();
+  } else {
+    ADLM_CUDA(cudaMemsetAsync(ws.hist, 0, sizeof(int) * (size_t)B * (C + 1), st));
     dim3 grid(min(cdiv(HW, 256), 64), B);
     k_label_hist<<<grid, 256, sizeof(int) * (C + 1), st>>>(target, HW, C, ws.hist);
     ADLM_LAUNCH_CHECK();
+    k_loss_prepare<<<1, 256, 0, st>>>(ws.hist, proto_class, B, C, N, ignore_void, ws.cls_count, ws.counts, ws.accum);
+    ADLM_LAUNCH_CHECK();
+    k_proto_rank<<<cdiv(N, 128), 128, 0, st>>>(proto_class, N, ws.rank);
+    ADLM_LAUNCH_CHECK();
   }
-  k_loss_prepare<<<1, 256, 0, st>>>(ws.hist, proto_class, B, C, N, ignore_void, ws.cls_count, ws.counts, ws.accum);
-  ADLM_LAUNCH_CHECK();
-  k_proto_rank<<<cdiv(N, 128), 128, 0, st>>>(proto_class, N, ws.rank);
-  ADLM_LAUNCH_CHECK();
   const int* counts = global_counts ? global_counts : ws.counts;
-  // own-class distances of pixels whose label has no prototypes are never written: clear the buffer
-  ADLM_CUDA(cudaMemsetAsync(ws.own, 0, sizeof(float) * (size_t)M * JMAX, st));
 
   StepExtras ex;
   ex.target = target;
@@ -437,13 +479,13 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
   ADLM_LAUNCH_CHECK();
   {
     dim3 grid(C, B);
-    k_kld_stats<<<grid, 256, 0, st>>>(ws.own, target, ws.hist, ws.cls_count, counts, HW, C,
-                                      w_kld * grad_scale, ws.gtab, ws.accum);
+    ADLM_CHECK_SUPPORTED((size_t)HW * sizeof(int) <= 200 * 1024, "feature map too large for the KLD kernel (h*w > 51200)");
+    ADLM_CUDA(cudaFuncSetAttribute(k_kld, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)HW * sizeof(int))));
+    k_kld<<<grid, 256, (size_t)HW * sizeof(int), st>>>(ws.own, target, ws.hist, ws.cls_count, counts, HW, C,
+                                                    w_kld * grad_scale, want_grad ? ws.own_grad : nullptr, ws.accum);
     ADLM_LAUNCH_CHECK();
   }
   if (want_grad) {
-    k_kld_grad<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(ws.own, target, ws.gtab, HW, C, M, ws.own_grad);
-    ADLM_LAUNCH_CHECK();
     StepExtras exb = ex;
     exb.own_dist = nullptr;
     exb.own_grad = ws.own_grad;
@@ -451,7 +493,7 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
                                 ws.bwd_scratch_bytes, st)) != ADLM_OK)
       return rc;
   }
-  k_finalize<<<1, 256, 0, st>>>(W, proto_class, C, N, w_ce, w_kld, w_l1, grad_scale, counts, ws.accum,
+  k_finalize<<<1, 1024, 0, st>>>(W, proto_class, C, N, w_ce, w_kld, w_l1, grad_scale, counts, ws.accum,
                                 dW, scalars);
   ADLM_LAUNCH_CHECK();
   return ADLM_OK;

@@ -519,13 +519,17 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
 }
 
 // dP[n][k] = sum over CTAs; dW[c][n] = sum over CTAs (stored [n][32] per CTA)
-__global__ void k_reduce_partials(const float* __restrict__ partials, int n_parts, int Npad2, int KP, int N, int K,
-                                  int C, float* __restrict__ dP, float* __restrict__ dW) {
+__global__ void __launch_bounds__(256)
+k_reduce_partials(const float* __restrict__ partials, int n_parts, int Npad2, int KP, int N, int K,
+                  int C, float* __restrict__ dP, float* __restrict__ dW) {
+  // 4 threads per output element, each sums a quarter of the per-CTA partials
   const size_t per = (size_t)Npad2 * KP + (size_t)Npad2 * 32;
   const int total = N * K + C * N;
-  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+  const int idx = (blockIdx.x * 256 + threadIdx.x) >> 2, q4 = threadIdx.x & 3;
+  float a = 0.f;
+  float* dst = nullptr;
+  if (idx < total) {
     size_t off;
-    float* dst;
     if (idx < N * K) {
       const int n = idx / K, k = idx - n * K;
       off = (size_t)n * KP + k;
@@ -535,11 +539,20 @@ __global__ void k_reduce_partials(const float* __restrict__ partials, int n_part
       off = (size_t)Npad2 * KP + (size_t)n * 32 + c;
       dst = dW ? dW + j : nullptr;
     }
-    if (dst == nullptr) continue;
-    float a = 0.f;
-    for (int q = 0; q < n_parts; ++q) a += partials[(size_t)q * per + off];
-    *dst = a;
+    if (dst != nullptr) {
+      float a0 = 0.f, a1 = 0.f;
+      int q = q4;
+      for (; q + 4 < n_parts; q += 8) {
+        a0 += partials[(size_t)q * per + off];
+        a1 += partials[(size_t)(q + 4) * per + off];
+      }
+      if (q < n_parts) a0 += partials[(size_t)q * per + off];
+      a = a0 + a1;
+    }
   }
+  a += __shfl_xor_sync(0xffffffffu, a, 1);
+  a += __shfl_xor_sync(0xffffffffu, a, 2);
+  if (q4 == 0 && dst != nullptr) *dst = a;
 }
 
 int g_sms = 0;
@@ -582,7 +595,7 @@ int launch_bwd(TcBwdParams prm, float* dP, float* dW, void* workspace, size_t wo
     k_tc_bwd_dp<KP><<<grid, DP_THREADS, bytes, st>>>(prm, NB);
     ADLM_LAUNCH_CHECK();
     const int total = prm.N * prm.K + prm.C * prm.N;
-    k_reduce_partials<<<(total + 255) / 256, 256, 0, st>>>(prm.partials, grid, Npad2, KP, prm.N, prm.K, prm.C, dP, dW);
+    k_reduce_partials<<<(total * 4 + 255) / 256, 256, 0, st>>>(prm.partials, grid, Npad2, KP, prm.N, prm.K, prm.C, dP, dW);
     ADLM_LAUNCH_CHECK();
   }
   return ADLM_OK;
