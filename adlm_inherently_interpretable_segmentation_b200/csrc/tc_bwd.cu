@@ -67,7 +67,7 @@ struct DzSmem {
   static __host__ __device__ size_t total(int Npad, int C8) { return misc(Npad, C8) + (size_t)Npad * 12 + 256; }
 };
 
-template <int KP>
+template <int KP, bool GENERIC>
 __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
   using L = DzSmem<KP>;
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -81,6 +81,7 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
   int* prs = reinterpret_cast<int*>(misc + (size_t)Npad * 8);
   uint64_t* bars = reinterpret_cast<uint64_t*>(misc + (size_t)Npad * 12);
   uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 4);
+  uint32_t* cmask = reinterpret_cast<uint32_t*>(misc + (size_t)Npad * 12 + 64);   // class bits per 16-prototype chunk
 
   const int tid = threadIdx.x, wg = tid >> 7, wt = tid & 127, warp_in_wg = wt >> 5;
   const bool kld = p.own_grad != nullptr;
@@ -117,6 +118,15 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
     pcs[n] = (kld && n < N) ? p.proto_class[n] : -1;
     prs[n] = (kld && n < N) ? p.proto_rank[n] : 0;
   }
+  __syncthreads();
+  for (int c = tid; c < Npad / 16; c += 256) {
+    uint32_t mk = 0u;
+    for (int i = 0; i < 16; ++i) {
+      const int pc = pcs[c * 16 + i];
+      if (pc >= 0 && pc < 32) mk |= 1u << pc;
+    }
+    cmask[c] = mk;
+  }
   fence_async_smem();
   fence_before();
   __syncthreads();
@@ -136,13 +146,26 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
   const long long stride = (long long)gridDim.x * 2;
   long long tile = (long long)blockIdx.x + (long long)wg * gridDim.x;
   uint32_t ph_a = 0, ph_z = 0;
+  const float eps = p.eps, epsm1 = p.eps - 1.f;
+  const bool act_log = p.act_mode == ADLM_ACT_LOG;
+
+  // features of the next tile travel while this one is processed
+  float zr[KP];
+  auto prefetch = [&](long long t) {
+    const long long m = t * TILE + wt;
+    const bool ok = t < p.num_tiles && m < p.M;
+    const int b = ok ? (int)(m / HW) : 0;
+    const float* src = p.z + ((size_t)b * K) * HW + (ok ? (m - (long long)b * HW) : 0);
+#pragma unroll
+    for (int k = 0; k < KP; ++k) zr[k] = (ok && k < K) ? __ldg(src + (size_t)k * HW) : CENTRE;
+  };
+  prefetch(tile);
 
   for (; tile < p.num_tiles; tile += stride) {
     const long long m = tile * TILE + wt;
     const bool valid = m < p.M;
     const int b = valid ? (int)(m / HW) : 0;
     const int pix = valid ? (int)(m - (long long)b * HW) : 0;
-    const float* zsrc = p.z + ((size_t)b * K) * HW + pix;
 
     // ---- operands of this tile: Zk (centred, rounded), dLk ----
     float x2 = 0.f;
@@ -151,8 +174,7 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
       float v[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const int k = k4 * 4 + j;
-        v[j] = rna_tf32((valid && k < K) ? __ldg(zsrc + (size_t)k * HW) - CENTRE : 0.f);
+        v[j] = rna_tf32(zr[k4 * 4 + j] - CENTRE);
         x2 = fmaf(v[j], v[j], x2);
       }
       *reinterpret_cast<float4*>(Zk + ((size_t)k4 * TILE + wt) * 4) = make_float4(v[0], v[1], v[2], v[3]);
@@ -168,9 +190,11 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
     }
     int lab = -1;
     if (kld && valid) lab = p.target[m];
+    const bool lab_ok = lab >= 0 && lab < 32;
     fence_async_smem();
     fence_before();
     named_bar_sync(1 + wg, 128);
+    prefetch(tile + stride);
 
     float rs = 0.f;
     for (int h = 0; h < 2; ++h) {
@@ -193,21 +217,44 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
         uint32_t ra[16], rg[16], out[16];
         tmem_ld16(tD + lane_field + ch * 16, ra);
         tmem_ld16(tG + lane_field + ch * 16, rg);
-        tmem_ld_wait();
         const int n0 = h * NH + ch * 16;
+        float xp[16];
+#pragma unroll
+        for (int v4 = 0; v4 < 4; ++v4) {
+          const float4 q = *reinterpret_cast<const float4*>(p2s + n0 + v4 * 4);
+          xp[v4 * 4] = x2 + q.x; xp[v4 * 4 + 1] = x2 + q.y; xp[v4 * 4 + 2] = x2 + q.z; xp[v4 * 4 + 3] = x2 + q.w;
+        }
+        tmem_ld_wait();
+        float g[16];
+        uint32_t pos = 0u;
+        // padding columns and out-of-range pixels need no masking: their dlogits.W is exactly 0
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
-          const int n = n0 + i;
-          const float pre = fmaf(-2.f, __uint_as_float(ra[i]), x2 + p2s[n]);
+          const float pre = fmaf(-2.f, __uint_as_float(ra[i]), xp[i]);
           const float d = fmaxf(pre, 0.f);
-          float g = __uint_as_float(rg[i]);
-          if (p.dsim != nullptr && valid && n < N) g += __ldg(p.dsim + (size_t)m * N + n);
-          g *= dsdd_of(d, p.eps, p.act_mode);
-          if (p.ddist != nullptr && valid && n < N) g += __ldg(p.ddist + ((size_t)b * N + n) * HW + pix);
-          if (lab >= 0 && pcs[n] == lab) g += __ldg(p.own_grad + (size_t)m * JMAX + prs[n]);
-          g = (pre > 0.f && valid && n < N) ? g : 0.f;
-          rs += g;
-          out[i] = __float_as_uint(rna_tf32(g));
+          float gv = __uint_as_float(rg[i]);
+          if (GENERIC) {
+            const int n = n0 + i;
+            if (p.dsim != nullptr && valid && n < N) gv += __ldg(p.dsim + (size_t)m * N + n);
+          }
+          gv *= act_log ? epsm1 * rcp_approx((d + 1.f) * (d + eps)) : -1.f;
+          if (GENERIC) {
+            const int n = n0 + i;
+            if (p.ddist != nullptr && valid && n < N) gv += __ldg(p.ddist + ((size_t)b * N + n) * HW + pix);
+          }
+          pos |= (pre > 0.f ? 1u : 0u) << i;
+          g[i] = gv;
+        }
+        if (lab_ok && ((cmask[n0 >> 4] >> lab) & 1u)) {     // KLD term: only the pixel's own-class prototypes
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (pcs[n0 + i] == lab) g[i] += __ldg(p.own_grad + (size_t)m * JMAX + prs[n0 + i]);
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const float gv = ((pos >> i) & 1u) ? g[i] : 0.f;
+          rs += gv;
+          out[i] = __float_as_uint(rna_tf32(gv));
         }
         tmem_st16(tD + lane_field + ch * 16, out);
       }
@@ -225,18 +272,24 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
     mbar_wait(bar_z, ph_z);
     ph_z ^= 1u;
     fence_after();
-    // ---- dz = 2 (rowsum(G) zc - G Pc) ----
+    // ---- dz = 2 (rowsum(G) zc - G Pc); zc re-read from the operand tile (tf32-rounded, 2^-12 relative) ----
     float* dst = p.dz + ((size_t)b * K) * HW + pix;
 #pragma unroll
     for (int ch = 0; ch < KP / 16; ++ch) {
       uint32_t r[16];
       tmem_ld16(tZ + lane_field + ch * 16, r);
+      float zc[16];
+#pragma unroll
+      for (int v4 = 0; v4 < 4; ++v4) {
+        const float4 q = *reinterpret_cast<const float4*>(Zk + ((size_t)(ch * 4 + v4) * TILE + wt) * 4);
+        zc[v4 * 4] = q.x; zc[v4 * 4 + 1] = q.y; zc[v4 * 4 + 2] = q.z; zc[v4 * 4 + 3] = q.w;
+      }
       tmem_ld_wait();
       if (valid) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           const int k = ch * 16 + i;
-          if (k < K) dst[(size_t)k * HW] = 2.f * (rs * (__ldg(zsrc + (size_t)k * HW) - CENTRE) - __uint_as_float(r[i]));
+          if (k < K) dst[(size_t)k * HW] = 2.f * fmaf(rs, zc[i], -__uint_as_float(r[i]));
         }
       }
     }
@@ -263,14 +316,15 @@ struct DpSmem {
   static __host__ __device__ size_t dlk(int Npad2, int C8) { return zk(Npad2, C8) + (size_t)KP * TILE * 4; }
   static __host__ __device__ size_t misc(int Npad2, int C8) { return dlk(Npad2, C8) + (size_t)C8 * TILE * 4; }
   // x2 [128] f32, lab [128] i32, img [128] i32, pix [128] i32, cs [2][2][128] f32, barriers
-  static __host__ __device__ size_t total(int Npad2, int C8) { return misc(Npad2, C8) + 128 * 16 + 512 * 4 + 128; }
+  static __host__ __device__ size_t total(int Npad2, int C8) { return misc(Npad2, C8) + 128 * 16 + 512 * 4 + 128 + 512; }
 };
 
-template <int KP>
-__global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p, int NB) {
+template <int KP, int NB, bool GENERIC>
+__global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p) {
   using L = DpSmem<KP>;
   extern __shared__ __align__(1024) uint8_t smem[];
-  const int Npad2 = NB * 128, C8 = p.C8, K = p.K, N = p.N, C = p.C, HW = p.HW;
+  constexpr int Npad2 = NB * 128;
+  const int C8 = p.C8, K = p.K, N = p.N, C = p.C, HW = p.HW;
   float* ZtB = reinterpret_cast<float*>(smem + L::zt());
   float* dLtB = reinterpret_cast<float*>(smem + L::dlt());
   float* PkA = reinterpret_cast<float*>(smem + L::pk());
@@ -285,6 +339,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
   float* css = reinterpret_cast<float*>(misc + 2048);           // [half][blk][128]
   uint64_t* bars = reinterpret_cast<uint64_t*>(misc + 2048 + 2048);
   uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 4);
+  uint32_t* clsm = reinterpret_cast<uint32_t*>(misc + 2048 + 2048 + 64);   // [32 classes][4 words]: pixels of the tile
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const bool kld = p.own_grad != nullptr;
@@ -345,6 +400,10 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
       const long long m = ((long long)blockIdx.x + (long long)it * gridDim.x) * TILE + cw;
       const bool valid = m < p.M;
       if (it > 0) mbar_wait(bar_free, (uint32_t)(it - 1) & 1u);
+      clsm[cw] = 0u;
+      named_bar_sync(2, 128);
+      const int mylab = (valid && kld) ? p.target[m] : -1;
+      if (mylab >= 0 && mylab < 32) atomicOr(&clsm[mylab * 4 + (cw >> 5)], 1u << (cw & 31));
       float x2 = 0.f;
 #pragma unroll
       for (int k4 = 0; k4 < KP / 4; ++k4) {
@@ -373,7 +432,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
       const int b = valid ? (int)(m / HW) : 0;
       imgs[cw] = b;
       pixs[cw] = valid ? (int)(m - (long long)b * HW) : 0;
-      labs[cw] = valid ? (kld ? p.target[m] : -1) : -2;
+      labs[cw] = valid ? mylab : -2;
       fence_async_smem();
       mbar_arrive(bar_full);
       prefetch(it + 1);
@@ -414,8 +473,9 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
     // ================= epilogue: thread = (prototype lane, pixel-column half) =================
     const int half = warp >> 2, lane_n = ((warp & 3) << 5) + lane;
     const uint32_t lane_field = (uint32_t)((warp & 3) * 32) << 16;
-    float p2[2] = {0.f, 0.f}, cs[2] = {0.f, 0.f};
-    int pcl[2] = {-5, -5}, prk[2] = {0, 0};
+    float p2[NB], cs[NB];
+    int pcl[NB], prk[NB];
+#pragma unroll
     for (int blk = 0; blk < NB; ++blk) {
       const int n = blk * 128 + lane_n;
       float a = 0.f;
@@ -424,12 +484,20 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
         a = fmaf(v.x, v.x, a); a = fmaf(v.y, v.y, a); a = fmaf(v.z, v.z, a); a = fmaf(v.w, v.w, a);
       }
       p2[blk] = a;
+      cs[blk] = 0.f;
+      pcl[blk] = -1;
+      prk[blk] = 0;
       if (kld && n < N) { pcl[blk] = p.proto_class[n]; prk[blk] = p.proto_rank[n]; }
+      if (pcl[blk] < 0 || pcl[blk] >= 32) pcl[blk] = -1;
     }
+    const float eps = p.eps, epsm1 = p.eps - 1.f;
+    const bool act_log = p.act_mode == ADLM_ACT_LOG;
     uint32_t g = 0;
     for (int it = 0; it < iters; ++it) {
       const long long m0 = ((long long)blockIdx.x + (long long)it * gridDim.x) * TILE;
+      const int npx = (int)((p.M - m0) < TILE ? (p.M - m0) : TILE);   // valid pixel columns of this tile
       mbar_wait(bar_full, (uint32_t)it & 1u);
+#pragma unroll
       for (int blk = 0; blk < NB; ++blk) {
         const int n = blk * 128 + lane_n;
         mbar_wait(bar_acc, g & 1u);
@@ -441,33 +509,54 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
             uint32_t ra[16], rg[16], og[16], os[16];
             tmem_ld16(tD1 + lane_field + c0, ra);
             tmem_ld16(tGl + lane_field + c0, rg);
+            float xp[16];
+#pragma unroll
+            for (int v4 = 0; v4 < 4; ++v4) {
+              const float4 q = *reinterpret_cast<const float4*>(x2s + c0 + v4 * 4);
+              xp[v4 * 4] = q.x + p2[blk]; xp[v4 * 4 + 1] = q.y + p2[blk]; xp[v4 * 4 + 2] = q.z + p2[blk]; xp[v4 * 4 + 3] = q.w + p2[blk];
+            }
+            // own-class pixels of this prototype among the 16 columns (KLD term), and the valid columns
+            const uint32_t hit = pcl[blk] >= 0 ? ((clsm[pcl[blk] * 4 + (c0 >> 5)] >> (c0 & 31)) & 0xffffu) : 0u;
+            const int nv = npx - c0;
+            const uint32_t vmask = (n < N && nv > 0) ? (nv >= 16 ? 0xffffu : ((1u << nv) - 1u)) : 0u;
             tmem_ld_wait();
+            float gvv[16], sv[16];
+            uint32_t pos = 0u;
+            // out-of-range pixel columns / padding prototypes: dlogits.W is exactly 0 there, only S needs masking
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-              const int px = c0 + i;
-              const int lab = labs[px];
-              const float pre = fmaf(-2.f, __uint_as_float(ra[i]), x2s[px] + p2[blk]);
+              const float pre = fmaf(-2.f, __uint_as_float(ra[i]), xp[i]);
               const float d = fmaxf(pre, 0.f);
-              float s, dsdd;
-              if (p.act_mode == ADLM_ACT_LOG) {
-                const float u = d + 1.f, v = d + p.eps;
-                s = LN2 * (lg2_approx(u) - lg2_approx(v));
-                dsdd = (p.eps - 1.f) * rcp_approx(u * v);
-              } else {
-                s = -d;
-                dsdd = -1.f;
-              }
               float gv = __uint_as_float(rg[i]);
-              const bool okpx = lab != -2 && n < N;
-              if (p.dsim != nullptr && okpx) gv += __ldg(p.dsim + (size_t)(m0 + px) * N + n);
-              gv *= dsdd;
-              if (p.ddist != nullptr && okpx) gv += __ldg(p.ddist + ((size_t)imgs[px] * N + n) * HW + pixs[px]);
-              if (lab == pcl[blk]) gv += __ldg(p.own_grad + (size_t)(m0 + px) * JMAX + prk[blk]);
-              gv = (pre > 0.f && okpx) ? gv : 0.f;
-              s = okpx ? s : 0.f;
+              if (GENERIC) {
+                if (p.dsim != nullptr && ((vmask >> i) & 1u)) gv += __ldg(p.dsim + (size_t)(m0 + c0 + i) * N + n);
+              }
+              if (act_log) {
+                const float u = d + 1.f, v = d + eps;
+                sv[i] = lg2_approx(u) - lg2_approx(v);          // log2 units; ln 2 is folded into the flush
+                gv *= epsm1 * rcp_approx(u * v);
+              } else {
+                sv[i] = -d;
+                gv = -gv;
+              }
+              if (GENERIC) {
+                if (p.ddist != nullptr && ((vmask >> i) & 1u))
+                  gv += __ldg(p.ddist + ((size_t)imgs[c0 + i] * N + n) * HW + pixs[c0 + i]);
+              }
+              pos |= (pre > 0.f ? 1u : 0u) << i;
+              gvv[i] = gv;
+            }
+            if (hit) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i)
+                if ((hit >> i) & 1u) gvv[i] += __ldg(p.own_grad + (size_t)(m0 + c0 + i) * JMAX + prk[blk]);
+            }
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float gv = ((pos >> i) & 1u) ? gvv[i] : 0.f;
               cs[blk] += gv;
               og[i] = __float_as_uint(rna_tf32(gv));
-              os[i] = __float_as_uint(rna_tf32(s));
+              os[i] = __float_as_uint(rna_tf32(((vmask >> i) & 1u) ? sv[i] : 0.f));
             }
             tmem_st16(tD1 + lane_field + c0, og);
             tmem_st16(tGl + lane_field + c0, os);
@@ -481,8 +570,11 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
     // ---- flush this CTA's partial sums ----
     mbar_wait(bar_free, (uint32_t)(iters - 1) & 1u);
     fence_after();
+#pragma unroll
     for (int blk = 0; blk < NB; ++blk) css[(half * 2 + blk) * 128 + lane_n] = cs[blk];
+    if (NB == 1) css[(half * 2 + 1) * 128 + lane_n] = 0.f;
     named_bar_sync(1, 256);
+    const float s_scale = act_log ? LN2 : 1.f;
     float* part = p.partials + (size_t)blockIdx.x * ((size_t)Npad2 * KP + (size_t)Npad2 * 32);
     for (int blk = 0; blk < NB; ++blk) {
       const int n = blk * 128 + lane_n;
@@ -508,7 +600,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
         tmem_ld_wait();
         if (n < N) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i) part[(size_t)Npad2 * KP + (size_t)n * 32 + half * 16 + i] = __uint_as_float(r[i]);
+          for (int i = 0; i < 16; ++i) part[(size_t)Npad2 * KP + (size_t)n * 32 + half * 16 + i] = s_scale * __uint_as_float(r[i]);
         }
       }
     }
@@ -577,8 +669,13 @@ int launch_bwd(TcBwdParams prm, float* dP, float* dW, void* workspace, size_t wo
   if (prm.dz != nullptr) {
     using L = DzSmem<KP>;
     const size_t bytes = L::total(prm.Npad, prm.C8);
-    ADLM_CUDA(cudaFuncSetAttribute(k_tc_bwd_dz<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-    k_tc_bwd_dz<KP><<<grid, 256, bytes, st>>>(prm);
+    if (prm.dsim != nullptr || prm.ddist != nullptr) {
+      ADLM_CUDA(cudaFuncSetAttribute(k_tc_bwd_dz<KP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+      k_tc_bwd_dz<KP, true><<<grid, 256, bytes, st>>>(prm);
+    } else {
+      ADLM_CUDA(cudaFuncSetAttribute(k_tc_bwd_dz<KP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+      k_tc_bwd_dz<KP, false><<<grid, 256, bytes, st>>>(prm);
+    }
     ADLM_LAUNCH_CHECK();
   }
   if (dP != nullptr || dW != nullptr) {
@@ -591,8 +688,15 @@ int launch_bwd(TcBwdParams prm, float* dP, float* dW, void* workspace, size_t wo
     }
     prm.partials = static_cast<float*>(workspace);
     const size_t bytes = L::total(Npad2, prm.C8);
-    ADLM_CUDA(cudaFuncSetAttribute(k_tc_bwd_dp<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-    k_tc_bwd_dp<KP><<<grid, DP_THREADS, bytes, st>>>(prm, NB);
+    const bool generic = prm.dsim != nullptr || prm.ddist != nullptr;
+#define ADLM_DP_LAUNCH(NBV, GEN)                                                                                       \
+  do {                                                                                                                 \
+    ADLM_CUDA(cudaFuncSetAttribute(k_tc_bwd_dp<KP, NBV, GEN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
+    k_tc_bwd_dp<KP, NBV, GEN><<<grid, DP_THREADS, bytes, st>>>(prm);                                                   \
+  } while (0)
+    if (NB == 1) { if (generic) ADLM_DP_LAUNCH(1, true); else ADLM_DP_LAUNCH(1, false); }
+    else         { if (generic) ADLM_DP_LAUNCH(2, true); else ADLM_DP_LAUNCH(2, false); }
+#undef ADLM_DP_LAUNCH
     ADLM_LAUNCH_CHECK();
     const int total = prm.N * prm.K + prm.C * prm.N;
     k_reduce_partials<<<(total * 4 + 255) / 256, 256, 0, st>>>(prm.partials, grid, Npad2, KP, prm.N, prm.K, prm.C, dP, dW);

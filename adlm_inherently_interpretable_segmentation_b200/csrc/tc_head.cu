@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
     for (int idx = tid; idx < Npad * Cpad; idx += NTHREADS) {
       const int n = idx / Cpad, c = idx - n * Cpad;
       const float v = (c < C && n < N) ? __ldg(p.W + (size_t)c * N + n) : 0.f;
-      Wk[(size_t)(n >> 2) * Cpad * 4 + c * 4 + (n & 3)] = rna_tf32(v);
+      Wk[(size_t)(n >> 2) * Cpad * 4 + c * 4 + (n & 3)] = rna_tf32(p.act_mode == ADLM_ACT_LOG ? LN2 * v : v);
     }
   } else {
     // plain fp32 [Npad][32] for the CUDA-core last layer
@@ -122,14 +122,18 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
       Wk[idx] = (c < C && n < N) ? __ldg(p.W + (size_t)c * N + n) : 0.f;
     }
   }
+  __syncthreads();
   for (int n = tid; n < Npad; n += NTHREADS) {
+    // 1xTF32: |p|^2 of the ROUNDED vector (so that z == p gives d == 0); 3xTF32: hi + lo is the fp32 value
     float a = 0.f;
-    if (n < N) {
-      for (int k = 0; k < K; ++k) {
-        const float v = __ldg(p.P + (size_t)n * K + k) - CENTRE;
-        const float u = X3 ? v : rna_tf32(v);   // 1xTF32: |p|^2 of the ROUNDED vector, so that z == p gives d == 0
-        a = fmaf(u, u, a);
+    for (int k4 = 0; k4 < KP / 4; ++k4) {
+      const float4 h4 = *reinterpret_cast<const float4*>(Pk_hi + ((size_t)k4 * Npad + n) * 4);
+      float4 v = h4;
+      if (X3) {
+        const float4 l4 = *reinterpret_cast<const float4*>(Pk_lo + ((size_t)k4 * Npad + n) * 4);
+        v.x += l4.x; v.y += l4.y; v.z += l4.z; v.w += l4.w;
       }
+      a = fmaf(v.x, v.x, a); a = fmaf(v.y, v.y, a); a = fmaf(v.z, v.z, a); a = fmaf(v.w, v.w, a);
     }
     p2s[n] = a;
     pcs[n] = (want_own && n < N) ? p.proto_class[n] : -1;
@@ -237,20 +241,28 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
       for (int c = 0; c < 32; ++c) lacc[X3 ? c : 0] = 0.f;
     }
     const uint32_t t1 = d1 + lane_field;
+    const bool act_log = p.act_mode == ADLM_ACT_LOG;
+    const float eps = p.eps;
     for (int ch = 0; ch < Npad / 16; ++ch) {
       uint32_t r[16];
       tmem_ld16(t1 + ch * 16, r);
+      float xp[16];
+#pragma unroll
+      for (int v4 = 0; v4 < 4; ++v4) {
+        const float4 q = *reinterpret_cast<const float4*>(p2s + ch * 16 + v4 * 4);
+        xp[v4 * 4] = x2 + q.x; xp[v4 * 4 + 1] = x2 + q.y; xp[v4 * 4 + 2] = x2 + q.z; xp[v4 * 4 + 3] = x2 + q.w;
+      }
       tmem_ld_wait();
       float dv[16];
       uint32_t sv_bits[16];
       float sv[16];
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
-        const int n = ch * 16 + i;
-        const float d = fmaxf(fmaf(-2.f, __uint_as_float(r[i]), x2 + p2s[n]), 0.f);
+        const float d = fmaxf(fmaf(-2.f, __uint_as_float(r[i]), xp[i]), 0.f);
         dv[i] = d;
         float s;
-        if (p.act_mode == ADLM_ACT_LOG) s = X3 ? logf((d + 1.f) / (d + p.eps)) : LN2 * (__log2f(d + 1.f) - __log2f(d + p.eps));
+        // 1xTF32: similarity in log2 units (ln 2 is folded into the last-layer operand Wk)
+        if (act_log) s = X3 ? logf((d + 1.f) / (d + eps)) : lg2_approx(d + 1.f) - lg2_approx(d + eps);
         else s = -d;
         sv[i] = s;
         sv_bits[i] = __float_as_uint(rna_tf32(s));
@@ -283,7 +295,7 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
           float* dst = p.sim + (size_t)m * N + ch * 16;
 #pragma unroll
           for (int i = 0; i < 16; ++i)
-            if (i < nmax) dst[i] = sv[i];
+            if (i < nmax) dst[i] = (!X3 && act_log) ? LN2 * sv[i] : sv[i];
         }
         if (lab_ok && ((cmask[ch] >> lab) & 1u)) {
 #pragma unroll
