@@ -42,7 +42,7 @@ static int check_shape(const char* fn, int B, int K, int HW, int N, int C) {
   }
   if (K > ADLM_MAX_K) { set_error("%s: unsupported: K=%d > %d", fn, K, ADLM_MAX_K); return ADLM_E_UNSUPPORTED; }
   if (C > ADLM_MAX_C) { set_error("%s: unsupported: C=%d > %d", fn, C, ADLM_MAX_C); return ADLM_E_UNSUPPORTED; }
-  if ((long long)B * HW >= (1ll << 31)) { set_error("%s: unsupported: B*HW >= 2^31", fn); return ADLM_E_UNSUPPORTED; }
+  if ((long long)B * HW >= (1ll << 31) - 256) { set_error("%s: unsupported: B*HW >= 2^31 - 256", fn); return ADLM_E_UNSUPPORTED; }
   return ADLM_OK;
 }
 

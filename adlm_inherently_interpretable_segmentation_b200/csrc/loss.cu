@@ -12,6 +12,8 @@
 //   kl_div(la_i, la_j, log_target) = sum q_j (la_j - la_i)  =>  kld_ij = (E_j[d_j-d_i] - E_i[d_j-d_i]) / 2
 // so one J x J matrix A[a][b] = E_a[d_b] per group gives every pair.  Gradient wrt d_a(m):
 //   sum_b c_ab * ( q_a ((d_a - d_b) - (A[a][a] - A[a][b])) + q_a - q_b ),  c_ab = -(w/T) exp(-kld_ab) / 2.
+#include <atomic>
+
 #include "common.cuh"
 
 namespace adlm {
@@ -117,18 +119,20 @@ __global__ void k_ce(const float* __restrict__ logits, const int32_t* __restrict
 }
 
 // One CTA per (label l = blockIdx.x, image b = blockIdx.y): the group's pixels are first compacted into a
-// shared-memory index list (a group is ~1/C of the image, so scanning with divergent lanes would waste ~C x
-// the work), then: per-prototype max, the J x J matrix A[a][b] = E_a[d_b], the pair terms, and — same CTA,
-// which owns exactly these pixels — dL/d(own distances) for the backward kernels.
+// shared-memory index list (a group is ~1/C of the image), then: per-prototype max, the J x J matrix
+// A[a][b] = E_a[d_b], the pair terms, and — same CTA, which owns exactly these pixels — dL/d(own distances)
+// for the backward kernels.  Thread = (pixel lane tid/16, prototype-in-class tid%16): ~50 registers, so all
+// B*C CTAs are resident at once.
 __global__ void __launch_bounds__(256)
 k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const int* __restrict__ hist,
       const int* __restrict__ cls_count, const int* __restrict__ counts, int HW, int C,
       float coef /* w_kld * grad_scale */, float* __restrict__ own_grad, double* __restrict__ accum) {
+  static_assert(JMAX == 16, "thread layout assumes 16 prototypes per class at most");
   extern __shared__ int s_list[];                 // [cnt] pixel indices of this group
   const int l = blockIdx.x, b = blockIdx.y;
   const int J = min(cls_count[l], JMAX);
   const int cnt = hist[b * (C + 1) + l];
-  const int tid = threadIdx.x, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31, j = tid & 15, pl = tid >> 4;
   if (cnt == 0) return;
   __shared__ int s_n;
   __shared__ float s_mx[JMAX], s_S[JMAX], s_lse[JMAX], s_cs[JMAX], s_r[JMAX];
@@ -139,48 +143,39 @@ k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const i
   const float* ob = own + (size_t)b * HW * JMAX;
   if (tid == 0) s_n = 0;
   __syncthreads();
-  for (int p0 = 0; p0 < HW; p0 += 256) {
-    const int p = p0 + tid;
-    const bool hit = p < HW && t[p] == l;
-    const unsigned bal = __ballot_sync(0xffffffffu, hit);
-    int base = 0;
-    if (lane == 0 && bal) base = atomicAdd(&s_n, __popc(bal));
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (hit) s_list[base + __popc(bal & ((1u << lane) - 1u))] = p;
+  for (int p0 = 0; p0 < HW; p0 += 1024) {
+    // four label loads in flight per thread; order inside the list is irrelevant
+    int pp[4];
+    bool hit[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      pp[u] = p0 + u * 256 + tid;
+      hit[u] = pp[u] < HW && t[pp[u]] == l;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const unsigned bal = __ballot_sync(0xffffffffu, hit[u]);
+      int base = 0;
+      if (lane == 0 && bal) base = atomicAdd(&s_n, __popc(bal));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (hit[u]) s_list[base + __popc(bal & ((1u << lane) - 1u))] = pp[u];
+    }
   }
   __syncthreads();
   const int n = s_n;                              // == cnt
   const bool valid_group = J >= 2 && n >= 2;
-  float4* og = own_grad ? reinterpret_cast<float4*>(own_grad + (size_t)b * HW * JMAX) : nullptr;
+  float* og = own_grad ? own_grad + (size_t)b * HW * JMAX : nullptr;
   if (!valid_group) {
     if (og)
-      for (int i = tid; i < n; i += 256) {
-        float4* o = og + (size_t)s_list[i] * (JMAX / 4);
-#pragma unroll
-        for (int v = 0; v < JMAX / 4; ++v) o[v] = make_float4(0.f, 0.f, 0.f, 0.f);
-      }
+      for (int i = pl; i < n; i += 16) og[(size_t)s_list[i] * JMAX + j] = 0.f;
     return;
   }
-  // pass A: per-prototype max
-  float mx[JMAX];
-#pragma unroll
-  for (int j = 0; j < JMAX; ++j) mx[j] = -INFINITY;
-  for (int i = tid; i < n; i += 256) {
-    const float4* o4 = reinterpret_cast<const float4*>(ob + (size_t)s_list[i] * JMAX);
-#pragma unroll
-    for (int v = 0; v < JMAX / 4; ++v) {
-      const float4 x = o4[v];
-      mx[4 * v] = fmaxf(mx[4 * v], x.x); mx[4 * v + 1] = fmaxf(mx[4 * v + 1], x.y);
-      mx[4 * v + 2] = fmaxf(mx[4 * v + 2], x.z); mx[4 * v + 3] = fmaxf(mx[4 * v + 3], x.w);
-    }
-  }
-#pragma unroll
-  for (int j = 0; j < JMAX; ++j) mx[j] = warp_max(mx[j]);
-  if (lane == 0) {
-#pragma unroll
-    for (int j = 0; j < JMAX; ++j) s_red[tid >> 5][j] = mx[j];
-  }
-  (&s_T[0][0])[tid] = 0.f;                        // 256 threads == JMAX*JMAX
+  // pass A: per-prototype max over the group's pixels
+  float mx = -INFINITY;
+  for (int i = pl; i < n; i += 16) mx = fmaxf(mx, ob[(size_t)s_list[i] * JMAX + j]);
+  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+  if (lane < 16) s_red[tid >> 5][j] = mx;
+  s_T[pl][j] = 0.f;                               // 256 threads == JMAX*JMAX
   if (tid < JMAX) s_S[tid] = 0.f;
   __syncthreads();
   if (tid < JMAX) {
@@ -189,55 +184,40 @@ k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const i
     s_mx[tid] = m;
   }
   __syncthreads();
-  // pass B: S_j = sum exp(d_j - mx_j), T[j][i] = sum exp(d_j - mx_j) d_i; thread = (pixel lane, quarter of i)
-  const int lane64 = tid & 63, q = tid >> 6;
-  float S[JMAX];
-  float T[JMAX][JMAX / 4];
+  // pass B: S_j = sum exp(d_j - mx_j), T[j][c] = sum exp(d_j - mx_j) d_c
+  {
+    const float mxj = s_mx[j];
+    float S = 0.f, T[JMAX];
 #pragma unroll
-  for (int j = 0; j < JMAX; ++j) {
-    S[j] = 0.f;
+    for (int c = 0; c < JMAX; ++c) T[c] = 0.f;
+    for (int i = pl; i < n; i += 16) {
+      const float* row = ob + (size_t)s_list[i] * JMAX;
+      const float dj = row[j];
+      const float4* o4 = reinterpret_cast<const float4*>(row);
+      float d[JMAX];
 #pragma unroll
-    for (int i = 0; i < JMAX / 4; ++i) T[j][i] = 0.f;
-  }
-  static_assert(JMAX / 4 == 4, "quarter layout assumes JMAX == 16");
-  for (int it = lane64; it < n; it += 64) {
-    const float4* o4 = reinterpret_cast<const float4*>(ob + (size_t)s_list[it] * JMAX);
-    float d[JMAX];
-#pragma unroll
-    for (int v = 0; v < JMAX / 4; ++v) {
-      const float4 x = o4[v];
-      d[4 * v] = x.x; d[4 * v + 1] = x.y; d[4 * v + 2] = x.z; d[4 * v + 3] = x.w;
-    }
-    const float4 dq4 = o4[q];
-    const float dq[4] = {dq4.x, dq4.y, dq4.z, dq4.w};
-#pragma unroll
-    for (int j = 0; j < JMAX; ++j) {
-      if (j < J) {
-        const float e = __expf(d[j] - s_mx[j]);
-        S[j] += e;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) T[j][i] = fmaf(e, dq[i], T[j][i]);
+      for (int v = 0; v < JMAX / 4; ++v) {
+        const float4 x = o4[v];
+        d[4 * v] = x.x; d[4 * v + 1] = x.y; d[4 * v + 2] = x.z; d[4 * v + 3] = x.w;
       }
+      const float e = (j < J) ? __expf(dj - mxj) : 0.f;
+      S += e;
+#pragma unroll
+      for (int c = 0; c < JMAX; ++c) T[c] = fmaf(e, d[c], T[c]);
     }
-  }
+    S += __shfl_xor_sync(0xffffffffu, S, 16);
 #pragma unroll
-  for (int j = 0; j < JMAX; ++j) {
-    S[j] = warp_sum(S[j]);
+    for (int c = 0; c < JMAX; ++c) T[c] += __shfl_xor_sync(0xffffffffu, T[c], 16);
+    if (lane < 16 && j < J) {
+      atomicAdd(&s_S[j], S);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) T[j][i] = warp_sum(T[j][i]);
-  }
-  if (lane == 0) {
-#pragma unroll
-    for (int j = 0; j < JMAX; ++j) {
-      if (q == 0) atomicAdd(&s_S[j], S[j]);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) atomicAdd(&s_T[j][q * 4 + i], T[j][i]);
+      for (int c = 0; c < JMAX; ++c) atomicAdd(&s_T[j][c], T[c]);
     }
   }
   __syncthreads();
   {
-    const int j = tid / JMAX, i = tid % JMAX;
-    if (j < J && i < J) s_T[j][i] = s_T[j][i] / s_S[j];     // A[j][i] = E_j[d_i]
+    const int a = tid / JMAX, i = tid % JMAX;
+    if (a < J && i < J) s_T[a][i] = s_T[a][i] / s_S[a];     // A[a][i] = E_a[d_i]
   }
   __syncthreads();
   const float n_terms = (float)counts[1];
@@ -271,58 +251,71 @@ k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const i
   }
   __syncthreads();
   if (og == nullptr) return;
-  // gradient wrt the own-class distances of every pixel of the group
-  for (int it = tid; it < n; it += 256) {
-    const int p = s_list[it];
-    const float4* o4 = reinterpret_cast<const float4*>(ob + (size_t)p * JMAX);
-    float d[JMAX], qv[JMAX], g[JMAX];
+  // gradient wrt the own-class distances: thread a of a 16-lane group owns d_a of the pixel; the sums over
+  // the other prototypes of the class run over shuffles inside the group
+  {
+    float kl[JMAX];
 #pragma unroll
-    for (int v = 0; v < JMAX / 4; ++v) {
-      const float4 x = o4[v];
-      d[4 * v] = x.x; d[4 * v + 1] = x.y; d[4 * v + 2] = x.z; d[4 * v + 3] = x.w;
-    }
+    for (int c = 0; c < JMAX; ++c) kl[c] = s_kl[j][c];   // zero for c >= J, c == a, a >= J
+    const float csa = s_cs[j], ra = s_r[j], lsea = s_lse[j];
+    for (int i0 = 0; i0 < n; i0 += 16) {
+      const int i = i0 + pl;
+      const bool act = i < n;
+      const int pidx = s_list[act ? i : 0];
+      const float da = ob[(size_t)pidx * JMAX + j];
+      const float qa = (j < J) ? __expf(da - lsea) : 0.f;
+      float cd = 0.f, cq = 0.f;
 #pragma unroll
-    for (int a = 0; a < JMAX; ++a) qv[a] = (a < J) ? __expf(d[a] - s_lse[a]) : 0.f;
-#pragma unroll
-    for (int a = 0; a < JMAX; ++a) {
-      float ga = 0.f;
-      if (a < J) {
-        float cd = 0.f, cq = 0.f;
-#pragma unroll
-        for (int c = 0; c < JMAX; ++c) {
-          if (c < J) {
-            const float cc = s_kl[a][c];
-            cd = fmaf(cc, d[c], cd);
-            cq = fmaf(cc, qv[c], cq);
-          }
-        }
-        ga = qv[a] * (d[a] * s_cs[a] - cd - s_r[a]) + qv[a] * s_cs[a] - cq;
+      for (int c = 0; c < JMAX; ++c) {
+        const float dc = __shfl_sync(0xffffffffu, da, c, 16);
+        const float qc = __shfl_sync(0xffffffffu, qa, c, 16);
+        cd = fmaf(kl[c], dc, cd);
+        cq = fmaf(kl[c], qc, cq);
       }
-      g[a] = ga;
+      const float ga = qa * (da * csa - cd - ra) + qa * csa - cq;
+      if (act) og[(size_t)pidx * JMAX + j] = ga;
     }
-    float4* o = og + (size_t)p * (JMAX / 4);
-#pragma unroll
-    for (int v = 0; v < JMAX / 4; ++v) o[v] = make_float4(g[4 * v], g[4 * v + 1], g[4 * v + 2], g[4 * v + 3]);
   }
 }
-// Single-CTA prologue of the step (small batches): label histogram per image, class sizes, the two loss
-// normalisers, prototype ranks, cleared accumulators — one launch instead of a memset and three kernels.
+
+// Prologue of the step in one launch: one CTA per image builds that image's label histogram in shared memory
+// and stores it; the last CTA to finish (ticket) derives the class sizes, the two loss normalisers and the
+// prototype ranks and clears the accumulators.  The ticket counters live in a small device array (zero at
+// module load, reset by the last CTA); the host rotates through the slots so that steps in flight on
+// different streams never share one.
+constexpr int TICKET_SLOTS = 64;
+__device__ unsigned int g_prepare_ticket[TICKET_SLOTS];
+
 __global__ void __launch_bounds__(1024)
 k_step_prepare(const int32_t* __restrict__ target, const int32_t* __restrict__ proto_class, int B, int HW, int C,
-               int N, int ignore_void, int* __restrict__ hist, int* __restrict__ cls_count,
+               int N, int ignore_void, int slot, int* __restrict__ hist, int* __restrict__ cls_count,
                int* __restrict__ counts, int32_t* __restrict__ rank, double* __restrict__ accum) {
-  extern __shared__ int sh[];                       // [B][C+1] histogram, then [C] class sizes
-  int* s_cls = sh + B * (C + 1);
-  __shared__ int s_valid, s_terms;
-  const int tid = threadIdx.x;
-  for (int i = tid; i < B * (C + 1) + C; i += 1024) sh[i] = 0;
+  __shared__ int sh[ADLM_MAX_C + 1];
+  __shared__ int s_cls[ADLM_MAX_C];
+  __shared__ int s_valid, s_terms, s_last;
+  const int tid = threadIdx.x, b = blockIdx.x;
+  for (int i = tid; i <= C; i += 1024) sh[i] = 0;
+  __syncthreads();
+  const int32_t* t = target + (size_t)b * HW;
+  for (int p = tid; p < HW; p += 1024) {
+    const int l = t[p];
+    if (l >= 0 && l <= C) atomicAdd(&sh[l], 1);
+  }
+  __syncthreads();
+  for (int i = tid; i <= C; i += 1024) hist[b * (C + 1) + i] = sh[i];
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned int prev = atomicAdd(&g_prepare_ticket[slot], 1u);
+    s_last = (prev == (unsigned int)(B - 1));
+    if (s_last) g_prepare_ticket[slot] = 0u;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  for (int c = tid; c < C; c += 1024) s_cls[c] = 0;
   if (tid == 0) { s_valid = 0; s_terms = 0; }
   __syncthreads();
-  const long long M = (long long)B * HW;
-  for (long long m = tid; m < M; m += 1024) {
-    const int l = target[m];
-    if (l >= 0 && l <= C) atomicAdd(&sh[(int)(m / HW) * (C + 1) + l], 1);
-  }
   for (int n = tid; n < N; n += 1024) {
     const int c = proto_class[n];
     if (c >= 0 && c < C) atomicAdd(&s_cls[c], 1);
@@ -332,9 +325,9 @@ k_step_prepare(const int32_t* __restrict__ target, const int32_t* __restrict__ p
   }
   __syncthreads();
   int valid = 0, terms = 0;
+  const volatile int* vh = hist;
   for (int i = tid; i < B * (C + 1); i += 1024) {
-    const int l = i % (C + 1), cnt = sh[i];
-    hist[i] = cnt;
+    const int l = i % (C + 1), cnt = vh[i];
     if (ignore_void) { if (l >= 1) valid += cnt; }
     else             { if (l < C) valid += cnt; }
     if (l < C && cnt >= 2 && s_cls[l] >= 2) terms += s_cls[l] * (s_cls[l] - 1) / 2;
@@ -380,16 +373,6 @@ __global__ void k_finalize(const float* __restrict__ W, const int32_t* __restric
     scalars[5] = n_valid;
     scalars[6] = n_terms;
     scalars[7] = 0.0;
-  }
-}
-
-__global__ void k_proto_rank(const int32_t* __restrict__ proto_class, int N, int32_t* __restrict__ rank) {
-  // rank of prototype n among the prototypes of its class (N is small; quadratic scan is fine)
-  for (int n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x) {
-    const int c = proto_class[n];
-    int r = 0;
-    for (int i = 0; i < n; ++i) r += (proto_class[i] == c);
-    rank[n] = r;
   }
 }
 
@@ -448,19 +431,11 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
   const bool want_grad = (dz != nullptr) || (dP != nullptr) || (dW != nullptr);
   float* logits = logits_out ? logits_out : ws.logits;
 
-  const size_t prep_smem = sizeof(int) * ((size_t)B * (C + 1) + C);
-  if (prep_smem <= 48 * 1024 && M <= (1ll << 21)) {
-    k_step_prepare<<<1, 1024, prep_smem, st>>>(target, proto_class, B, HW, C, N, ignore_void, ws.hist, ws.cls_count,
-                                               ws.counts, ws.rank, ws.accum);
-    ADLM_LAUNCH_CHECK();
-  } else {
-    ADLM_CUDA(cudaMemsetAsync(ws.hist, 0, sizeof(int) * (size_t)B * (C + 1), st));
-    dim3 grid(min(cdiv(HW, 256), 64), B);
-    k_label_hist<<<grid, 256, sizeof(int) * (C + 1), st>>>(target, HW, C, ws.hist);
-    ADLM_LAUNCH_CHECK();
-    k_loss_prepare<<<1, 256, 0, st>>>(ws.hist, proto_class, B, C, N, ignore_void, ws.cls_count, ws.counts, ws.accum);
-    ADLM_LAUNCH_CHECK();
-    k_proto_rank<<<cdiv(N, 128), 128, 0, st>>>(proto_class, N, ws.rank);
+  {
+    static std::atomic<unsigned int> next_slot{0};
+    const int slot = (int)(next_slot.fetch_add(1u, std::memory_order_relaxed) % TICKET_SLOTS);
+    k_step_prepare<<<B, 1024, 0, st>>>(target, proto_class, B, HW, C, N, ignore_void, slot, ws.hist, ws.cls_count,
+                                       ws.counts, ws.rank, ws.accum);
     ADLM_LAUNCH_CHECK();
   }
   const int* counts = global_counts ? global_counts : ws.counts;

@@ -91,21 +91,63 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
     for (int i = 0; i < 4; ++i) mbar_init(smem_u32(&bars[i]), 1);
     mbar_init_fence();
   }
-  for (int idx = tid; idx < (KP / 4) * Npad; idx += 256) {
-    const int n = idx % Npad, k4 = idx / Npad;
-    float v[4];
+  // features of the first tile travel while the operands are staged
+  const int Mi = (int)p.M;
+  const int stride = (int)gridDim.x * 2;
+  int tile = (int)blockIdx.x + wg * (int)gridDim.x;
+  float zr[KP];
+  auto prefetch = [&](int t) {
+    const int m = t * TILE + wt;
+    if (t < p.num_tiles && m < Mi) {
+      const int b = m / HW;
+      const float* src = p.z + ((size_t)b * K) * HW + (m - b * HW);
+      if (K == KP) {
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int k = k4 * 4 + j;
-      v[j] = rna_tf32((n < N && k < K) ? __ldg(p.P + (size_t)n * K + k) - CENTRE : 0.f);
-      Pt[(size_t)(n >> 2) * KP * 4 + k * 4 + (n & 3)] = v[j];      // rows k, K index n
+        for (int k = 0; k < KP; ++k) { zr[k] = __ldg(src); src += HW; }
+      } else {
+#pragma unroll
+        for (int k = 0; k < KP; ++k) zr[k] = (k < K) ? __ldg(src + (size_t)k * HW) : CENTRE;
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < KP; ++k) zr[k] = CENTRE;
     }
-    *reinterpret_cast<float4*>(Pk + (size_t)idx * 4) = make_float4(v[0], v[1], v[2], v[3]);
-  }
+  };
+  prefetch(tile);
+
+  stage_rows_kmajor<KP, false>(Pk, Pk, p.P, N, K, Npad, CENTRE, tid, 256);
+  // Wt: rows = prototypes, K index = class: [C8/4][Npad][4]; padding first, then W [C][N] streamed coalesced
   for (int idx = tid; idx < C8 * Npad; idx += 256) {
     const int c = idx / Npad, n = idx - c * Npad;
-    const float v = (c < C && n < N && p.dlogits != nullptr) ? __ldg(p.W + (size_t)c * N + n) : 0.f;
-    Wt[(size_t)(c >> 2) * Npad * 4 + n * 4 + (c & 3)] = rna_tf32(v);   // rows n, K index c
+    if (!(c < C && n < N && p.dlogits != nullptr)) Wt[(size_t)(c >> 2) * Npad * 4 + n * 4 + (c & 3)] = 0.f;
+  }
+  if (p.dlogits != nullptr) {
+    const int CN = C * N;
+    for (int i0 = 0; i0 < CN; i0 += 256 * 4) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int idx = i0 + u * 256 + tid;
+        v[u] = idx < CN ? __ldg(p.W + idx) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int idx = i0 + u * 256 + tid;
+        if (idx < CN) {
+          const int c = idx / N, n = idx - c * N;
+          Wt[(size_t)(c >> 2) * Npad * 4 + n * 4 + (c & 3)] = rna_tf32_mask(v[u]);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  // Pt: the same rounded prototypes transposed (rows k, K index n): [Npad/4][KP][4], built from Pk
+  for (int idx = tid; idx < (Npad / 4) * KP; idx += 256) {
+    const int k = idx % KP, n4 = idx / KP;
+    float v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = Pk[((size_t)(k >> 2) * Npad + n4 * 4 + j) * 4 + (k & 3)];
+    *reinterpret_cast<float4*>(Pt + (size_t)idx * 4) = make_float4(v[0], v[1], v[2], v[3]);
   }
   __syncthreads();
   for (int n = tid; n < Npad; n += 256) {
@@ -143,29 +185,15 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
   const uint32_t idesc_h = make_idesc_tf32(TILE, NH), idesc_z = make_idesc_tf32(TILE, KP);
   const int ksteps = (K + 7) >> 3;
 
-  const long long stride = (long long)gridDim.x * 2;
-  long long tile = (long long)blockIdx.x + (long long)wg * gridDim.x;
   uint32_t ph_a = 0, ph_z = 0;
   const float eps = p.eps, epsm1 = p.eps - 1.f;
   const bool act_log = p.act_mode == ADLM_ACT_LOG;
 
-  // features of the next tile travel while this one is processed
-  float zr[KP];
-  auto prefetch = [&](long long t) {
-    const long long m = t * TILE + wt;
-    const bool ok = t < p.num_tiles && m < p.M;
-    const int b = ok ? (int)(m / HW) : 0;
-    const float* src = p.z + ((size_t)b * K) * HW + (ok ? (m - (long long)b * HW) : 0);
-#pragma unroll
-    for (int k = 0; k < KP; ++k) zr[k] = (ok && k < K) ? __ldg(src + (size_t)k * HW) : CENTRE;
-  };
-  prefetch(tile);
-
   for (; tile < p.num_tiles; tile += stride) {
-    const long long m = tile * TILE + wt;
-    const bool valid = m < p.M;
-    const int b = valid ? (int)(m / HW) : 0;
-    const int pix = valid ? (int)(m - (long long)b * HW) : 0;
+    const int m = tile * TILE + wt;
+    const bool valid = m < Mi;
+    const int b = valid ? m / HW : 0;
+    const int pix = valid ? m - b * HW : 0;
 
     // ---- operands of this tile: Zk (centred, rounded), dLk ----
     float x2 = 0.f;
@@ -174,7 +202,7 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
       float v[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        v[j] = rna_tf32(zr[k4 * 4 + j] - CENTRE);
+        v[j] = rna_tf32_mask(zr[k4 * 4 + j] - CENTRE);
         x2 = fmaf(v[j], v[j], x2);
       }
       *reinterpret_cast<float4*>(Zk + ((size_t)k4 * TILE + wt) * 4) = make_float4(v[0], v[1], v[2], v[3]);
@@ -184,7 +212,7 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int c = c4 * 4 + j;
-        v[j] = (valid && c < C && p.dlogits != nullptr) ? rna_tf32(__ldg(p.dlogits + (size_t)m * C + c)) : 0.f;
+        v[j] = (valid && c < C && p.dlogits != nullptr) ? rna_tf32_fast(__ldg(p.dlogits + (size_t)m * C + c)) : 0.f;
       }
       *reinterpret_cast<float4*>(dLk + ((size_t)c4 * TILE + wt) * 4) = make_float4(v[0], v[1], v[2], v[3]);
     }
@@ -254,7 +282,7 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
         for (int i = 0; i < 16; ++i) {
           const float gv = ((pos >> i) & 1u) ? g[i] : 0.f;
           rs += gv;
-          out[i] = __float_as_uint(rna_tf32(gv));
+          out[i] = __float_as_uint(rna_tf32_fast(gv));
         }
         tmem_st16(tD + lane_field + ch * 16, out);
       }
@@ -353,20 +381,29 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
     mbar_init(smem_u32(&bars[3]), 1);     // free: every MMA of the tile done
     mbar_init_fence();
   }
-  for (int idx = tid; idx < (KP / 4) * Npad2; idx += DP_THREADS) {
-    const int n = idx % Npad2, k4 = idx / Npad2;
-    float v[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int k = k4 * 4 + j;
-      v[j] = rna_tf32((n < N && k < K) ? __ldg(p.P + (size_t)n * K + k) - CENTRE : 0.f);
-    }
-    *reinterpret_cast<float4*>(PkA + (size_t)idx * 4) = make_float4(v[0], v[1], v[2], v[3]);
-  }
+  stage_rows_kmajor<KP, false>(PkA, PkA, p.P, N, K, Npad2, CENTRE, tid, DP_THREADS);
   for (int idx = tid; idx < C8 * Npad2; idx += DP_THREADS) {
     const int c = idx / Npad2, n = idx - c * Npad2;
-    const float v = (c < C && n < N && has_dl) ? __ldg(p.W + (size_t)c * N + n) : 0.f;
-    WtA[(size_t)(c >> 2) * Npad2 * 4 + n * 4 + (c & 3)] = rna_tf32(v);
+    if (!(c < C && n < N && has_dl)) WtA[(size_t)(c >> 2) * Npad2 * 4 + n * 4 + (c & 3)] = 0.f;
+  }
+  if (has_dl) {
+    const int CN = C * N;
+    for (int i0 = 0; i0 < CN; i0 += DP_THREADS * 4) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int idx = i0 + u * DP_THREADS + tid;
+        v[u] = idx < CN ? __ldg(p.W + idx) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int idx = i0 + u * DP_THREADS + tid;
+        if (idx < CN) {
+          const int c = idx / N, n = idx - c * N;
+          WtA[(size_t)(c >> 2) * Npad2 * 4 + n * 4 + (c & 3)] = rna_tf32_mask(v[u]);
+        }
+      }
+    }
   }
   for (int idx = tid; idx < 32 * TILE; idx += DP_THREADS) dLtB[idx] = 0.f;
   fence_async_smem();
@@ -385,20 +422,33 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
     const int cw = tid - 256;
     float zr[KP];
     float dlr[32];
+    const int Mi = (int)p.M;
     auto prefetch = [&](int it) {
-      const long long m = ((long long)blockIdx.x + (long long)it * gridDim.x) * TILE + cw;
-      const bool ok = it < iters && m < p.M;
-      const int b = ok ? (int)(m / HW) : 0;
-      const float* src = p.z + ((size_t)b * K) * HW + (ok ? (m - (long long)b * HW) : 0);
+      const int m = ((int)blockIdx.x + it * (int)gridDim.x) * TILE + cw;
+      if (it < iters && m < Mi) {
+        const int b = m / HW;
+        const float* src = p.z + ((size_t)b * K) * HW + (m - b * HW);
+        if (K == KP) {
 #pragma unroll
-      for (int k = 0; k < KP; ++k) zr[k] = (ok && k < K) ? __ldg(src + (size_t)k * HW) : CENTRE;
+          for (int k = 0; k < KP; ++k) { zr[k] = __ldg(src); src += HW; }
+        } else {
 #pragma unroll
-      for (int c = 0; c < 32; ++c) dlr[c] = (ok && has_dl && c < C) ? __ldg(p.dlogits + (size_t)m * C + c) : 0.f;
+          for (int k = 0; k < KP; ++k) zr[k] = (k < K) ? __ldg(src + (size_t)k * HW) : CENTRE;
+        }
+        const float* dl = p.dlogits + (size_t)m * C;
+#pragma unroll
+        for (int c = 0; c < 32; ++c) dlr[c] = (has_dl && c < C) ? __ldg(dl + c) : 0.f;
+      } else {
+#pragma unroll
+        for (int k = 0; k < KP; ++k) zr[k] = CENTRE;
+#pragma unroll
+        for (int c = 0; c < 32; ++c) dlr[c] = 0.f;
+      }
     };
     prefetch(0);
     for (int it = 0; it < iters; ++it) {
-      const long long m = ((long long)blockIdx.x + (long long)it * gridDim.x) * TILE + cw;
-      const bool valid = m < p.M;
+      const int m = ((int)blockIdx.x + it * (int)gridDim.x) * TILE + cw;
+      const bool valid = m < Mi;
       if (it > 0) mbar_wait(bar_free, (uint32_t)(it - 1) & 1u);
       clsm[cw] = 0u;
       named_bar_sync(2, 128);
@@ -410,7 +460,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
         float v[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          v[j] = rna_tf32(zr[k4 * 4 + j] - CENTRE);
+          v[j] = rna_tf32_mask(zr[k4 * 4 + j] - CENTRE);
           x2 = fmaf(v[j], v[j], x2);
           ZtB[off_sw128(k4 * 4 + j, cw, KP)] = v[j];
         }
@@ -422,16 +472,16 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
           float v[4];
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            v[j] = rna_tf32(dlr[c4 * 4 + j]);
+            v[j] = rna_tf32_fast(dlr[c4 * 4 + j]);
             if (c4 * 4 + j < C) dLtB[off_sw128(c4 * 4 + j, cw, 32)] = v[j];
           }
           *reinterpret_cast<float4*>(dLkB + ((size_t)c4 * TILE + cw) * 4) = make_float4(v[0], v[1], v[2], v[3]);
         }
       }
       x2s[cw] = x2;
-      const int b = valid ? (int)(m / HW) : 0;
+      const int b = valid ? m / HW : 0;
       imgs[cw] = b;
-      pixs[cw] = valid ? (int)(m - (long long)b * HW) : 0;
+      pixs[cw] = valid ? m - b * HW : 0;
       labs[cw] = valid ? mylab : -2;
       fence_async_smem();
       mbar_arrive(bar_full);
@@ -555,8 +605,8 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
             for (int i = 0; i < 16; ++i) {
               const float gv = ((pos >> i) & 1u) ? gvv[i] : 0.f;
               cs[blk] += gv;
-              og[i] = __float_as_uint(rna_tf32(gv));
-              os[i] = __float_as_uint(rna_tf32(((vmask >> i) & 1u) ? sv[i] : 0.f));
+              og[i] = __float_as_uint(rna_tf32_fast(gv));
+              os[i] = __float_as_uint(rna_tf32_fast(((vmask >> i) & 1u) ? sv[i] : 0.f));
             }
             tmem_st16(tD1 + lane_field + c0, og);
             tmem_st16(tGl + lane_field + c0, os);

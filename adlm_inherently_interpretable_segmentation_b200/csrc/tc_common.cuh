@@ -115,6 +115,10 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+__device__ __forceinline__ void named_bar_arrive(int id, int nthreads) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
 __device__ __forceinline__ float lg2_approx(float x) {
   float r;
   asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
@@ -134,6 +138,74 @@ __device__ __forceinline__ float rna_tf32(float x) {
   uint32_t r;
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
   return __uint_as_float(r);
+}
+
+// Same rounding in one integer add: magnitude + half an ulp(tf32).  The 13 low bits stay in place — the tensor
+// core ignores them — so this form is for MMA operands whose exact rounded value is not needed elsewhere
+// (similarities, gradients).  Finite inputs only.
+__device__ __forceinline__ float rna_tf32_fast(float x) { return __uint_as_float(__float_as_uint(x) + 0x1000u); }
+// ... and with the low bits cleared (two instructions instead of cvt.rna's four): operands whose rounded
+// value also enters fp32 arithmetic (|z|^2, |p|^2, the lo part of a 3xTF32 split)
+__device__ __forceinline__ float rna_tf32_mask(float x) {
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+}
+
+// Stage a row-major [rows_valid x K] fp32 matrix (prototypes) as a canonical K-major operand
+// [KP/4][rows_pad][4]: value = rna(x - centre) (hi) and, for 3xTF32, lo = rna((x - centre) - hi).
+// Rows >= rows_valid and columns >= K are zero.  Fast path (K == KP, 16-byte aligned base): every thread
+// streams float4s of the flat array — fully coalesced, four loads in flight per thread.
+template <int KP, bool X3>
+__device__ __forceinline__ void stage_rows_kmajor(float* __restrict__ hi, float* __restrict__ lo,
+                                                  const float* __restrict__ src, int rows_valid, int K,
+                                                  int rows_pad, float centre, int tid, int nthreads) {
+  constexpr int Q = KP / 4;
+  const int total = rows_pad * Q;
+  if (K == KP && (reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
+    const float4* src4 = reinterpret_cast<const float4*>(src);
+    for (int f0 = 0; f0 < total; f0 += nthreads * 4) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int f = f0 + u * nthreads + tid;
+        v[u] = (f < rows_valid * Q) ? __ldg(src4 + f) : make_float4(centre, centre, centre, centre);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int f = f0 + u * nthreads + tid;
+        if (f < total) {
+          const int n = f / Q, k4 = f - n * Q;
+          const float x[4] = {v[u].x - centre, v[u].y - centre, v[u].z - centre, v[u].w - centre};
+          float h[4], l[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            h[j] = rna_tf32_mask(x[j]);
+            l[j] = X3 ? rna_tf32_mask(x[j] - h[j]) : 0.f;
+          }
+          *reinterpret_cast<float4*>(hi + ((size_t)k4 * rows_pad + n) * 4) = make_float4(h[0], h[1], h[2], h[3]);
+          if (X3) *reinterpret_cast<float4*>(lo + ((size_t)k4 * rows_pad + n) * 4) = make_float4(l[0], l[1], l[2], l[3]);
+        }
+      }
+    }
+  } else {
+    for (int idx = tid; idx < total; idx += nthreads) {
+      const int n = idx % rows_pad, k4 = idx / rows_pad;
+      float h[4], l[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int k = k4 * 4 + j;
+        const float x = (n < rows_valid && k < K) ? __ldg(src + (size_t)n * K + k) - centre : 0.f;
+        h[j] = rna_tf32_mask(x);
+        l[j] = X3 ? rna_tf32_mask(x - h[j]) : 0.f;
+      }
+      *reinterpret_cast<float4*>(hi + (size_t)idx * 4) = make_float4(h[0], h[1], h[2], h[3]);
+      if (X3) *reinterpret_cast<float4*>(lo + (size_t)idx * 4) = make_float4(l[0], l[1], l[2], l[3]);
+    }
+  }
+}
+
+// zero a shared-memory region of n4 float4s
+__device__ __forceinline__ void smem_zero4(float* dst, int n4, int tid, int nthreads) {
+  for (int i = tid; i < n4; i += nthreads) reinterpret_cast<float4*>(dst)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
 }  // namespace tc

@@ -29,6 +29,17 @@ constexpr int JMAX = ADLM_MAX_PROTOS_PER_CLASS;
 constexpr float LN2 = 0.6931471805599453f;
 constexpr float CENTRE = 0.5f;
 
+// -DADLM_PHASE_CLOCKS: CTA 0 records clock64() at the phase boundaries of its first tiles (tools/phase_clocks.py)
+#ifdef ADLM_PHASE_CLOCKS
+__device__ long long g_phase[2][64];
+#define ADLM_PHASE(i)                                                        \
+  do {                                                                       \
+    if (blockIdx.x == 0 && wt == 0 && (i) < 64) g_phase[wg][(i)] = clock64(); \
+  } while (0)
+#else
+#define ADLM_PHASE(i)
+#endif
+
 struct TcFwdParams {
   const float* z;
   const float* P;
@@ -88,38 +99,75 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
   const int tid = threadIdx.x, wg = tid >> 7, wt = tid & 127, warp_in_wg = wt >> 5;
   const bool want_own = p.own_dist != nullptr;
 
+  ADLM_PHASE(0);
   // ---- one-time setup: TMEM, barriers, prototype / last-layer operands ----
   if (tid < 32) tmem_alloc(smem_u32(tmem_base_s), NWG * 256);
   if (tid == 32) {
     for (int i = 0; i < 4; ++i) mbar_init(smem_u32(&bars[i]), 1);
     mbar_init_fence();
   }
-  // Pk: [KP/4][Npad][4], centred and rounded (3xTF32: hi and lo = rna(x - hi))
-  for (int idx = tid; idx < (KP / 4) * Npad; idx += NTHREADS) {
-    const int n = idx % Npad, k4 = idx / Npad;
-    float hi[4], lo[4];
+  // the first tile's features start travelling before the operand staging below
+  const int stride = (int)gridDim.x * NWG;
+  int tile = (int)blockIdx.x + wg * (int)gridDim.x;
+  const int Mi = (int)p.M;
+  float zr[KP];
+  auto prefetch = [&](int t) {
+    const int m = t * TILE + wt;
+    if (t < p.num_tiles && m < Mi) {
+      const int b = m / HW;
+      const float* src = p.z + ((size_t)b * K) * HW + (m - b * HW);
+      if (K == KP) {
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int k = k4 * 4 + j;
-      const float v = (n < N && k < K) ? __ldg(p.P + (size_t)n * K + k) - CENTRE : 0.f;
-      hi[j] = rna_tf32(v);
-      lo[j] = X3 ? rna_tf32(v - hi[j]) : 0.f;
+        for (int k = 0; k < KP; ++k) { zr[k] = __ldg(src); src += HW; }
+      } else {
+#pragma unroll
+        for (int k = 0; k < KP; ++k) zr[k] = (k < K) ? __ldg(src + (size_t)k * HW) : CENTRE;
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < KP; ++k) zr[k] = CENTRE;
     }
-    *reinterpret_cast<float4*>(Pk_hi + (size_t)idx * 4) = make_float4(hi[0], hi[1], hi[2], hi[3]);
-    if (X3) *reinterpret_cast<float4*>(Pk_lo + (size_t)idx * 4) = make_float4(lo[0], lo[1], lo[2], lo[3]);
-  }
+  };
+  prefetch(tile);
+
+  // Pk: [KP/4][Npad][4], centred and rounded (3xTF32: hi and lo = rna(x - hi))
+  stage_rows_kmajor<KP, X3>(Pk_hi, Pk_lo, p.P, N, K, Npad, CENTRE, tid, NTHREADS);
   if (!X3) {
-    // Wk: B operand of MMA2, rows = classes, K index = prototype: [Npad/4][Cpad][4]
+    // Wk: B operand of MMA2, rows = classes, K index = prototype: [Npad/4][Cpad][4]; ln 2 folded in (the
+    // epilogue produces similarities in log2 units).  Padding first (disjoint from the valid entries), then
+    // the valid entries streamed coalesced from W [C][N].
     for (int idx = tid; idx < Npad * Cpad; idx += NTHREADS) {
       const int n = idx / Cpad, c = idx - n * Cpad;
-      const float v = (c < C && n < N) ? __ldg(p.W + (size_t)c * N + n) : 0.f;
-      Wk[(size_t)(n >> 2) * Cpad * 4 + c * 4 + (n & 3)] = rna_tf32(p.act_mode == ADLM_ACT_LOG ? LN2 * v : v);
+      if (!(c < C && n < N)) Wk[(size_t)(n >> 2) * Cpad * 4 + c * 4 + (n & 3)] = 0.f;
+    }
+    const float wscale = p.act_mode == ADLM_ACT_LOG ? LN2 : 1.f;
+    const int CN = C * N;
+    for (int i0 = 0; i0 < CN; i0 += NTHREADS * 4) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int idx = i0 + u * NTHREADS + tid;
+        v[u] = idx < CN ? __ldg(p.W + idx) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int idx = i0 + u * NTHREADS + tid;
+        if (idx < CN) {
+          const int c = idx / N, n = idx - c * N;
+          Wk[(size_t)(n >> 2) * Cpad * 4 + c * 4 + (n & 3)] = rna_tf32_mask(wscale * v[u]);
+        }
+      }
     }
   } else {
     // plain fp32 [Npad][32] for the CUDA-core last layer
     for (int idx = tid; idx < Npad * 32; idx += NTHREADS) {
       const int n = idx >> 5, c = idx & 31;
-      Wk[idx] = (c < C && n < N) ? __ldg(p.W + (size_t)c * N + n) : 0.f;
+      if (!(c < C && n < N)) Wk[idx] = 0.f;
+    }
+    const int CN = C * N;
+    for (int idx = tid; idx < CN; idx += NTHREADS) {
+      const int c = idx / N, n = idx - c * N;
+      Wk[n * 32 + c] = __ldg(p.W + idx);
     }
   }
   __syncthreads();
@@ -163,31 +211,27 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
   const uint32_t idesc1 = make_idesc_tf32(TILE, Npad), idesc2 = make_idesc_tf32(TILE, Cpad);
   const int ksteps = (K + 7) >> 3;
 
-  // tile sequence of this warpgroup: tiles blockIdx.x + (wg + NWG*j) * gridDim.x
-  const long long stride = (long long)gridDim.x * NWG;
-  long long tile = (long long)blockIdx.x + (long long)wg * gridDim.x;
-
-  float zr[KP];
-  auto prefetch = [&](long long t) {
-    const long long m = t * TILE + wt;
-    if (t < p.num_tiles && m < p.M) {
-      const int b = (int)(m / HW);
-      const float* src = p.z + ((size_t)b * K) * HW + (m - (long long)b * HW);
-#pragma unroll
-      for (int k = 0; k < KP; ++k) zr[k] = (k < K) ? __ldg(src + (size_t)k * HW) : CENTRE;
-    } else {
-#pragma unroll
-      for (int k = 0; k < KP; ++k) zr[k] = CENTRE;
-    }
+  ADLM_PHASE(1);
+  // Ping-pong of the two warpgroups: the MUFU-bound epilogue 1 is entered with a token (named barriers 3 + wg),
+  // so one group's epilogue overlaps the other's loads, MMAs and stores instead of both fighting for the
+  // MUFU pipe and then both idling.  n_mine / n_other: tiles of this / the other warpgroup.
+  auto tiles_of = [&](int g) {
+    const int first = (int)blockIdx.x + g * (int)gridDim.x;
+    return first < p.num_tiles ? (p.num_tiles - 1 - first) / stride + 1 : 0;
   };
-  prefetch(tile);
-
+  const int n_mine = tiles_of(wg), n_other = NWG == 2 ? tiles_of(1 - wg) : 0;
+  if (NWG == 2 && wg == 1 && n_other > 0) named_bar_arrive(3, 256);   // WG0 holds the token first
+  int it = 0;
+  (void)n_mine;
   uint32_t parity = 0;
-  for (; tile < p.num_tiles; tile += stride, parity ^= 1u) {
-    const long long m = tile * TILE + wt;
-    const bool valid = m < p.M;
-    const int b = valid ? (int)(m / HW) : 0;
-    const int pix = valid ? (int)(m - (long long)b * HW) : 0;
+  int ph = 2;
+  (void)ph;
+  for (; tile < p.num_tiles; tile += stride, parity ^= 1u, ++it) {
+    ADLM_PHASE(ph); ++ph;                      // +0 tile start
+    const int m = tile * TILE + wt;
+    const bool valid = m < Mi;
+    const int b = valid ? m / HW : 0;
+    const int pix = valid ? m - b * HW : 0;
 
     // ---- convert: registers -> tf32 operand tile; |z|^2 ----
     float x2 = 0.f;
@@ -197,8 +241,8 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const float v = zr[k4 * 4 + j] - CENTRE;
-        hi[j] = rna_tf32(v);
-        lo[j] = X3 ? rna_tf32(v - hi[j]) : 0.f;
+        hi[j] = rna_tf32_mask(v);
+        lo[j] = X3 ? rna_tf32_mask(v - hi[j]) : 0.f;
         const float u = X3 ? v : hi[j];
         x2 = fmaf(u, u, x2);
       }
@@ -208,6 +252,7 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
     fence_async_smem();
     fence_before();
     named_bar_sync(1 + wg, 128);
+    ADLM_PHASE(ph); ++ph;                      // +1 converted, barrier passed
     if (wt == 0) {
       fence_after();
       const uint32_t a_hi = smem_u32(Ahi), a_lo = smem_u32(Alo), b_hi = smem_u32(Pk_hi), b_lo = smem_u32(Pk_lo);
@@ -225,7 +270,9 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
       mma_commit(bar_d1);
     }
     // next tile's features travel while the tensor core and the epilogue work
+    ADLM_PHASE(ph); ++ph;                      // +2 MMA1 issued
     prefetch(tile + stride);
+    ADLM_PHASE(ph); ++ph;                      // +3 prefetch issued
 
     int lab = -1;
     if (want_own && valid) lab = p.target[m];
@@ -233,8 +280,10 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
 
     mbar_wait(bar_d1, parity);
     fence_after();
+    ADLM_PHASE(ph); ++ph;                      // +4 MMA1 done
 
     // ---- epilogue 1: distances -> similarities ----
+    if (NWG == 2) named_bar_sync(3 + wg, 256);
     float lacc[X3 ? 32 : 1];
     if (X3) {
 #pragma unroll
@@ -243,16 +292,14 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
     const uint32_t t1 = d1 + lane_field;
     const bool act_log = p.act_mode == ADLM_ACT_LOG;
     const float eps = p.eps;
-    for (int ch = 0; ch < Npad / 16; ++ch) {
-      uint32_t r[16];
-      tmem_ld16(t1 + ch * 16, r);
+    const int nch = Npad / 16;
+    auto chunk = [&](int ch, const uint32_t (&r)[16]) {
       float xp[16];
 #pragma unroll
       for (int v4 = 0; v4 < 4; ++v4) {
         const float4 q = *reinterpret_cast<const float4*>(p2s + ch * 16 + v4 * 4);
         xp[v4 * 4] = x2 + q.x; xp[v4 * 4 + 1] = x2 + q.y; xp[v4 * 4 + 2] = x2 + q.z; xp[v4 * 4 + 3] = x2 + q.w;
       }
-      tmem_ld_wait();
       float dv[16];
       uint32_t sv_bits[16];
       float sv[16];
@@ -262,10 +309,14 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
         dv[i] = d;
         float s;
         // 1xTF32: similarity in log2 units (ln 2 is folded into the last-layer operand Wk)
+#if defined(ADLM_EXP) && ADLM_EXP == 1
+        if (act_log) s = (d + 1.f) - 0.5f * (d + eps);
+#else
         if (act_log) s = X3 ? logf((d + 1.f) / (d + eps)) : lg2_approx(d + 1.f) - lg2_approx(d + eps);
+#endif
         else s = -d;
         sv[i] = s;
-        sv_bits[i] = __float_as_uint(rna_tf32(s));
+        sv_bits[i] = __float_as_uint(rna_tf32_fast(s));
       }
       if (!X3) {
         tmem_st16(t1 + ch * 16, sv_bits);
@@ -303,8 +354,29 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
             if (pcs[ch * 16 + i] == lab) p.own_dist[(size_t)m * JMAX + prs[ch * 16 + i]] = dv[i];
         }
       }
+    };
+    {
+      // TMEM loads run one chunk ahead of the arithmetic
+      uint32_t ra[16], rb[16];
+      tmem_ld16(t1, ra);
+      for (int ch = 0; ch < nch; ch += 2) {
+        tmem_ld_wait();
+        if (ch + 1 < nch) tmem_ld16(t1 + (ch + 1) * 16, rb);
+        chunk(ch, ra);
+        if (ch + 1 < nch) {
+          tmem_ld_wait();
+          if (ch + 2 < nch) tmem_ld16(t1 + (ch + 2) * 16, ra);
+          chunk(ch + 1, rb);
+        }
+      }
+    }
+    if (NWG == 2) {
+      // hand the token over if the other group still has an epilogue that will wait for it
+      const bool other_waits = wg == 0 ? (it + 1 <= n_other) : (it + 2 <= n_other);
+      if (other_waits) named_bar_arrive(3 + (1 - wg), 256);
     }
 
+    ADLM_PHASE(ph); ++ph;                      // +5 epilogue 1 done
     float lg[32];
     if (!X3) {
       // ---- MMA2: logits = S . W^T with S read from TMEM ----
@@ -339,25 +411,41 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
       for (int c = 0; c < 32; ++c) lg[c] = lacc[X3 ? c : 0];
     }
 
-    // ---- epilogue 2: logits + argmax ----
-    if (valid) {
-      float* dst = p.logits + (size_t)m * C;
+    ADLM_PHASE(ph); ++ph;                      // +6 MMA2 done, logits in registers
+    // ---- epilogue 2: logits + argmax.  The tile's logits are contiguous in HBM ([128 px][C]); they are
+    // transposed through the (now idle) A-operand buffer so that the stores are full 16-byte coalesced ----
+    {
+      float* stg = Ahi;                        // 128 * C floats <= KP * 128 floats
       int best = 0;
       float bv = lg[0];
 #pragma unroll
       for (int c = 0; c < 32; ++c) {
         if (c < C) {
-          dst[c] = lg[c];
+          stg[wt * C + c] = lg[c];
           if (c > 0 && lg[c] > bv) { bv = lg[c]; best = c; }
         }
       }
-      if (p.argmax != nullptr) p.argmax[m] = best;
+      if (valid && p.argmax != nullptr) p.argmax[m] = best;
+      named_bar_sync(1 + wg, 128);
+      const int m0 = tile * TILE;
+      const int npx = min(TILE, Mi - m0);
+      float* dst = p.logits + (size_t)m0 * C;
+      const int cnt = npx * C;
+      if ((cnt & 3) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
+        for (int i = wt; i < (cnt >> 2); i += 128)
+          reinterpret_cast<float4*>(dst)[i] = reinterpret_cast<const float4*>(stg)[i];
+      } else {
+        for (int i = wt; i < cnt; i += 128) dst[i] = stg[i];
+      }
+      named_bar_sync(1 + wg, 128);             // staging buffer is the next tile's operand buffer
     }
     // TMEM reads of this tile are complete (wait::ld); order them before the next tile's MMAs
     fence_before();
+    ADLM_PHASE(ph); ++ph;                      // +7 stored
   }
 
   __syncthreads();
+  ADLM_PHASE(63);
   if (tid < 32) tmem_dealloc(tmem_base, NWG * 256);
 }
 
@@ -416,11 +504,10 @@ int tc_head_fwd(const HeadShape& s, int prec_mode, const float* z, const float* 
   }
 }
 
-int tc_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mask, const float* P, int N,
-                 const int32_t* proto_class, long long patch_base, int prec_mode,
-                 unsigned long long* packed_min, cudaStream_t st) {
-  (void)prec_mode;
-  return simt_push_scan(z, n_img, K, HW, mask, P, N, proto_class, patch_base, packed_min, st);
+#ifdef ADLM_PHASE_CLOCKS
+extern "C" ADLM_API int adlm_debug_phase_clocks(long long* host_out) {
+  return cudaMemcpyFromSymbol(host_out, g_phase, sizeof(long long) * 128) == cudaSuccess ? 0 : -3;
 }
+#endif
 
 }  // namespace adlm

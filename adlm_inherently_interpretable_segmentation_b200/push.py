@@ -26,7 +26,10 @@ import numpy as np
 import torch
 
 from . import _lib
-from .head import _check_cuda_f32, _prec, _proto_2d, DEFAULT_PRECISION
+from .head import _check_cuda_f32, _prec, _proto_2d
+
+#: the search must reproduce the fp32 argmin: tcgen05 3xTF32 (fp32-class distances) unless told otherwise
+PUSH_DEFAULT_PRECISION = "tf32x3"
 
 NORM_MEAN = (0.485, 0.456, 0.406)   # segmentation/constants.py:6-7 (find_nearest.to_normalized_tensor)
 NORM_STD = (0.229, 0.224, 0.225)
@@ -82,7 +85,7 @@ class PushSearch:
         self.proto_class = proto_class.to(device=self.device, dtype=torch.int32).contiguous()
         if int(self.proto_class.max()) >= _lib.MAX_PUSH_CLASSES:
             raise NotImplementedError(f"push supports up to {_lib.MAX_PUSH_CLASSES} classes (uint32 patch mask)")
-        self.prec = _prec(precision or DEFAULT_PRECISION)
+        self.prec = _prec(precision or PUSH_DEFAULT_PRECISION)
         self.packed = torch.full((self.N,), _lib.PUSH_NONE, device=self.device, dtype=torch.int64)
         self._lut_cache = {}
         self.hw = None

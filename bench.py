@@ -215,7 +215,7 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    prec = args.precision or head.DEFAULT_PRECISION
+    prec = args.precision or "tf32"
     c = CFG
     B, K, h, w, N, C = c["B"], c["K"], c["h"], c["w"], c["N"], c["C"]
     M = B * h * w
@@ -323,7 +323,7 @@ def main():
     # ---- secondary metric: push imgs/s over a resident synthetic shard (configs[2] per-GPU slice)
     push_res = None
     if not args.no_push:
-        push_res = bench_push(torch, dist, push, synth, dev, rank, world, prec, pk)
+        push_res = bench_push(torch, dist, push, synth, dev, rank, world, "tf32x3", pk)
 
     cpu = None
     if rank == 0 and not args.no_cpu:
