@@ -14,8 +14,11 @@ namespace adlm {
 
 namespace {
 
-// One CTA per (patch row, image): OR the class bits of every label pixel whose row maps to this
-// patch row into a shared-memory row of w masks.  Label rows are read coalesced.
+// One CTA per (patch row, image): OR the class bits of every label pixel whose row maps to this patch row into
+// a shared-memory row of w masks.  Label rows are streamed 16 pixels (one 16-byte load) per thread; the 16
+// pixels fall into at most a few patches, so their bits are combined in registers and flushed with one
+// shared-memory atomicOr per patch (skipped when the bits are already there).
+template <bool VEC>
 __global__ void __launch_bounds__(256)
 k_patch_class_mask(const uint8_t* __restrict__ labels, int H, int Wimg, const int32_t* __restrict__ row_lut,
                    const int32_t* __restrict__ col_lut, int h, int w, uint32_t* __restrict__ mask_out) {
@@ -23,8 +26,6 @@ k_patch_class_mask(const uint8_t* __restrict__ labels, int H, int Wimg, const in
   const int pi = blockIdx.x, img = blockIdx.y;
   for (int j = threadIdx.x; j < w; j += blockDim.x) smask[j] = 0u;
   __syncthreads();
-  // rows mapped to patch row pi: the LUT is monotone, find the range by scanning from an estimate
-  // (kept simple: every thread tests the row it strides over)
   const uint8_t* lab = labels + (size_t)img * H * Wimg;
   // first/last row of this patch row (binary search on the monotone LUT)
   int lo = 0, hi = H;
@@ -33,15 +34,56 @@ k_patch_class_mask(const uint8_t* __restrict__ labels, int H, int Wimg, const in
   hi = H;
   while (lo < hi) { const int mid = (lo + hi) >> 1; if (row_lut[mid] <= pi) lo = mid + 1; else hi = mid; }
   const int r1 = lo;
-  const int n = (r1 - r0) * Wimg;
-  for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
-    const int r = r0 + idx / Wimg, j = idx - (idx / Wimg) * Wimg;
-    const unsigned l = lab[(size_t)r * Wimg + j];
-    if (l > 0u && l <= 32u) {
-      const uint32_t bit = 1u << (l - 1u);
-      const int pj = col_lut[j];
-      // neighbouring lanes usually hit the same patch with the same class: skip redundant atomics
-      if ((smask[pj] & bit) == 0u) atomicOr(&smask[pj], bit);
+  if (VEC) {
+    const int vpr = Wimg >> 4;                      // 16-pixel vectors per row
+    const int nvec = (r1 - r0) * vpr;
+    const uint4* base = reinterpret_cast<const uint4*>(lab + (size_t)r0 * Wimg);
+    auto consume = [&](int vec, const uint4 v) {
+      const int cv = vec % vpr;
+      const int4* lut4 = reinterpret_cast<const int4*>(col_lut + cv * 16);
+      const uint32_t words[4] = {v.x, v.y, v.z, v.w};
+      int cur = -1;
+      uint32_t bits = 0u;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int4 pj4 = __ldg(lut4 + q);
+        const int pjs[4] = {pj4.x, pj4.y, pj4.z, pj4.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const unsigned l = (words[q] >> (8 * e)) & 0xffu;
+          if (pjs[e] != cur) {
+            if (bits != 0u && (smask[cur] & bits) != bits) atomicOr(&smask[cur], bits);
+            cur = pjs[e];
+            bits = 0u;
+          }
+          if (l - 1u < 32u) bits |= 1u << (l - 1u);
+        }
+      }
+      if (bits != 0u && (smask[cur] & bits) != bits) atomicOr(&smask[cur], bits);
+    };
+    for (int v0 = threadIdx.x; v0 < nvec; v0 += 4 * 256) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int vec = v0 + u * 256;
+        v[u] = vec < nvec ? __ldg(base + vec) : make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int vec = v0 + u * 256;
+        if (vec < nvec) consume(vec, v[u]);
+      }
+    }
+  } else {
+    const int n = (r1 - r0) * Wimg;
+    for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
+      const int r = r0 + idx / Wimg, j = idx - (idx / Wimg) * Wimg;
+      const unsigned l = lab[(size_t)r * Wimg + j];
+      if (l > 0u && l <= 32u) {
+        const uint32_t bit = 1u << (l - 1u);
+        const int pj = col_lut[j];
+        if ((smask[pj] & bit) == 0u) atomicOr(&smask[pj], bit);
+      }
     }
   }
   __syncthreads();
@@ -173,7 +215,11 @@ int patch_class_mask_impl(const uint8_t* labels, int n_img, int H, int Wimg, con
                           const int32_t* col_lut, int h, int w, uint32_t* mask_out, cudaStream_t st) {
   dim3 grid(h, n_img);
   KernelTimer timer(ADLM_K_PATCH_MASK, st);
-  k_patch_class_mask<<<grid, 256, sizeof(uint32_t) * w, st>>>(labels, H, Wimg, row_lut, col_lut, h, w, mask_out);
+  // 16-byte label loads need Wimg % 16 == 0 and 16-byte aligned rows / LUT
+  const bool vec = (Wimg % 16 == 0) && ((reinterpret_cast<uintptr_t>(labels) & 15u) == 0) &&
+                   ((reinterpret_cast<uintptr_t>(col_lut) & 15u) == 0);
+  if (vec) k_patch_class_mask<true><<<grid, 256, sizeof(uint32_t) * w, st>>>(labels, H, Wimg, row_lut, col_lut, h, w, mask_out);
+  else     k_patch_class_mask<false><<<grid, 256, sizeof(uint32_t) * w, st>>>(labels, H, Wimg, row_lut, col_lut, h, w, mask_out);
   ADLM_LAUNCH_CHECK();
   return ADLM_OK;
 }
