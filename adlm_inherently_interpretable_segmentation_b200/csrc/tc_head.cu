@@ -40,26 +40,6 @@ __device__ long long g_phase[2][64];
 #define ADLM_PHASE(i)
 #endif
 
-struct TcFwdParams {
-  const float* z;
-  const float* P;
-  const float* W;
-  float* logits;
-  float* dist;
-  float* sim;
-  int32_t* argmax;
-  const int32_t* target;
-  const int32_t* proto_class;
-  const int32_t* proto_rank;
-  float* own_dist;
-  int B, K, HW, N, C;
-  float eps;
-  int act_mode;
-  int Npad, Cpad;
-  long long M;
-  int num_tiles;
-};
-
 template <int KP, bool X3>
 struct FwdSmem {
   static constexpr int NWG = X3 ? 1 : 2;
@@ -496,6 +476,7 @@ int tc_head_fwd(const HeadShape& s, int prec_mode, const float* z, const float* 
   prm.M = (long long)s.B * s.HW;
   prm.num_tiles = (int)((prm.M + TILE - 1) / TILE);
   const bool x3 = prec_mode == ADLM_PREC_TF32X3;
+  if (!x3 && s.K <= 64) return tc_head_fwd_ws(prm, st);     // warp-specialised pipeline (tc_head_ws.cu)
   const int kp = s.K <= 32 ? 32 : (s.K <= 64 ? 64 : 128);
   switch (kp) {
     case 32: return x3 ? launch_fwd<32, true>(prm, st) : launch_fwd<32, false>(prm, st);

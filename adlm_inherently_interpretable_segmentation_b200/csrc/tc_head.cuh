@@ -4,6 +4,28 @@
 
 namespace adlm {
 
+struct TcFwdParams {
+  const float* z;
+  const float* P;
+  const float* W;
+  float* logits;
+  float* dist;
+  float* sim;
+  int32_t* argmax;
+  const int32_t* target;
+  const int32_t* proto_class;
+  const int32_t* proto_rank;
+  float* own_dist;
+  int B, K, HW, N, C;
+  float eps;
+  int act_mode;
+  int Npad, Cpad;
+  long long M;
+  int num_tiles;
+};
+// 1xTF32, K <= 64: producer / MMA / epilogue warps, double-buffered TMEM accumulators (tc_head_ws.cu)
+int tc_head_fwd_ws(const TcFwdParams& prm, cudaStream_t st);
+
 int tc_head_fwd(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
                 float* logits, float* dist, float* sim, int32_t* argmax, const StepExtras& ex,
                 cudaStream_t st);
