@@ -98,7 +98,16 @@ struct StepExtras {
   const int32_t* proto_rank = nullptr;   // [N] rank of the prototype inside its class
   float* own_dist = nullptr;             // [B*HW, JMAX] fwd: distances to the label's own class
   const float* own_grad = nullptr;       // [B*HW, JMAX] bwd: dL/d(own_dist) from the KLD term
+  // fused cross entropy in the forward (module.py:156-165,210-211); honoured by the warp-specialised tcgen05
+  // forward only — callers must check head_fwd_fuses_ce() and run the separate CE kernel otherwise
+  const int32_t* ce_counts = nullptr;    // [0] = number of CE patches
+  float* ce_dlogits = nullptr;           // [B*HW, C] | null
+  double* ce_accum = nullptr;            // [0] += loss sum, [1] += correct
+  float ce_scale = 0.f;                  // w_ce * grad_scale
+  int ignore_void = 0;
 };
+// true when head_fwd_dispatch(prec_mode, shape) runs the kernel that honours the ce_* extras
+bool head_fwd_fuses_ce(const HeadShape& s, int prec_mode);
 
 int simt_head_fwd(const HeadShape& s, const float* z, const float* P, const float* W,
                   float* logits, float* dist, float* sim, int32_t* argmax,

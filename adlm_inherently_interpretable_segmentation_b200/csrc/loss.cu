@@ -31,52 +31,6 @@ int group_table_floats() { return GT_SIZE; }
 
 namespace {
 
-// hist[b][l], l in [0, C]; labels outside [0, C] are ignored everywhere.
-__global__ void k_label_hist(const int32_t* __restrict__ target, int HW, int C, int* __restrict__ hist) {
-  extern __shared__ int sh[];
-  const int b = blockIdx.y;
-  for (int i = threadIdx.x; i <= C; i += blockDim.x) sh[i] = 0;
-  __syncthreads();
-  const int32_t* t = target + (size_t)b * HW;
-  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < HW; p += gridDim.x * blockDim.x) {
-    const int l = t[p];
-    if (l >= 0 && l <= C) atomicAdd(&sh[l], 1);
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i <= C; i += blockDim.x)
-    if (sh[i]) atomicAdd(&hist[b * (C + 1) + i], sh[i]);
-}
-
-// counts[0] = number of CE patches, counts[1] = number of KLD terms; cls_count[c] = prototypes of class c.
-// Also zeroes the double accumulators.
-__global__ void k_loss_prepare(const int* __restrict__ hist, const int32_t* __restrict__ proto_class,
-                               int B, int C, int N, int ignore_void, int* __restrict__ cls_count,
-                               int* __restrict__ counts, double* __restrict__ accum) {
-  __shared__ int s_cls[ADLM_MAX_C];
-  __shared__ int s_valid, s_terms;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) s_cls[c] = 0;
-  if (threadIdx.x == 0) { s_valid = 0; s_terms = 0; }
-  __syncthreads();
-  for (int n = threadIdx.x; n < N; n += blockDim.x) {
-    const int c = proto_class[n];
-    if (c >= 0 && c < C) atomicAdd(&s_cls[c], 1);
-  }
-  __syncthreads();
-  int valid = 0, terms = 0;
-  for (int i = threadIdx.x; i < B * (C + 1); i += blockDim.x) {
-    const int l = i % (C + 1), cnt = hist[i];
-    if (ignore_void) { if (l >= 1) valid += cnt; }          // class = l-1 in [0, C)
-    else             { if (l < C) valid += cnt; }
-    if (l < C && cnt >= 2 && s_cls[l] >= 2) terms += s_cls[l] * (s_cls[l] - 1) / 2;
-  }
-  atomicAdd(&s_valid, valid);
-  atomicAdd(&s_terms, terms);
-  __syncthreads();
-  for (int c = threadIdx.x; c < C; c += blockDim.x) cls_count[c] = s_cls[c];
-  if (threadIdx.x == 0) { counts[0] = s_valid; counts[1] = s_terms; }
-  if (threadIdx.x < 4) accum[threadIdx.x] = 0.0;
-}
-
 // One thread per pixel: CE contribution, correctness, dlogits (module.py:156-165,210-211).
 __global__ void k_ce(const float* __restrict__ logits, const int32_t* __restrict__ target, long long M,
                      int C, int ignore_void, float w_ce_scaled, const int* __restrict__ counts,
@@ -379,6 +333,7 @@ __global__ void k_finalize(const float* __restrict__ W, const int32_t* __restric
 }  // namespace
 
 // ---------------------------------------------------------------------------------- host side
+static std::atomic<unsigned int> g_next_ticket_slot{0};
 struct StepWorkspace {  // carved out of the caller's workspace buffer
   float* logits;     // [M, C]
   float* dlogits;    // [M, C]
@@ -432,8 +387,7 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
   float* logits = logits_out ? logits_out : ws.logits;
 
   {
-    static std::atomic<unsigned int> next_slot{0};
-    const int slot = (int)(next_slot.fetch_add(1u, std::memory_order_relaxed) % TICKET_SLOTS);
+    const int slot = (int)(g_next_ticket_slot.fetch_add(1u, std::memory_order_relaxed) % TICKET_SLOTS);
     k_step_prepare<<<B, 1024, 0, st>>>(target, proto_class, B, HW, C, N, ignore_void, slot, ws.hist, ws.cls_count,
                                        ws.counts, ws.rank, ws.accum);
     ADLM_LAUNCH_CHECK();
@@ -445,13 +399,24 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
   ex.proto_class = proto_class;
   ex.proto_rank = ws.rank;
   ex.own_dist = ws.own;
+  const bool fuse_ce = head_fwd_fuses_ce(s, prec_mode);
+  if (fuse_ce) {
+    // CE, accuracy and dlogits come out of the forward kernel's logits registers; logits touch HBM only on request
+    ex.ce_counts = counts;
+    ex.ce_dlogits = want_grad ? ws.dlogits : nullptr;
+    ex.ce_accum = ws.accum;
+    ex.ce_scale = w_ce * grad_scale;
+    ex.ignore_void = ignore_void;
+  }
   int rc;
-  if ((rc = head_fwd_dispatch(s, prec_mode, z, P, W, logits, nullptr, nullptr, argmax_out, ex, st)) != ADLM_OK)
+  if ((rc = head_fwd_dispatch(s, prec_mode, z, P, W, fuse_ce ? logits_out : logits, nullptr, nullptr, argmax_out, ex,
+                              st)) != ADLM_OK)
     return rc;
-
-  k_ce<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(logits, target, M, C, ignore_void, w_ce * grad_scale,
-                                                    counts, want_grad ? ws.dlogits : nullptr, ws.accum);
-  ADLM_LAUNCH_CHECK();
+  if (!fuse_ce) {
+    k_ce<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(logits, target, M, C, ignore_void, w_ce * grad_scale,
+                                                      counts, want_grad ? ws.dlogits : nullptr, ws.accum);
+    ADLM_LAUNCH_CHECK();
+  }
   {
     dim3 grid(C, B);
     ADLM_CHECK_SUPPORTED((size_t)HW * sizeof(int) <= 200 * 1024, "feature map too large for the KLD kernel (h*w > 51200)");
@@ -476,12 +441,11 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
 
 int step_counts_impl(const int32_t* target, int B, int HW, const int32_t* proto_class, int N, int C,
                      int ignore_void, int32_t* counts_out, void* workspace, cudaStream_t st) {
+  // the step's own prologue kernel, with the normalisers redirected to the caller's buffer (one launch)
   StepWorkspace ws = carve_step_workspace(workspace, B, 1, HW, N, C);
-  ADLM_CUDA(cudaMemsetAsync(ws.hist, 0, sizeof(int) * (size_t)B * (C + 1), st));
-  dim3 grid(min(cdiv(HW, 256), 64), B);
-  k_label_hist<<<grid, 256, sizeof(int) * (C + 1), st>>>(target, HW, C, ws.hist);
-  ADLM_LAUNCH_CHECK();
-  k_loss_prepare<<<1, 256, 0, st>>>(ws.hist, proto_class, B, C, N, ignore_void, ws.cls_count, counts_out, ws.accum);
+  const int slot = (int)(g_next_ticket_slot.fetch_add(1u, std::memory_order_relaxed) % TICKET_SLOTS);
+  k_step_prepare<<<B, 1024, 0, st>>>(target, proto_class, B, HW, C, N, ignore_void, slot, ws.hist, ws.cls_count,
+                                     counts_out, ws.rank, ws.accum);
   ADLM_LAUNCH_CHECK();
   return ADLM_OK;
 }

@@ -25,6 +25,17 @@ constexpr int JMAX = ADLM_MAX_PROTOS_PER_CLASS;
 constexpr float LN2 = 0.6931471805599453f;
 constexpr float CENTRE = 0.5f;
 
+// -DADLM_PHASE_CLOCKS: CTA 0 of k_tc_bwd_dp records clock64() per role (0 builder, 1 MMA issuer, 2 epilogue warp 0)
+#ifdef ADLM_PHASE_CLOCKS
+__device__ long long g_dp_phase[3][64];
+#define DP_PHASE(role, i)                                                                           \
+  do {                                                                                              \
+    if (blockIdx.x == 0 && (threadIdx.x & 31) == 0 && (i) < 64) g_dp_phase[(role)][(i)] = clock64(); \
+  } while (0)
+#else
+#define DP_PHASE(role, i)
+#endif
+
 struct TcBwdParams {
   const float* z;
   const float* P;
@@ -412,6 +423,9 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
   fence_after();
 
   const uint32_t tmem_base = *tmem_base_s;
+  if (warp == 8) DP_PHASE(0, 0);
+  if (warp == 12) DP_PHASE(1, 0);
+  if (warp == 0) DP_PHASE(2, 0);
   const uint32_t tD1 = tmem_base, tGl = tmem_base + 128, tP0 = tmem_base + 256, tW0 = tmem_base + 256 + NB * KP;
   const uint32_t bar_full = smem_u32(&bars[0]), bar_acc = smem_u32(&bars[1]), bar_gs = smem_u32(&bars[2]),
                  bar_free = smem_u32(&bars[3]);
@@ -449,7 +463,9 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
     for (int it = 0; it < iters; ++it) {
       const int m = ((int)blockIdx.x + it * (int)gridDim.x) * TILE + cw;
       const bool valid = m < Mi;
+      if (warp == 8) DP_PHASE(0, 1 + it * 8);
       if (it > 0) mbar_wait(bar_free, (uint32_t)(it - 1) & 1u);
+      if (warp == 8) DP_PHASE(0, 2 + it * 8);
       clsm[cw] = 0u;
       named_bar_sync(2, 128);
       const int mylab = (valid && kld) ? p.target[m] : -1;
@@ -485,7 +501,9 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
       labs[cw] = valid ? mylab : -2;
       fence_async_smem();
       mbar_arrive(bar_full);
+      if (warp == 8) DP_PHASE(0, 3 + it * 8);
       prefetch(it + 1);
+      if (warp == 8) DP_PHASE(0, 4 + it * 8);
     }
   } else if (warp == 12) {
     // ================= MMA issuer =================
@@ -496,6 +514,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
       for (int it = 0; it < iters; ++it) {
         mbar_wait(bar_full, (uint32_t)it & 1u);
         fence_after();
+        DP_PHASE(1, 1 + it * 8);
         for (int blk = 0; blk < NB; ++blk) {
           const uint32_t a0 = smem_u32(PkA) + blk * 128 * 16, b0 = smem_u32(ZkB);
           for (int ks = 0; ks < ksteps; ++ks)
@@ -506,7 +525,9 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
             mma_ss(tGl, make_desc(w0 + ks * 2 * Npad2 * 16, Npad2 * 16, 128), make_desc(l0 + ks * 2 * TILE * 16, TILE * 16, 128),
                    idesc_t, ks > 0 ? 1u : 0u);
           mma_commit(bar_acc);
+          DP_PHASE(1, 2 + it * 8 + blk * 3);
           mbar_wait(bar_gs, g & 1u);
+          DP_PHASE(1, 3 + it * 8 + blk * 3);
           ++g;
           fence_after();
           const uint32_t zt0 = smem_u32(ZtB), lt0 = smem_u32(dLtB);
@@ -517,6 +538,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
           }
         }
         mma_commit(bar_free);
+        DP_PHASE(1, 8 + it * 8);
       }
     }
   } else {
@@ -546,11 +568,14 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
     for (int it = 0; it < iters; ++it) {
       const long long m0 = ((long long)blockIdx.x + (long long)it * gridDim.x) * TILE;
       const int npx = (int)((p.M - m0) < TILE ? (p.M - m0) : TILE);   // valid pixel columns of this tile
+      if (warp == 0) DP_PHASE(2, 1 + it * 8);
       mbar_wait(bar_full, (uint32_t)it & 1u);
 #pragma unroll
       for (int blk = 0; blk < NB; ++blk) {
         const int n = blk * 128 + lane_n;
+        if (warp == 0) DP_PHASE(2, 2 + it * 8 + blk * 3);
         mbar_wait(bar_acc, g & 1u);
+        if (warp == 0) DP_PHASE(2, 3 + it * 8 + blk * 3);
         ++g;
         fence_after();
         if (blk * 128 + (warp & 3) * 32 < N) {       // warps whose 32 prototypes are all padding skip the math
@@ -615,6 +640,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
         }
         fence_before();
         mbar_arrive(bar_gs);
+        if (warp == 0) DP_PHASE(2, 4 + it * 8 + blk * 3);
       }
     }
     // ---- flush this CTA's partial sums ----
@@ -756,6 +782,12 @@ int launch_bwd(TcBwdParams prm, float* dP, float* dW, void* workspace, size_t wo
 }
 
 }  // namespace
+
+#ifdef ADLM_PHASE_CLOCKS
+extern "C" ADLM_API int adlm_debug_dp_phase_clocks(long long* host_out) {
+  return cudaMemcpyFromSymbol(host_out, g_dp_phase, sizeof(long long) * 192) == cudaSuccess ? 0 : -3;
+}
+#endif
 
 size_t tc_bwd_workspace_bytes(int K, int N) {
   const int NB = (N + 127) / 128, Npad2 = NB * 128, KP = K <= 32 ? 32 : 64;

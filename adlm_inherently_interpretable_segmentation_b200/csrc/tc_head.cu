@@ -461,6 +461,7 @@ int launch_fwd(const TcFwdParams& prm, cudaStream_t st) {
 int tc_head_fwd(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
                 float* logits, float* dist, float* sim, int32_t* argmax, const StepExtras& ex,
                 cudaStream_t st) {
+  ADLM_CHECK_ARG(logits != nullptr || (ex.ce_accum != nullptr && head_fwd_fuses_ce(s, prec_mode)), "logits must be non-null");
   ADLM_CHECK_SUPPORTED(s.K <= 128, "tensor-core path needs K <= 128 (use precision fp32)");
   ADLM_CHECK_SUPPORTED(s.N <= 224, "tensor-core path needs N <= 224 (use precision fp32)");
   ADLM_CHECK_SUPPORTED(s.C <= 32, "tensor-core path needs C <= 32 (use precision fp32)");
@@ -469,6 +470,8 @@ int tc_head_fwd(const HeadShape& s, int prec_mode, const float* z, const float* 
   prm.logits = logits; prm.dist = dist; prm.sim = sim; prm.argmax = argmax;
   prm.target = ex.target; prm.proto_class = ex.proto_class; prm.proto_rank = ex.proto_rank;
   prm.own_dist = ex.own_dist;
+  prm.ce_counts = ex.ce_counts; prm.dlogits = ex.ce_dlogits; prm.ce_accum = ex.ce_accum;
+  prm.ce_scale = ex.ce_scale; prm.ignore_void = ex.ignore_void;
   prm.B = s.B; prm.K = s.K; prm.HW = s.HW; prm.N = s.N; prm.C = s.C;
   prm.eps = s.eps; prm.act_mode = s.act_mode;
   prm.Npad = (s.N + 15) & ~15;

@@ -16,6 +16,12 @@ struct TcFwdParams {
   const int32_t* proto_class;
   const int32_t* proto_rank;
   float* own_dist;
+  // fused cross entropy (warp-specialised kernel only): all null / 0 = plain forward
+  const int32_t* ce_counts;   // [0] = number of CE patches (device)
+  float* dlogits;             // [M, C] | null
+  double* ce_accum;           // [0] += sum of losses, [1] += correct patches
+  float ce_scale;             // w_ce * grad_scale
+  int ignore_void;
   int B, K, HW, N, C;
   float eps;
   int act_mode;

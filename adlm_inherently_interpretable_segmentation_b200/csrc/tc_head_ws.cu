@@ -272,26 +272,64 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
       int best = 0;
       float bv = lg[0];
 #pragma unroll
-      for (int c = 0; c < 32; ++c) {
-        if (c < C) {
-          stg[row * C + c] = lg[c];
-          if (c > 0 && lg[c] > bv) { bv = lg[c]; best = c; }
-        }
-      }
+      for (int c = 1; c < 32; ++c)
+        if (c < C && lg[c] > bv) { bv = lg[c]; best = c; }
       if (m < Mi && p.argmax != nullptr) p.argmax[m] = best;
-      named_bar_sync(1 + half, 128);
       const int m0 = tile * TILE;
       const int npx = min(TILE, Mi - m0);
-      float* dst = p.logits + (size_t)m0 * C;
       const int cnt = npx * C;
       const int t128 = tid & 127;
-      if ((cnt & 3) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
-        for (int i = t128; i < (cnt >> 2); i += 128)
-          reinterpret_cast<float4*>(dst)[i] = reinterpret_cast<const float4*>(stg)[i];
-      } else {
-        for (int i = t128; i < cnt; i += 128) dst[i] = stg[i];
+      // a [128 px][C] tile is contiguous in HBM: transpose through shared memory, store 16 bytes per thread
+      auto store_tile = [&](float* base) {
+#pragma unroll
+        for (int c = 0; c < 32; ++c)
+          if (c < C) stg[row * C + c] = lg[c];
+        named_bar_sync(1 + half, 128);
+        float* dst = base + (size_t)m0 * C;
+        if ((cnt & 3) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
+          for (int i = t128; i < (cnt >> 2); i += 128)
+            reinterpret_cast<float4*>(dst)[i] = reinterpret_cast<const float4*>(stg)[i];
+        } else {
+          for (int i = t128; i < cnt; i += 128) dst[i] = stg[i];
+        }
+        named_bar_sync(1 + half, 128);         // the staging buffer is reused
+      };
+      if (p.logits != nullptr) store_tile(p.logits);
+      if (p.ce_accum != nullptr) {
+        // cross entropy over the non-void patches (module.py:156-165), accuracy (:210-211), and
+        // dlogits = w_ce * grad_scale / n_patches * (softmax - onehot), all from the registers
+        int tg = (m < Mi) ? p.target[m] : -1;
+        bool ok;
+        if (p.ignore_void) { ok = tg >= 1 && tg <= C; tg -= 1; }
+        else               { ok = tg >= 0 && tg < C; }
+        float loss = 0.f, hit = 0.f;
+        if (ok) {
+          float se = 0.f, lt = 0.f;
+#pragma unroll
+          for (int c = 0; c < 32; ++c)
+            if (c < C) {
+              se += __expf(lg[c] - bv);
+              if (c == tg) lt = lg[c];
+            }
+          const float lse = bv + __logf(se);
+          loss = lse - lt;
+          hit = (best == tg) ? 1.f : 0.f;
+          const float sc = p.ce_scale / (float)p.ce_counts[0];
+#pragma unroll
+          for (int c = 0; c < 32; ++c)
+            if (c < C) lg[c] = sc * (__expf(lg[c] - lse) - (c == tg ? 1.f : 0.f));
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) lg[c] = 0.f;
+        }
+        if (p.dlogits != nullptr) store_tile(p.dlogits);
+        loss = warp_sum(loss);
+        hit = warp_sum(hit);
+        if (lane == 0) {
+          if (loss != 0.f) atomicAdd(&p.ce_accum[0], (double)loss);
+          if (hit != 0.f) atomicAdd(&p.ce_accum[1], (double)hit);
+        }
       }
-      named_bar_sync(1 + half, 128);           // the staging buffer is reused two tiles later
     };
 
     for (int it = 0; it < iters; ++it) {

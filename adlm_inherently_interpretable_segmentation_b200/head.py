@@ -172,7 +172,8 @@ class _StepResult(dict):
 
 def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
                weights=(1.0, 0.25, 1e-4), grad_scale=1.0, eps=1e-4, precision=None,
-               need_grads=True, want_logits=False, want_argmax=False, workspace=None, global_counts=None):
+               need_grads=True, want_logits=False, want_argmax=False, workspace=None, global_counts=None,
+               grads_out=None):
     """One C-ABI call for module.py:137-222 + :236 on given features.
 
     z (B,K,h,w); target (B,h,w) integer labels already resized to the feature map (dataset.py:23-31);
@@ -180,7 +181,8 @@ def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
       scalars (8,) float64 [loss, cross_entropy, kld_loss, l1, n_correct, n_patches, n_kld_terms, 0],
       dz, dP (shaped like prototypes), dW (None when need_grads is False), logits, argmax (optional).
     Gradients are those of (loss * grad_scale).  global_counts: (2,) int32 CUDA tensor overriding the
-    CE / KLD normalisers (data-parallel shards, see parallel.py), or None."""
+    CE / KLD normalisers (data-parallel shards, see parallel.py), or None.  grads_out: optional flat fp32
+    CUDA buffer with at least N*K + C*N elements; dP and dW are then views into it ([dP | dW], one collective)."""
     lib = _lib.load()
     _check_cuda_f32("conv_features", z)
     _check_cuda_f32("prototype_vectors", prototypes)
@@ -205,8 +207,14 @@ def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
             workspace = torch.empty(need, device=dev, dtype=torch.uint8)
         scalars = torch.empty(_lib.STEP_NSCALARS, device=dev, dtype=torch.float64)
         dz = torch.empty_like(z) if need_grads else None
-        dP = torch.empty((N, K), device=dev, dtype=torch.float32) if need_grads else None
-        dW = torch.empty((C, N), device=dev, dtype=torch.float32) if need_grads else None
+        if need_grads and grads_out is not None:
+            if grads_out.dtype != torch.float32 or not grads_out.is_cuda or grads_out.numel() < N * K + C * N:
+                raise ValueError("grads_out must be a CUDA float32 buffer with >= N*K + C*N elements")
+            dP = grads_out[:N * K].view(N, K)
+            dW = grads_out[N * K:N * K + C * N].view(C, N)
+        else:
+            dP = torch.empty((N, K), device=dev, dtype=torch.float32) if need_grads else None
+            dW = torch.empty((C, N), device=dev, dtype=torch.float32) if need_grads else None
         logits = torch.empty((B, h, w, C), device=dev, dtype=torch.float32) if want_logits else None
         amax = torch.empty((B, h, w), device=dev, dtype=torch.int32) if want_argmax else None
         rc = lib.adlm_step_fwd_bwd(_lib.ptr(z), B, K, HW, _lib.ptr(P), _lib.ptr(W), N, C, c_float(eps),

@@ -77,20 +77,45 @@ def merge_owned_rows(rows, group=None):
     return rows
 
 
+_ADDITIVE = {}
+
+
+def _additive_mask(device, rank, replicated=(3, 5, 6)):
+    """(8,) float64: 1 for the additive loss scalars, and for the replicated ones (raw L1 norm, the two global
+    normalisers, identical on every rank) 1 on rank 0 only, so that a SUM over ranks keeps their value"""
+    key = (device, rank, tuple(replicated))
+    if key not in _ADDITIVE:
+        m = torch.ones(8, dtype=torch.float64)
+        if rank != 0:
+            m[list(replicated)] = 0.0
+        _ADDITIVE[key] = m.to(device)
+    return _ADDITIVE[key]
+
+
 def dp_fused_step(ppnet_or_params, z, target, proto_class, ignore_void=True, weights=(1.0, 0.25, 1e-4),
                   grad_scale=1.0, precision=None, group=None, workspace=None):
     """Data-parallel fused step on this rank's image shard.  Returns the head.fused_step result with dP, dW
     and scalars already reduced (identical on every rank, equal to the single-GPU step on the whole batch);
-    dz is the gradient for this rank's features only (it feeds the local backbone backward)."""
+    dz is the gradient for this rank's features only (it feeds the local backbone backward).
+
+    Two collectives per step: the 8-byte sum of the loss normalisers before the kernels run, and one fp32
+    sum of the flat buffer [dP | dW | 8 loss scalars] after them (the kernels write dP and dW straight into it)."""
     from . import head
     prototypes, weight = ppnet_or_params
     rank, size = world(group)
     C = weight.shape[0]
+    if size == 1:
+        return head.fused_step(z, prototypes, weight, target, proto_class, ignore_void=ignore_void, weights=weights,
+                               grad_scale=grad_scale, precision=precision, workspace=workspace)
     counts = head.step_counts(target, proto_class, C, ignore_void, workspace=workspace, K=z.shape[1])
     allreduce_counts(counts, group)
     w_ce, w_kld, w_l1 = weights
+    n_grad = prototypes.numel() + weight.numel()
+    flat = torch.empty(n_grad + 8, device=z.device, dtype=torch.float32)
     res = head.fused_step(z, prototypes, weight, target, proto_class, ignore_void=ignore_void,
                           weights=(w_ce, w_kld, w_l1 / size), grad_scale=grad_scale, precision=precision,
-                          global_counts=counts, workspace=workspace)
-    allreduce_head_grads(res.dP, res.dW, res.scalars, group)
+                          global_counts=counts, workspace=workspace, grads_out=flat)
+    flat[n_grad:].copy_(res.scalars * _additive_mask(z.device, rank))
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    res["scalars"] = flat[n_grad:].to(torch.float64)
     return res
