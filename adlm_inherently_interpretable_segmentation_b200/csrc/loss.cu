@@ -77,7 +77,9 @@ __global__ void k_ce(const float* __restrict__ logits, const int32_t* __restrict
 // A[a][b] = E_a[d_b], the pair terms, and — same CTA, which owns exactly these pixels — dL/d(own distances)
 // for the backward kernels.  Thread = (pixel lane tid/16, prototype-in-class tid%16): ~50 registers, so all
 // B*C CTAs are resident at once.
-__global__ void __launch_bounds__(256)
+constexpr int KLD_THREADS = 512, KLD_PL = KLD_THREADS / 16, KLD_WARPS = KLD_THREADS / 32;
+
+__global__ void __launch_bounds__(KLD_THREADS)
 k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const int* __restrict__ hist,
       const int* __restrict__ cls_count, const int* __restrict__ counts, int HW, int C,
       float coef /* w_kld * grad_scale */, float* __restrict__ own_grad, double* __restrict__ accum) {
@@ -91,19 +93,19 @@ k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const i
   __shared__ int s_n;
   __shared__ float s_mx[JMAX], s_S[JMAX], s_lse[JMAX], s_cs[JMAX], s_r[JMAX];
   __shared__ float s_T[JMAX][JMAX];
-  __shared__ float s_red[8][JMAX];
+  __shared__ float s_red[KLD_WARPS][JMAX];
   __shared__ float s_kl[JMAX][JMAX];
   const int32_t* t = target + (size_t)b * HW;
   const float* ob = own + (size_t)b * HW * JMAX;
   if (tid == 0) s_n = 0;
   __syncthreads();
-  for (int p0 = 0; p0 < HW; p0 += 1024) {
+  for (int p0 = 0; p0 < HW; p0 += 4 * KLD_THREADS) {
     // four label loads in flight per thread; order inside the list is irrelevant
     int pp[4];
     bool hit[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      pp[u] = p0 + u * 256 + tid;
+      pp[u] = p0 + u * KLD_THREADS + tid;
       hit[u] = pp[u] < HW && t[pp[u]] == l;
     }
 #pragma unroll
@@ -121,20 +123,20 @@ k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const i
   float* og = own_grad ? own_grad + (size_t)b * HW * JMAX : nullptr;
   if (!valid_group) {
     if (og)
-      for (int i = pl; i < n; i += 16) og[(size_t)s_list[i] * JMAX + j] = 0.f;
+      for (int i = pl; i < n; i += KLD_PL) og[(size_t)s_list[i] * JMAX + j] = 0.f;
     return;
   }
   // pass A: per-prototype max over the group's pixels
   float mx = -INFINITY;
-  for (int i = pl; i < n; i += 16) mx = fmaxf(mx, ob[(size_t)s_list[i] * JMAX + j]);
+  for (int i = pl; i < n; i += KLD_PL) mx = fmaxf(mx, ob[(size_t)s_list[i] * JMAX + j]);
   mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
   if (lane < 16) s_red[tid >> 5][j] = mx;
-  s_T[pl][j] = 0.f;                               // 256 threads == JMAX*JMAX
+  if (tid < JMAX * JMAX) s_T[pl][j] = 0.f;
   if (tid < JMAX) s_S[tid] = 0.f;
   __syncthreads();
   if (tid < JMAX) {
     float m = s_red[0][tid];
-    for (int w = 1; w < 8; ++w) m = fmaxf(m, s_red[w][tid]);
+    for (int w = 1; w < KLD_WARPS; ++w) m = fmaxf(m, s_red[w][tid]);
     s_mx[tid] = m;
   }
   __syncthreads();
@@ -144,7 +146,7 @@ k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const i
     float S = 0.f, T[JMAX];
 #pragma unroll
     for (int c = 0; c < JMAX; ++c) T[c] = 0.f;
-    for (int i = pl; i < n; i += 16) {
+    for (int i = pl; i < n; i += KLD_PL) {
       const float* row = ob + (size_t)s_list[i] * JMAX;
       const float dj = row[j];
       const float4* o4 = reinterpret_cast<const float4*>(row);
@@ -169,14 +171,14 @@ k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const i
     }
   }
   __syncthreads();
-  {
+  if (tid < JMAX * JMAX) {
     const int a = tid / JMAX, i = tid % JMAX;
     if (a < J && i < J) s_T[a][i] = s_T[a][i] / s_S[a];     // A[a][i] = E_a[d_i]
   }
   __syncthreads();
   const float n_terms = (float)counts[1];
   float esum = 0.f;
-  {
+  if (tid < JMAX * JMAX) {
     const int a = tid / JMAX, c = tid % JMAX;
     float cv = 0.f;
     if (a < J && c < J && a != c) {
@@ -212,7 +214,7 @@ k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const i
 #pragma unroll
     for (int c = 0; c < JMAX; ++c) kl[c] = s_kl[j][c];   // zero for c >= J, c == a, a >= J
     const float csa = s_cs[j], ra = s_r[j], lsea = s_lse[j];
-    for (int i0 = 0; i0 < n; i0 += 16) {
+    for (int i0 = 0; i0 < n; i0 += KLD_PL) {
       const int i = i0 + pl;
       const bool act = i < n;
       const int pidx = s_list[act ? i : 0];
@@ -421,7 +423,7 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
     dim3 grid(C, B);
     ADLM_CHECK_SUPPORTED((size_t)HW * sizeof(int) <= 200 * 1024, "feature map too large for the KLD kernel (h*w > 51200)");
     ADLM_CUDA(cudaFuncSetAttribute(k_kld, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)HW * sizeof(int))));
-    k_kld<<<grid, 256, (size_t)HW * sizeof(int), st>>>(ws.own, target, ws.hist, ws.cls_count, counts, HW, C,
+    k_kld<<<grid, KLD_THREADS, (size_t)HW * sizeof(int), st>>>(ws.own, target, ws.hist, ws.cls_count, counts, HW, C,
                                                     w_kld * grad_scale, want_grad ? ws.own_grad : nullptr, ws.accum);
     ADLM_LAUNCH_CHECK();
   }
