@@ -40,6 +40,18 @@ k_patch_class_mask(const uint8_t* __restrict__ labels, int H, int Wimg, const in
     const uint4* base = reinterpret_cast<const uint4*>(lab + (size_t)r0 * Wimg);
     auto consume = [&](int vec, const uint4 v) {
       const int cv = vec % vpr;
+      // label maps are piecewise constant: 16 equal labels need one bit and the patch range of the run
+      // (the column LUT is monotone with steps <= 1 when patches are at least one pixel wide, w <= Wimg)
+      if (w <= Wimg && v.y == v.x && v.z == v.x && v.w == v.x && v.x == (v.x & 0xffu) * 0x01010101u) {
+        const unsigned l = v.x & 0xffu;
+        if (l - 1u < 32u) {
+          const uint32_t bit = 1u << (l - 1u);
+          const int pj1 = __ldg(col_lut + cv * 16 + 15);
+          for (int pj = __ldg(col_lut + cv * 16); pj <= pj1; ++pj)
+            if ((smask[pj] & bit) == 0u) atomicOr(&smask[pj], bit);
+        }
+        return;
+      }
       const int4* lut4 = reinterpret_cast<const int4*>(col_lut + cv * 16);
       const uint32_t words[4] = {v.x, v.y, v.z, v.w};
       int cur = -1;

@@ -124,3 +124,28 @@ def test_push_full_resolution_image(prec):
     assert (ids == oidx).mean() >= 0.98
     same = ids == oidx
     assert np.array_equal(new_protos.cpu().numpy()[same], opatch[same].astype(np.float32))
+
+
+def test_push_single_pass_tf32_only_differs_in_near_ties():
+    """precision='tf32' (one TF32 pass) is NOT the default for push: its winners may differ from the fp32 argmin,
+    but only where the fp32 distances of the two candidates are within the TF32 error of each other."""
+    n_img, K, h, w, N, C, H, W = 3, 64, 33, 41, 190, 19, 264, 328
+    zn, Pn, _ = synth.head_inputs(n_img, K, h, w, N, C, seed=91)
+    labels = synth.block_labels(n_img, H, W, C, block=8, seed=92)
+    z, P = cuda(zn, Pn)
+    lab = torch.from_numpy(labels).cuda()
+    pc = proto_class(N, C)
+    exact = push.PushSearch(P, pc, precision="tf32x3")
+    exact.scan(z, lab, 0)
+    fast = push.PushSearch(P, pc, precision="tf32")
+    fast.scan(z, lab, 0)
+    d3, id3 = push.unpack(exact.packed.cpu().numpy())
+    d1, id1 = push.unpack(fast.packed.cpu().numpy())
+    assert np.array_equal(id3 >= 0, id1 >= 0)
+    found = id3 >= 0
+    assert np.allclose(d1[found], d3[found], atol=0.05)
+    dist = orc.l2_distances(zn, Pn)                                  # (n_img, N, h, w) fp32-class reference
+    flat = dist.transpose(1, 0, 2, 3).reshape(N, -1)
+    for j in np.nonzero(found & (id1 != id3))[0]:
+        assert flat[j, id1[j]] - flat[j, id3[j]] <= 0.05, f"prototype {j}: not a near-tie"
+    assert (id1 == id3)[found].mean() >= 0.8

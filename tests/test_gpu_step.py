@@ -159,3 +159,32 @@ def test_autograd_function_continues_into_the_features():
     assert torch.allclose(W.grad, res.dW / 5, rtol=1e-5, atol=1e-8)
     zd = z.detach()
     assert torch.allclose(pre.grad, res.dz / 5 * zd * (1 - zd), rtol=1e-4, atol=1e-9)
+
+
+@pytest.mark.parametrize("prec", ["tf32", "tf32x3"])
+def test_step_flat_gradient_buffer_and_optional_logits(prec):
+    """grads_out: dP / dW are views into one flat buffer (the data-parallel step reduces it with a single
+    collective); asking for logits / argmax must not change losses or gradients (tf32: CE is fused into the
+    forward kernel's epilogue and logits touch HBM only on request)."""
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    B, K, h, w, N, C = 3, 64, 33, 29, 190, 19
+    zn, Pn, Wn = synth.head_inputs(B, K, h, w, N, C, w_noise=0.1, seed=311)
+    z, P, W = cuda(zn, Pn, Wn)
+    target = torch.from_numpy(synth.block_labels(B, h, w, C, block=4, seed=312).astype(np.int32)).cuda()
+    pc = torch.arange(N, dtype=torch.int32, device="cuda") // (N // C)
+    plain = head.fused_step(z, P, W, target, pc, precision=prec)
+    flat = torch.full((N * K + C * N + 8,), float("nan"), device="cuda")
+    res = head.fused_step(z, P, W, target, pc, precision=prec, grads_out=flat, want_logits=True, want_argmax=True)
+    assert res.dP.data_ptr() == flat.data_ptr() and res.dW.data_ptr() == flat[N * K:].data_ptr()
+    # the KLD statistics and the CE sum accumulate with atomics (order varies between launches): not bit-equal
+    for got, want in ((res.dP, plain.dP), (res.dW, plain.dW), (res.dz, plain.dz)):
+        assert parity.rel_err(got.cpu().numpy(), want.cpu().numpy()) <= 1e-4
+    assert np.allclose(res.scalars.cpu().numpy(), plain.scalars.cpu().numpy(), rtol=1e-6)
+    assert bool(torch.isnan(flat[N * K + C * N:]).all())          # the tail belongs to the caller
+    ref = head.head_forward(z, P, W, precision=prec, want_dist=False, want_argmax=True)
+    assert torch.equal(res.logits, ref["logits"]) and torch.equal(res.argmax, ref["argmax"])
+    n_correct = int(((res.argmax.flatten() + 1) == target.flatten()).sum())
+    assert int(res.scalars[4]) == n_correct
+    with pytest.raises(ValueError):
+        head.fused_step(z, P, W, target, pc, precision=prec, grads_out=flat[:10])
