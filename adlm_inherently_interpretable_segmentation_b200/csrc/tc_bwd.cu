@@ -228,7 +228,11 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
       *reinterpret_cast<float4*>(dLk + ((size_t)c4 * TILE + wt) * 4) = make_float4(v[0], v[1], v[2], v[3]);
     }
     int lab = -1;
-    if (kld && valid) lab = p.target[m];
+    if (kld && valid) {
+      lab = p.target[m];
+      // pull the pixel's 64-byte line of own-class KLD gradients into L1 before the epilogue needs it
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(p.own_grad + (size_t)m * JMAX));
+    }
     const bool lab_ok = lab >= 0 && lab < 32;
     fence_async_smem();
     fence_before();
@@ -355,7 +359,9 @@ struct DpSmem {
   static __host__ __device__ size_t dlk(int Npad2, int C8) { return zk(Npad2, C8) + (size_t)KP * TILE * 4; }
   static __host__ __device__ size_t misc(int Npad2, int C8) { return dlk(Npad2, C8) + (size_t)C8 * TILE * 4; }
   // x2 [128] f32, lab [128] i32, img [128] i32, pix [128] i32, cs [2][2][128] f32, barriers
-  static __host__ __device__ size_t total(int Npad2, int C8) { return misc(Npad2, C8) + 128 * 16 + 512 * 4 + 128 + 512; }
+  // ... + own-class KLD gradients of the tile [128 px][16] f32 (cp.async by the builder warps)
+  static __host__ __device__ size_t ogs(int Npad2, int C8) { return misc(Npad2, C8) + 128 * 16 + 512 * 4 + 128 + 512; }
+  static __host__ __device__ size_t total(int Npad2, int C8) { return ogs(Npad2, C8) + 128 * 16 * 4; }
 };
 
 template <int KP, int NB, bool GENERIC>
@@ -379,6 +385,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
   uint64_t* bars = reinterpret_cast<uint64_t*>(misc + 2048 + 2048);
   uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 4);
   uint32_t* clsm = reinterpret_cast<uint32_t*>(misc + 2048 + 2048 + 64);   // [32 classes][4 words]: pixels of the tile
+  float* ogs = reinterpret_cast<float*>(smem + L::ogs(Npad2, C8));           // [128 px][16]: dL/d(own distances)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const bool kld = p.own_grad != nullptr;
@@ -467,6 +474,14 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
       if (it > 0) mbar_wait(bar_free, (uint32_t)(it - 1) & 1u);
       if (warp == 8) DP_PHASE(0, 2 + it * 8);
       clsm[cw] = 0u;
+      if (kld && valid) {
+        // the tile's own-class KLD gradients travel straight into shared memory while the operands are converted
+        const float* src = p.own_grad + (size_t)m * JMAX;
+        const uint32_t dst = smem_u32(ogs + cw * JMAX);
+#pragma unroll
+        for (int v = 0; v < JMAX / 4; ++v)
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst + v * 16), "l"(src + v * 4) : "memory");
+      }
       named_bar_sync(2, 128);
       const int mylab = (valid && kld) ? p.target[m] : -1;
       if (mylab >= 0 && mylab < 32) atomicOr(&clsm[mylab * 4 + (cw >> 5)], 1u << (cw & 31));
@@ -499,6 +514,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
       imgs[cw] = b;
       pixs[cw] = valid ? m - b * HW : 0;
       labs[cw] = valid ? mylab : -2;
+      asm volatile("cp.async.wait_all;" ::: "memory");
       fence_async_smem();
       mbar_arrive(bar_full);
       if (warp == 8) DP_PHASE(0, 3 + it * 8);
@@ -624,7 +640,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
             if (hit) {
 #pragma unroll
               for (int i = 0; i < 16; ++i)
-                if ((hit >> i) & 1u) gvv[i] += __ldg(p.own_grad + (size_t)(m0 + c0 + i) * JMAX + prk[blk]);
+                if ((hit >> i) & 1u) gvv[i] += ogs[(c0 + i) * JMAX + prk[blk]];
             }
 #pragma unroll
             for (int i = 0; i < 16; ++i) {

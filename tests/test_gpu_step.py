@@ -177,9 +177,10 @@ def test_step_flat_gradient_buffer_and_optional_logits(prec):
     flat = torch.full((N * K + C * N + 8,), float("nan"), device="cuda")
     res = head.fused_step(z, P, W, target, pc, precision=prec, grads_out=flat, want_logits=True, want_argmax=True)
     assert res.dP.data_ptr() == flat.data_ptr() and res.dW.data_ptr() == flat[N * K:].data_ptr()
-    # the KLD statistics and the CE sum accumulate with atomics (order varies between launches): not bit-equal
+    # the KLD statistics and the CE sum accumulate with atomics (order varies between launches): not bit-equal,
+    # and in tf32 a last-bit change of a KLD gradient can flip the TF32 rounding of an MMA operand (2^-11 of one term)
     for got, want in ((res.dP, plain.dP), (res.dW, plain.dW), (res.dz, plain.dz)):
-        assert parity.rel_err(got.cpu().numpy(), want.cpu().numpy()) <= 1e-4
+        assert parity.rel_err(got.cpu().numpy(), want.cpu().numpy()) <= (1e-3 if prec == "tf32" else 1e-4)
     assert np.allclose(res.scalars.cpu().numpy(), plain.scalars.cpu().numpy(), rtol=1e-6)
     assert bool(torch.isnan(flat[N * K + C * N:]).all())          # the tail belongs to the caller
     ref = head.head_forward(z, P, W, precision=prec, want_dist=False, want_argmax=True)
