@@ -80,6 +80,10 @@ bool head_fwd_fuses_ce(const HeadShape& s, int prec_mode) {
   return prec_mode == ADLM_PREC_TF32 && s.K <= 64 && s.N <= 224 && s.C <= 32;
 }
 
+bool head_bwd_fuses_finalize(const HeadShape& s, int prec_mode, const float* dP, const float* dW) {
+  return prec_mode == ADLM_PREC_TF32 && s.K <= 64 && s.N <= 192 && s.C <= 32 && dW != nullptr && dP != nullptr;
+}
+
 size_t head_bwd_workspace_bytes(int prec_mode, int K, int N) {
   if (prec_mode != ADLM_PREC_TF32 || K > 64 || N > 192) return 0;
   return tc_bwd_workspace_bytes(K, N);

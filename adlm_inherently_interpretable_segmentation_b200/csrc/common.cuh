@@ -92,6 +92,13 @@ struct HeadShape {
 };
 
 // optional extras of the fused step
+struct StepFinalize {
+  double* scalars = nullptr;             // [8] out; null = not requested
+  const int32_t* counts = nullptr;       // [2] loss normalisers
+  const double* accum = nullptr;         // [4] CE sum, correct, KLD sum
+  float w_ce = 0.f, w_kld = 0.f, w_l1 = 0.f, grad_scale = 1.f;
+};
+
 struct StepExtras {
   const int32_t* target = nullptr;       // [B,HW] labels (un-shifted)
   const int32_t* proto_class = nullptr;  // [N]
@@ -105,9 +112,13 @@ struct StepExtras {
   double* ce_accum = nullptr;            // [0] += loss sum, [1] += correct
   float ce_scale = 0.f;                  // w_ce * grad_scale
   int ignore_void = 0;
+  // fused step epilogue (L1 term of dW, L1 value, the 8 scalars; module.py:213-222) inside the partials
+  // reduction of the tensor-core backward — callers must check head_bwd_fuses_finalize()
+  StepFinalize fin;
 };
 // true when head_fwd_dispatch(prec_mode, shape) runs the kernel that honours the ce_* extras
 bool head_fwd_fuses_ce(const HeadShape& s, int prec_mode);
+bool head_bwd_fuses_finalize(const HeadShape& s, int prec_mode, const float* dP, const float* dW);
 
 int simt_head_fwd(const HeadShape& s, const float* z, const float* P, const float* W,
                   float* logits, float* dist, float* sim, int32_t* argmax,

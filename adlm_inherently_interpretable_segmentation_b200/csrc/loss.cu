@@ -272,12 +272,22 @@ k_step_prepare(const int32_t* __restrict__ target, const int32_t* __restrict__ p
   for (int c = tid; c < C; c += 1024) s_cls[c] = 0;
   if (tid == 0) { s_valid = 0; s_terms = 0; }
   __syncthreads();
-  for (int n = tid; n < N; n += 1024) {
-    const int c = proto_class[n];
-    if (c >= 0 && c < C) atomicAdd(&s_cls[c], 1);
-    int r = 0;
-    for (int i = 0; i < n; ++i) r += (proto_class[i] == c);
-    rank[n] = r;
+  // rank of a prototype inside its class: one warp-ballot pass per 32 candidates over a shared copy
+  __shared__ int s_pc[1024];
+  for (int n0 = 0; n0 < N; n0 += 1024) {
+    const int n = n0 + tid;
+    const int c = n < N ? proto_class[n] : -2;
+    __syncthreads();
+    s_pc[tid] = c;
+    __syncthreads();
+    if (n < N) {
+      if (c >= 0 && c < C) atomicAdd(&s_cls[c], 1);
+      int r = 0;
+      for (int i = 0; i < tid; ++i) r += (s_pc[i] == c);
+      if (n0 > 0)
+        for (int i = 0; i < n0; ++i) r += (proto_class[i] == c);
+      rank[n] = r;
+    }
   }
   __syncthreads();
   int valid = 0, terms = 0;
@@ -427,17 +437,27 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
                                                     w_kld * grad_scale, want_grad ? ws.own_grad : nullptr, ws.accum);
     ADLM_LAUNCH_CHECK();
   }
+  bool fin_fused = false;
   if (want_grad) {
     StepExtras exb = ex;
     exb.own_dist = nullptr;
     exb.own_grad = ws.own_grad;
+    if (head_bwd_fuses_finalize(s, prec_mode, dP, dW)) {
+      exb.fin.scalars = scalars;
+      exb.fin.counts = counts;
+      exb.fin.accum = ws.accum;
+      exb.fin.w_ce = w_ce; exb.fin.w_kld = w_kld; exb.fin.w_l1 = w_l1; exb.fin.grad_scale = grad_scale;
+      fin_fused = true;
+    }
     if ((rc = head_bwd_dispatch(s, prec_mode, z, P, W, ws.dlogits, nullptr, nullptr, dz, dP, dW, exb, ws.bwd_scratch,
                                 ws.bwd_scratch_bytes, st)) != ADLM_OK)
       return rc;
   }
-  k_finalize<<<1, 1024, 0, st>>>(W, proto_class, C, N, w_ce, w_kld, w_l1, grad_scale, counts, ws.accum,
-                                dW, scalars);
-  ADLM_LAUNCH_CHECK();
+  if (!fin_fused) {
+    k_finalize<<<1, 1024, 0, st>>>(W, proto_class, C, N, w_ce, w_kld, w_l1, grad_scale, counts, ws.accum,
+                                  dW, scalars);
+    ADLM_LAUNCH_CHECK();
+  }
   return ADLM_OK;
 }
 

@@ -702,15 +702,17 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
   if (warp == 12) tmem_dealloc(tmem_base, 512);
 }
 
-// dP[n][k] = sum over CTAs; dW[c][n] = sum over CTAs (stored [n][32] per CTA)
+// dP[n][k] = sum over CTAs; dW[c][n] = sum over CTAs (stored [n][32] per CTA).  With fin.scalars set this is
+// also the step's epilogue: dW += w_l1 * sign(W) off the class identity, block 0 writes the eight scalars.
 __global__ void __launch_bounds__(256)
 k_reduce_partials(const float* __restrict__ partials, int n_parts, int Npad2, int KP, int N, int K,
-                  int C, float* __restrict__ dP, float* __restrict__ dW) {
+                  int C, float* __restrict__ dP, float* __restrict__ dW, const float* __restrict__ W,
+                  const int32_t* __restrict__ proto_class, const StepFinalize fin) {
   // 4 threads per output element, each sums a quarter of the per-CTA partials
   const size_t per = (size_t)Npad2 * KP + (size_t)Npad2 * 32;
   const int total = N * K + C * N;
   const int idx = (blockIdx.x * 256 + threadIdx.x) >> 2, q4 = threadIdx.x & 3;
-  float a = 0.f;
+  float a = 0.f, extra = 0.f;
   float* dst = nullptr;
   if (idx < total) {
     size_t off;
@@ -722,6 +724,10 @@ k_reduce_partials(const float* __restrict__ partials, int n_parts, int Npad2, in
       const int j = idx - N * K, c = j / N, n = j - c * N;
       off = (size_t)Npad2 * KP + (size_t)n * 32 + c;
       dst = dW ? dW + j : nullptr;
+      if (fin.scalars != nullptr && q4 == 0 && dst != nullptr && proto_class[n] != c) {
+        const float w = W[j];
+        extra = fin.w_l1 * fin.grad_scale * ((w > 0.f) ? 1.f : ((w < 0.f) ? -1.f : 0.f));
+      }
     }
     if (dst != nullptr) {
       float a0 = 0.f, a1 = 0.f;
@@ -736,7 +742,35 @@ k_reduce_partials(const float* __restrict__ partials, int n_parts, int Npad2, in
   }
   a += __shfl_xor_sync(0xffffffffu, a, 1);
   a += __shfl_xor_sync(0xffffffffu, a, 2);
-  if (q4 == 0 && dst != nullptr) *dst = a;
+  if (q4 == 0 && dst != nullptr) *dst = a + extra;
+
+  if (fin.scalars != nullptr && blockIdx.x == 0) {
+    __shared__ float s_part[8];
+    float l1 = 0.f;
+    for (int i = threadIdx.x; i < C * N; i += 256) {
+      const int c = i / N, n = i - c * N;
+      if (proto_class[n] != c) l1 += fabsf(W[i]);
+    }
+    l1 = warp_sum(l1);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = l1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double tot = 0.0;
+      for (int w = 0; w < 8; ++w) tot += (double)s_part[w];
+      const double n_valid = (double)fin.counts[0], n_terms = (double)fin.counts[1];
+      const double ce = n_valid > 0 ? fin.accum[0] / n_valid
+                                     : __longlong_as_double(0x7ff8000000000000LL);  // empty mean = NaN, as torch
+      const double kld = n_terms > 0 ? fin.accum[2] / n_terms : 0.0;
+      fin.scalars[0] = (double)fin.w_ce * ce + (double)fin.w_kld * kld + (double)fin.w_l1 * tot;
+      fin.scalars[1] = ce;
+      fin.scalars[2] = kld;
+      fin.scalars[3] = tot;
+      fin.scalars[4] = fin.accum[1];
+      fin.scalars[5] = n_valid;
+      fin.scalars[6] = n_terms;
+      fin.scalars[7] = 0.0;
+    }
+  }
 }
 
 int g_sms = 0;
@@ -755,7 +789,8 @@ bool tc_bwd_supported(const HeadShape& s, int prec_mode) {
 }
 
 template <int KP>
-int launch_bwd(TcBwdParams prm, float* dP, float* dW, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+int launch_bwd(TcBwdParams prm, float* dP, float* dW, const StepFinalize& fin, void* workspace, size_t workspace_bytes,
+               cudaStream_t st) {
   const int grid = prm.num_tiles < sm_count() ? prm.num_tiles : sm_count();
   KernelTimer timer(ADLM_K_HEAD_BWD, st);
   if (prm.dz != nullptr) {
@@ -791,7 +826,8 @@ int launch_bwd(TcBwdParams prm, float* dP, float* dW, void* workspace, size_t wo
 #undef ADLM_DP_LAUNCH
     ADLM_LAUNCH_CHECK();
     const int total = prm.N * prm.K + prm.C * prm.N;
-    k_reduce_partials<<<(total * 4 + 255) / 256, 256, 0, st>>>(prm.partials, grid, Npad2, KP, prm.N, prm.K, prm.C, dP, dW);
+    k_reduce_partials<<<(total * 4 + 255) / 256, 256, 0, st>>>(prm.partials, grid, Npad2, KP, prm.N, prm.K, prm.C, dP, dW,
+                                                               prm.W, prm.proto_class, fin);
     ADLM_LAUNCH_CHECK();
   }
   return ADLM_OK;
@@ -830,8 +866,8 @@ int tc_head_bwd(const HeadShape& s, int prec_mode, const float* z, const float* 
   prm.C8 = (s.C + 7) & ~7;
   prm.M = (long long)s.B * s.HW;
   prm.num_tiles = (int)((prm.M + TILE - 1) / TILE);
-  if (s.K <= 32) return launch_bwd<32>(prm, dP, dW, workspace, workspace_bytes, st);
-  return launch_bwd<64>(prm, dP, dW, workspace, workspace_bytes, st);
+  if (s.K <= 32) return launch_bwd<32>(prm, dP, dW, ex.fin, workspace, workspace_bytes, st);
+  return launch_bwd<64>(prm, dP, dW, ex.fin, workspace, workspace_bytes, st);
 }
 
 }  // namespace adlm

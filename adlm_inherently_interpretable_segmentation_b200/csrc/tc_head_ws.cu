@@ -251,6 +251,13 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
       const int b = t & 1, jb = t >> 1;
       const int tile = tile_of(t);
       const int m = tile * TILE + row;
+      // label and CE normaliser travel while the last-layer MMA finishes
+      int tg = -1;
+      float ce_sc = 0.f;
+      if (p.ce_accum != nullptr) {
+        if (m < Mi) tg = p.target[m];
+        ce_sc = p.ce_scale / (float)p.ce_counts[0];
+      }
       mbar_wait(bar(B_D2FULL + b), (uint32_t)jb & 1u);
       fence_after();
       const uint32_t d2 = tD2 + b * Cpad + lane_field;
@@ -298,7 +305,6 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
       if (p.ce_accum != nullptr) {
         // cross entropy over the non-void patches (module.py:156-165), accuracy (:210-211), and
         // dlogits = w_ce * grad_scale / n_patches * (softmax - onehot), all from the registers
-        int tg = (m < Mi) ? p.target[m] : -1;
         bool ok;
         if (p.ignore_void) { ok = tg >= 1 && tg <= C; tg -= 1; }
         else               { ok = tg >= 0 && tg < C; }
@@ -314,7 +320,7 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
           const float lse = bv + __logf(se);
           loss = lse - lt;
           hit = (best == tg) ? 1.f : 0.f;
-          const float sc = p.ce_scale / (float)p.ce_counts[0];
+          const float sc = ce_sc;
 #pragma unroll
           for (int c = 0; c < 32; ++c)
             if (c < C) lg[c] = sc * (__expf(lg[c] - lse) - (c == tg ? 1.f : 0.f));
