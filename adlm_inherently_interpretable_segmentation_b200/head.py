@@ -173,7 +173,7 @@ class _StepResult(dict):
 def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
                weights=(1.0, 0.25, 1e-4), grad_scale=1.0, eps=1e-4, precision=None,
                need_grads=True, want_logits=False, want_argmax=False, workspace=None, global_counts=None,
-               grads_out=None):
+               grads_out=None, dz_out=None):
     """One C-ABI call for module.py:137-222 + :236 on given features.
 
     z (B,K,h,w); target (B,h,w) integer labels already resized to the feature map (dataset.py:23-31);
@@ -182,7 +182,8 @@ def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
       dz, dP (shaped like prototypes), dW (None when need_grads is False), logits, argmax (optional).
     Gradients are those of (loss * grad_scale).  global_counts: (2,) int32 CUDA tensor overriding the
     CE / KLD normalisers (data-parallel shards, see parallel.py), or None.  grads_out: optional flat fp32
-    CUDA buffer with at least N*K + C*N elements; dP and dW are then views into it ([dP | dW], one collective)."""
+    CUDA buffer with at least N*K + C*N elements; dP and dW are then views into it ([dP | dW], one collective).
+    dz_out: optional preallocated contiguous fp32 CUDA tensor shaped like z that receives dz (pipelined callers)."""
     lib = _lib.load()
     _check_cuda_f32("conv_features", z)
     _check_cuda_f32("prototype_vectors", prototypes)
@@ -206,7 +207,12 @@ def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
         if workspace is None or workspace.numel() < need:
             workspace = torch.empty(need, device=dev, dtype=torch.uint8)
         scalars = torch.empty(_lib.STEP_NSCALARS, device=dev, dtype=torch.float64)
-        dz = torch.empty_like(z) if need_grads else None
+        if need_grads and dz_out is not None:
+            if dz_out.shape != z.shape or dz_out.dtype != torch.float32 or not dz_out.is_cuda or not dz_out.is_contiguous():
+                raise ValueError("dz_out must be a contiguous CUDA float32 tensor shaped like z")
+            dz = dz_out
+        else:
+            dz = torch.empty_like(z) if need_grads else None
         if need_grads and grads_out is not None:
             if grads_out.dtype != torch.float32 or not grads_out.is_cuda or grads_out.numel() < N * K + C * N:
                 raise ValueError("grads_out must be a CUDA float32 buffer with >= N*K + C*N elements")

@@ -93,7 +93,7 @@ def _additive_mask(device, rank, replicated=(3, 5, 6)):
 
 
 def dp_fused_step(ppnet_or_params, z, target, proto_class, ignore_void=True, weights=(1.0, 0.25, 1e-4),
-                  grad_scale=1.0, precision=None, group=None, workspace=None):
+                  grad_scale=1.0, precision=None, group=None, workspace=None, dz_out=None):
     """Data-parallel fused step on this rank's image shard.  Returns the head.fused_step result with dP, dW
     and scalars already reduced (identical on every rank, equal to the single-GPU step on the whole batch);
     dz is the gradient for this rank's features only (it feeds the local backbone backward).
@@ -106,7 +106,7 @@ def dp_fused_step(ppnet_or_params, z, target, proto_class, ignore_void=True, wei
     C = weight.shape[0]
     if size == 1:
         return head.fused_step(z, prototypes, weight, target, proto_class, ignore_void=ignore_void, weights=weights,
-                               grad_scale=grad_scale, precision=precision, workspace=workspace)
+                               grad_scale=grad_scale, precision=precision, workspace=workspace, dz_out=dz_out)
     counts = head.step_counts(target, proto_class, C, ignore_void, workspace=workspace, K=z.shape[1])
     allreduce_counts(counts, group)
     w_ce, w_kld, w_l1 = weights
@@ -114,7 +114,7 @@ def dp_fused_step(ppnet_or_params, z, target, proto_class, ignore_void=True, wei
     flat = torch.empty(n_grad + 8, device=z.device, dtype=torch.float32)
     res = head.fused_step(z, prototypes, weight, target, proto_class, ignore_void=ignore_void,
                           weights=(w_ce, w_kld, w_l1 / size), grad_scale=grad_scale, precision=precision,
-                          global_counts=counts, workspace=workspace, grads_out=flat)
+                          global_counts=counts, workspace=workspace, grads_out=flat, dz_out=dz_out)
     flat[n_grad:].copy_(res.scalars * _additive_mask(z.device, rank))
     dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
     res["scalars"] = flat[n_grad:].to(torch.float64)

@@ -11,7 +11,8 @@ DeepLabv2/ResNet-101 backbone is out of scope (BASELINE north_star) and is not t
 Prints ONE JSON line (rank 0):
   value      Mpixels/s over all ranks, inputs resident in HBM, CUDA-event timed, max over ranks
   e2e        same metric through the public C-ABI-backed API with HOST buffers: pinned H2D of the step's
-             features + labels and D2H of its results (loss scalars, dz, dP, dW) inside the timed region
+             features + labels and D2H of its results (loss scalars, dz, dP, dW) inside the timed region,
+             double-buffered over three streams so both PCIe directions overlap the kernels
   roofline   dominant kernel's achieved HBM GB/s (algorithmic bytes / CUDA-event launch time) vs MEASURED_PEAKS
   cpu_baseline  the reference's operator sequence (oracle/torch_port.py) on this box's host cores
   push       secondary metric of BASELINE.json: push imgs/s over a resident synthetic shard
@@ -244,7 +245,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, n, sampler=None):
+    def timed(fn, n, sampler=None, drain=None):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         ctx = sampler if sampler is not None else _Null()
@@ -252,6 +253,8 @@ def main():
             e0.record()
             for i in range(n):
                 fn(i)
+            if drain is not None:
+                drain()
             e1.record()
             barrier()
         ms = e0.elapsed_time(e1)
@@ -287,38 +290,71 @@ def main():
                 "peak_source": pk["source"], "kernels": kern,
                 "share_of_step": kern[dom]["avg_ms"] / (ms / K_steps)}
 
-    # ---- e2e leg: host buffers in, host buffers out, through the public API
-    n_host = 4
+    # ---- e2e leg: host buffers in, host buffers out, through the public API.  Double-buffered over three streams
+    # (H2D | kernels | D2H) so the two PCIe directions and the kernels overlap; the caller receives step i-2's
+    # results on the host while step i is issued.  Every step's copies are inside the timed region.
+    n_host, NB = 4, 3
     hz = [zs[i].cpu().pin_memory() for i in range(n_host)]
     ht = [tgts[i].cpu().pin_memory() for i in range(n_host)]
-    dz_h = torch.empty((B, K, h, w), dtype=torch.float32).pin_memory()
-    dP_h = torch.empty((N, K), dtype=torch.float32).pin_memory()
-    dW_h = torch.empty((C, N), dtype=torch.float32).pin_memory()
-    sc_h = torch.empty(_lib.STEP_NSCALARS, dtype=torch.float64).pin_memory()
-    z_d = torch.empty((B, K, h, w), device=dev, dtype=torch.float32)
-    t_d = torch.empty((B, h, w), device=dev, dtype=torch.int32)
+    n_grad = N * K + C * N
+    dz_h = [torch.empty((B, K, h, w), dtype=torch.float32).pin_memory() for _ in range(NB)]
+    g_h = [torch.empty(n_grad, dtype=torch.float32).pin_memory() for _ in range(NB)]
+    sc_h = [torch.empty(_lib.STEP_NSCALARS, dtype=torch.float64).pin_memory() for _ in range(NB)]
+    z_d = [torch.empty((B, K, h, w), device=dev, dtype=torch.float32) for _ in range(NB)]
+    t_d = [torch.empty((B, h, w), device=dev, dtype=torch.int32) for _ in range(NB)]
+    dz_d = [torch.empty((B, K, h, w), device=dev, dtype=torch.float32) for _ in range(NB)]
+    g_d = [torch.empty(n_grad, device=dev, dtype=torch.float32) for _ in range(NB)]
+    sc_d = [torch.empty(_lib.STEP_NSCALARS, device=dev, dtype=torch.float64) for _ in range(NB)]
     h2d = hz[0].numel() * 4 + ht[0].numel() * 4
-    d2h = dz_h.numel() * 4 + dP_h.numel() * 4 + dW_h.numel() * 4 + sc_h.numel() * 8
+    d2h = dz_h[0].numel() * 4 + n_grad * 4 + _lib.STEP_NSCALARS * 8
+    cur = torch.cuda.current_stream()
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+    ev_in = [torch.cuda.Event() for _ in range(NB)]
+    ev_cmp = [torch.cuda.Event() for _ in range(NB)]
+    ev_out = [torch.cuda.Event() for _ in range(NB)]
+    for b in range(NB):
+        ev_cmp[b].record(cur)
+        ev_out[b].record(cur)
 
     def e2e_step(i):
-        j = i % n_host
-        z_d.copy_(hz[j], non_blocking=True)
-        t_d.copy_(ht[j], non_blocking=True)
+        j, b = i % n_host, i % NB
+        with torch.cuda.stream(s_in):
+            s_in.wait_event(ev_cmp[b])                 # the kernels of step i-NB have consumed z_d[b]
+            z_d[b].copy_(hz[j], non_blocking=True)
+            t_d[b].copy_(ht[j], non_blocking=True)
+            ev_in[b].record(s_in)
+        cur.wait_event(ev_in[b])
+        cur.wait_event(ev_out[b])                      # the D2H of step i-NB has drained dz_d[b] / g_d[b]
         if world > 1:
-            r = parallel.dp_fused_step((P, Wt), z_d, t_d, pc, weights=WEIGHTS, precision=prec, workspace=ws)
+            r = parallel.dp_fused_step((P, Wt), z_d[b], t_d[b], pc, weights=WEIGHTS, precision=prec, workspace=ws,
+                                       dz_out=dz_d[b])
+            g_d[b][:N * K].copy_(r.dP.reshape(-1))
+            g_d[b][N * K:].copy_(r.dW.reshape(-1))
         else:
-            r = head.fused_step(z_d, P, Wt, t_d, pc, weights=WEIGHTS, precision=prec, workspace=ws)
-        dz_h.copy_(r.dz, non_blocking=True)
-        dP_h.copy_(r.dP.reshape(N, K), non_blocking=True)
-        dW_h.copy_(r.dW, non_blocking=True)
-        sc_h.copy_(r.scalars, non_blocking=True)
-        torch.cuda.current_stream().synchronize()      # the caller holds the step's results on the host
+            r = head.fused_step(z_d[b], P, Wt, t_d[b], pc, weights=WEIGHTS, precision=prec, workspace=ws,
+                                dz_out=dz_d[b], grads_out=g_d[b])
+        sc_d[b].copy_(r.scalars)
+        ev_cmp[b].record(cur)
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(ev_cmp[b])
+            dz_h[b].copy_(dz_d[b], non_blocking=True)
+            g_h[b].copy_(g_d[b], non_blocking=True)
+            sc_h[b].copy_(sc_d[b], non_blocking=True)
+            ev_out[b].record(s_out)
+        ev_out[(i - 2) % NB].synchronize()             # the caller now holds step i-2's results on the host
 
-    for i in range(3):
+    def e2e_drain():
+        for b in range(NB):
+            cur.wait_event(ev_out[b])                  # the closing event sees the last D2H
+
+    for i in range(6):
         e2e_step(i)
-    ms_e2e = timed(e2e_step, K_steps)
+    ms_e2e = timed(e2e_step, K_steps, drain=e2e_drain)
+    if not all(bool(torch.isfinite(x).all()) for x in sc_h + dz_h):
+        raise RuntimeError("e2e leg: non-finite results on the host")
     e2e = {"value": world * M * K_steps / (ms_e2e * 1e-3) / 1e6, "unit": "Mpixels/s",
-           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / K_steps}
+           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / K_steps,
+           "pipeline": "3 buffers, 3 streams (H2D | kernels | D2H); results of step i-2 are on the host when step i has been issued"}
 
     # ---- secondary metric: push imgs/s over a resident synthetic shard (configs[2] per-GPU slice)
     push_res = None
