@@ -18,7 +18,8 @@ MAX_PROTOS_PER_CLASS = 16
 MAX_PUSH_CLASSES = 32
 STEP_NSCALARS = 8
 PUSH_NONE = 0x7FFFFFFFFFFFFFFF
-ABI_VERSION = 4
+ABI_VERSION = 5
+DP_MAX_WORLD = 16
 
 # name -> (restype, argtypes); kept next to include/adlm_head.h (tests check they agree)
 SIGNATURES = {
@@ -48,6 +49,21 @@ SIGNATURES = {
     "adlm_push_gather": (c_int, [c_void_p, c_int, c_int, c_int, c_longlong, c_void_p, c_int,
                                  c_void_p, c_void_p]),
 }
+
+
+
+class DpComm(ctypes.Structure):
+    """adlm_dp_comm (include/adlm_head.h)"""
+    _fields_ = [("rank", c_int), ("world", c_int), ("seq", c_ulonglong), ("peers", ctypes.POINTER(c_void_p))]
+
+
+SIGNATURES["adlm_dp_exchange_bytes"] = (c_size_t, [c_int, c_int, c_int, c_int])
+SIGNATURES["adlm_dp_exchange_layout"] = (c_int, [c_int, c_int, c_int, c_int, c_void_p])
+SIGNATURES["adlm_step_fwd_bwd_dp"] = (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int,
+                                              c_float, c_int, c_void_p, c_void_p, c_int,
+                                              c_float, c_float, c_float, c_float,
+                                              c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                              c_void_p, c_void_p, c_size_t, ctypes.POINTER(DpComm), c_void_p])
 
 _lib = None
 

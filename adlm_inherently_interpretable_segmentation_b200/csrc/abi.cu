@@ -177,7 +177,57 @@ int adlm_step_fwd_bwd(const float* z, int B, int K, int HW, const float* P, cons
   HeadShape s{B, K, HW, N, C, eps, ADLM_ACT_LOG};
   return step_fwd_bwd_impl(s, prec_mode, z, P, W, target, proto_class, ignore_void, w_ce, w_kld, w_l1,
                            grad_scale, global_counts, logits_out, argmax_out, dz, dP, dW, scalars, workspace,
-                           (cudaStream_t)stream);
+                           nullptr, (cudaStream_t)stream);
+}
+
+size_t adlm_dp_exchange_bytes(int K, int N, int C, int world) {
+  if (K <= 0 || N <= 0 || C <= 0 || world <= 0 || world > ADLM_DP_MAX_WORLD) return 0;
+  return dp_layout(K, N, C, world).total;
+}
+
+int adlm_dp_exchange_layout(int K, int N, int C, int world, size_t* out8) {
+  ADLM_CHECK_ARG(out8 != nullptr, "null pointer argument");
+  ADLM_CHECK_ARG(K > 0 && N > 0 && C > 0 && world > 0 && world <= ADLM_DP_MAX_WORLD, "bad size");
+  const DpLayout l = dp_layout(K, N, C, world);
+  out8[0] = l.cnt; out8[1] = l.cflag; out8[2] = l.acc; out8[3] = l.gflag; out8[4] = l.grad; out8[5] = l.total;
+  out8[6] = (size_t)l.n_grad_pad; out8[7] = (size_t)l.n_blocks;
+  return ADLM_OK;
+}
+
+int adlm_step_fwd_bwd_dp(const float* z, int B, int K, int HW, const float* P, const float* W, int N, int C,
+                         float eps, int prec_mode, const int32_t* target, const int32_t* proto_class,
+                         int ignore_void, float w_ce, float w_kld, float w_l1, float grad_scale,
+                         float* logits_out, int32_t* argmax_out, float* dz, float* dP, float* dW,
+                         double* scalars, void* workspace, size_t workspace_bytes, const adlm_dp_comm* comm,
+                         void* stream) {
+  int rc = check_shape(__func__, B, K, HW, N, C);
+  if (rc != ADLM_OK) return rc;
+  ADLM_CHECK_ARG(z && P && W && target && proto_class && scalars && workspace && comm, "null pointer argument");
+  ADLM_CHECK_ARG(comm->peers != nullptr, "comm->peers is null");
+  ADLM_CHECK_ARG(comm->world >= 1 && comm->world <= ADLM_DP_MAX_WORLD, "comm->world outside [1, ADLM_DP_MAX_WORLD]");
+  ADLM_CHECK_ARG(comm->rank >= 0 && comm->rank < comm->world, "comm->rank outside [0, world)");
+  ADLM_CHECK_ARG(comm->seq >= 1, "comm->seq starts at 1");
+  ADLM_CHECK_ARG(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  if (workspace_bytes < step_workspace_bytes(B, K, HW, N, C)) {
+    set_error("%s: workspace too small (%zu < %zu)", __func__, workspace_bytes, step_workspace_bytes(B, K, HW, N, C));
+    return ADLM_E_WORKSPACE;
+  }
+  DpComm cm;
+  cm.rank = comm->rank;
+  cm.world = comm->world;
+  // the flags hold the low 32 bits of the counter; 0 is the buffers' initial state, so it is skipped
+  cm.seq = (unsigned int)(comm->seq & 0xffffffffull);
+  if (cm.seq == 0u) cm.seq = 0x80000000u | (unsigned int)(comm->seq & 1ull);
+  if ((cm.seq & 1u) != (unsigned int)(comm->seq & 1ull)) cm.seq ^= 1u;
+  for (int r = 0; r < cm.world; ++r) {
+    ADLM_CHECK_ARG(comm->peers[r] != nullptr && ((uintptr_t)comm->peers[r] & 255) == 0,
+                   "comm->peers[r] must be non-null and 256-byte aligned");
+    cm.peer[r] = static_cast<char*>(comm->peers[r]);
+  }
+  HeadShape s{B, K, HW, N, C, eps, ADLM_ACT_LOG};
+  return step_fwd_bwd_impl(s, prec_mode, z, P, W, target, proto_class, ignore_void, w_ce, w_kld, w_l1,
+                           grad_scale, nullptr, logits_out, argmax_out, dz, dP, dW, scalars, workspace,
+                           &cm, (cudaStream_t)stream);
 }
 
 int adlm_step_counts(const int32_t* target, int B, int HW, const int32_t* proto_class, int N, int C,

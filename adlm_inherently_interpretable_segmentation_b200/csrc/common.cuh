@@ -91,12 +91,67 @@ struct HeadShape {
   int act_mode;
 };
 
+// ---- data-parallel exchange over peer-mapped memory (NVLink / NVSwitch) -----------------------
+// Every rank owns one exchange buffer that all ranks of the node have mapped (adlm_dp_comm.peers).  A rank
+// publishes by storing into slot [parity][its rank] of EVERY peer's buffer, then release-storing the step's
+// sequence number into the matching flag; a consumer spins (acquire) on the flags in its OWN buffer and sums
+// the slots in rank order, so every rank obtains bit-identical totals.  Two parities: a rank can be at most
+// one step ahead of a peer (it needs the peer's counts of step s+1 to get past the prologue of step s+1, and
+// those are published after the peer's step s has drained), so slot parity s&1 is never overwritten early.
+constexpr int DP_MAX_WORLD = ADLM_DP_MAX_WORLD;
+struct DpComm {
+  int rank = 0, world = 1;
+  unsigned int seq = 0;                  // 0 = exchange disabled
+  char* peer[DP_MAX_WORLD] = {};
+};
+struct DpLayout {                        // byte offsets inside one rank's exchange buffer
+  size_t cnt, cflag, acc, gflag, grad, total;
+  int n_grad, n_grad_pad, n_blocks;
+};
+__host__ __device__ inline int dp_reduce_blocks(int K, int N, int C) { return ((N * K + C * N) * 4 + 255) / 256; }
+__host__ __device__ inline DpLayout dp_layout(int K, int N, int C, int world) {
+  DpLayout l;
+  auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+  l.n_grad = N * K + C * N;
+  l.n_grad_pad = (l.n_grad + 63) / 64 * 64;
+  l.n_blocks = dp_reduce_blocks(K, N, C);
+  size_t off = 0;
+  l.cnt = off;   off += up((size_t)2 * world * 2 * sizeof(int));            // [2][W][2] int32 loss normalisers
+  l.cflag = off; off += up((size_t)2 * world * sizeof(unsigned int));      // [2][W] u32
+  l.acc = off;   off += up((size_t)2 * world * 4 * sizeof(double));        // [2][W][4] f64 CE / correct / KLD sums
+  l.gflag = off; off += up((size_t)2 * world * l.n_blocks * sizeof(unsigned int));  // [2][W][n_blocks] u32
+  l.grad = off;  off += up((size_t)2 * world * l.n_grad_pad * sizeof(float));      // [2][W][n_grad_pad] f32
+  l.total = off;
+  return l;
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// bounded spin (~3 s at 2 GHz): a dead peer turns into NaN results instead of a hung GPU
+__device__ __forceinline__ bool dp_wait_flag(const unsigned int* p, unsigned int v) {
+  const long long t0 = clock64();
+  while (ld_acquire_sys(p) != v) {
+    if (clock64() - t0 > 6000000000LL) return false;
+    __nanosleep(40);
+  }
+  return true;
+}
+#endif
+
 // optional extras of the fused step
 struct StepFinalize {
   double* scalars = nullptr;             // [8] out; null = not requested
   const int32_t* counts = nullptr;       // [2] loss normalisers
-  const double* accum = nullptr;         // [4] CE sum, correct, KLD sum
+  const double* accum = nullptr;         // [4] CE sum, correct, KLD sum, exchange time-outs
   float w_ce = 0.f, w_kld = 0.f, w_l1 = 0.f, grad_scale = 1.f;
+  DpComm comm;                           // comm.seq != 0: dP/dW/sums are exchanged with the peers in the same kernel
+  DpLayout lay = {};
 };
 
 struct StepExtras {
@@ -143,7 +198,7 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
                       const int32_t* target, const int32_t* proto_class, int ignore_void,
                       float w_ce, float w_kld, float w_l1, float grad_scale, const int32_t* global_counts,
                       float* logits_out, int32_t* argmax_out, float* dz, float* dP, float* dW,
-                      double* scalars, void* workspace, cudaStream_t st);
+                      double* scalars, void* workspace, const DpComm* comm, cudaStream_t st);
 int step_counts_impl(const int32_t* target, int B, int HW, const int32_t* proto_class, int N, int C,
                      int ignore_void, int32_t* counts_out, void* workspace, cudaStream_t st);
 

@@ -245,7 +245,8 @@ __device__ unsigned int g_prepare_ticket[TICKET_SLOTS];
 __global__ void __launch_bounds__(1024)
 k_step_prepare(const int32_t* __restrict__ target, const int32_t* __restrict__ proto_class, int B, int HW, int C,
                int N, int ignore_void, int slot, int* __restrict__ hist, int* __restrict__ cls_count,
-               int* __restrict__ counts, int32_t* __restrict__ rank, double* __restrict__ accum) {
+               int* __restrict__ counts, int32_t* __restrict__ rank, double* __restrict__ accum,
+               const DpComm comm, const DpLayout lay) {
   __shared__ int sh[ADLM_MAX_C + 1];
   __shared__ int s_cls[ADLM_MAX_C];
   __shared__ int s_valid, s_terms, s_last;
@@ -302,8 +303,39 @@ k_step_prepare(const int32_t* __restrict__ target, const int32_t* __restrict__ p
   if (terms) atomicAdd(&s_terms, terms);
   __syncthreads();
   for (int c = tid; c < C; c += 1024) cls_count[c] = s_cls[c];
-  if (tid == 0) { counts[0] = s_valid; counts[1] = s_terms; }
   if (tid < 4) accum[tid] = 0.0;
+  if (comm.seq == 0u) {
+    if (tid == 0) { counts[0] = s_valid; counts[1] = s_terms; }
+    return;
+  }
+  // data-parallel: publish this shard's normalisers to every peer, wait for theirs, sum in rank order
+  __shared__ int s_all[DP_MAX_WORLD][2];
+  __shared__ int s_timeout;
+  if (tid == 0) s_timeout = 0;
+  __syncthreads();
+  const int par = (int)(comm.seq & 1u), Wd = comm.world;
+  if (tid < Wd) {
+    char* pb = comm.peer[tid];
+    volatile int* slot_out = reinterpret_cast<volatile int*>(pb + lay.cnt) + (par * Wd + comm.rank) * 2;
+    slot_out[0] = s_valid;
+    slot_out[1] = s_terms;
+    __threadfence_system();
+    st_release_sys(reinterpret_cast<unsigned int*>(pb + lay.cflag) + par * Wd + comm.rank, comm.seq);
+    char* me = comm.peer[comm.rank];
+    const bool ok = dp_wait_flag(reinterpret_cast<const unsigned int*>(me + lay.cflag) + par * Wd + tid, comm.seq);
+    const volatile int* slot_in = reinterpret_cast<const volatile int*>(me + lay.cnt) + (par * Wd + tid) * 2;
+    s_all[tid][0] = slot_in[0];
+    s_all[tid][1] = slot_in[1];
+    if (!ok) s_timeout = 1;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int v = 0, t2 = 0;
+    for (int r = 0; r < Wd; ++r) { v += s_all[r][0]; t2 += s_all[r][1]; }
+    counts[0] = v;
+    counts[1] = t2;
+    if (s_timeout) accum[3] = 1.0;
+  }
 }
 
 // l1 = |W * (1 - identity^T)|_1 (module.py:213-218), dW += w_l1 * sign(W) * mask, final scalars.
@@ -391,7 +423,7 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
                       const int32_t* target, const int32_t* proto_class, int ignore_void,
                       float w_ce, float w_kld, float w_l1, float grad_scale, const int32_t* global_counts,
                       float* logits_out, int32_t* argmax_out, float* dz, float* dP, float* dW,
-                      double* scalars, void* workspace, cudaStream_t st) {
+                      double* scalars, void* workspace, const DpComm* comm, cudaStream_t st) {
   const int B = s.B, HW = s.HW, N = s.N, C = s.C;
   const long long M = (long long)B * HW;
   StepWorkspace ws = carve_step_workspace(workspace, B, s.K, HW, N, C);
@@ -400,11 +432,21 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
 
   {
     const int slot = (int)(g_next_ticket_slot.fetch_add(1u, std::memory_order_relaxed) % TICKET_SLOTS);
+    DpComm cm;
+    DpLayout lay = {};
+    if (comm != nullptr) {
+      if (!(want_grad && dz && head_fwd_fuses_ce(s, prec_mode) && head_bwd_fuses_finalize(s, prec_mode, dP, dW))) {
+        set_error("adlm_step_fwd_bwd_dp: needs ADLM_PREC_TF32, K <= 64, N <= 192, C <= 32 and dz, dP, dW");
+        return ADLM_E_UNSUPPORTED;
+      }
+      cm = *comm;
+      lay = dp_layout(s.K, N, C, cm.world);
+    }
     k_step_prepare<<<B, 1024, 0, st>>>(target, proto_class, B, HW, C, N, ignore_void, slot, ws.hist, ws.cls_count,
-                                       ws.counts, ws.rank, ws.accum);
+                                       ws.counts, ws.rank, ws.accum, cm, lay);
     ADLM_LAUNCH_CHECK();
   }
-  const int* counts = global_counts ? global_counts : ws.counts;
+  const int* counts = (global_counts && !comm) ? global_counts : ws.counts;
 
   StepExtras ex;
   ex.target = target;
@@ -447,6 +489,10 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
       exb.fin.counts = counts;
       exb.fin.accum = ws.accum;
       exb.fin.w_ce = w_ce; exb.fin.w_kld = w_kld; exb.fin.w_l1 = w_l1; exb.fin.grad_scale = grad_scale;
+      if (comm != nullptr) {
+        exb.fin.comm = *comm;
+        exb.fin.lay = dp_layout(s.K, N, C, comm->world);
+      }
       fin_fused = true;
     }
     if ((rc = head_bwd_dispatch(s, prec_mode, z, P, W, ws.dlogits, nullptr, nullptr, dz, dP, dW, exb, ws.bwd_scratch,
@@ -467,7 +513,7 @@ int step_counts_impl(const int32_t* target, int B, int HW, const int32_t* proto_
   StepWorkspace ws = carve_step_workspace(workspace, B, 1, HW, N, C);
   const int slot = (int)(g_next_ticket_slot.fetch_add(1u, std::memory_order_relaxed) % TICKET_SLOTS);
   k_step_prepare<<<B, 1024, 0, st>>>(target, proto_class, B, HW, C, N, ignore_void, slot, ws.hist, ws.cls_count,
-                                     counts_out, ws.rank, ws.accum);
+                                     counts_out, ws.rank, ws.accum, DpComm{}, DpLayout{});
   ADLM_LAUNCH_CHECK();
   return ADLM_OK;
 }

@@ -742,6 +742,45 @@ k_reduce_partials(const float* __restrict__ partials, int n_parts, int Npad2, in
   }
   a += __shfl_xor_sync(0xffffffffu, a, 1);
   a += __shfl_xor_sync(0xffffffffu, a, 2);
+
+  // ---- data-parallel: the all-reduce of [dP | dW | loss sums] happens here, over peer-mapped memory
+  const DpComm& cm = fin.comm;
+  const DpLayout& lay = fin.lay;
+  __shared__ int s_timeout;
+  const int par = (int)(cm.seq & 1u), Wd = cm.world;
+  if (cm.seq != 0u) {
+    if (threadIdx.x == 0) s_timeout = 0;
+    if (idx < total) {
+      for (int r = q4; r < Wd; r += 4) {
+        volatile float* slot = reinterpret_cast<volatile float*>(cm.peer[r] + lay.grad) +
+                               (size_t)(par * Wd + cm.rank) * lay.n_grad_pad;
+        slot[idx] = a;
+      }
+    }
+    if (blockIdx.x == 0 && threadIdx.x < 4 * Wd) {
+      const int r = threadIdx.x >> 2, k = threadIdx.x & 3;
+      volatile double* slot = reinterpret_cast<volatile double*>(cm.peer[r] + lay.acc) + (size_t)(par * Wd + cm.rank) * 4;
+      slot[k] = fin.accum[k];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x < Wd) {
+      const int r = threadIdx.x;
+      st_release_sys(reinterpret_cast<unsigned int*>(cm.peer[r] + lay.gflag) +
+                         (size_t)(par * Wd + cm.rank) * lay.n_blocks + blockIdx.x, cm.seq);
+      const bool ok = dp_wait_flag(reinterpret_cast<const unsigned int*>(cm.peer[cm.rank] + lay.gflag) +
+                                       (size_t)(par * Wd + r) * lay.n_blocks + blockIdx.x, cm.seq);
+      if (!ok) s_timeout = 1;
+    }
+    __syncthreads();
+    if (idx < total && q4 == 0) {
+      const volatile float* mine = reinterpret_cast<const volatile float*>(cm.peer[cm.rank] + lay.grad) +
+                                   (size_t)par * Wd * lay.n_grad_pad + idx;
+      float t = 0.f;
+      for (int r = 0; r < Wd; ++r) t += mine[(size_t)r * lay.n_grad_pad];
+      a = s_timeout ? __int_as_float(0x7fc00000) : t;
+    }
+  }
   if (q4 == 0 && dst != nullptr) *dst = a + extra;
 
   if (fin.scalars != nullptr && blockIdx.x == 0) {
@@ -757,18 +796,29 @@ k_reduce_partials(const float* __restrict__ partials, int n_parts, int Npad2, in
     if (threadIdx.x == 0) {
       double tot = 0.0;
       for (int w = 0; w < 8; ++w) tot += (double)s_part[w];
+      double acc[4] = {fin.accum[0], fin.accum[1], fin.accum[2], fin.accum[3]};
+      if (cm.seq != 0u) {
+        const volatile double* mine = reinterpret_cast<const volatile double*>(cm.peer[cm.rank] + lay.acc) +
+                                      (size_t)par * Wd * 4;
+        for (int k = 0; k < 4; ++k) {
+          double t = 0.0;
+          for (int r = 0; r < Wd; ++r) t += mine[r * 4 + k];
+          acc[k] = t;
+        }
+        if (s_timeout) acc[3] += 1.0;
+      }
       const double n_valid = (double)fin.counts[0], n_terms = (double)fin.counts[1];
-      const double ce = n_valid > 0 ? fin.accum[0] / n_valid
+      const double ce = n_valid > 0 ? acc[0] / n_valid
                                      : __longlong_as_double(0x7ff8000000000000LL);  // empty mean = NaN, as torch
-      const double kld = n_terms > 0 ? fin.accum[2] / n_terms : 0.0;
+      const double kld = n_terms > 0 ? acc[2] / n_terms : 0.0;
       fin.scalars[0] = (double)fin.w_ce * ce + (double)fin.w_kld * kld + (double)fin.w_l1 * tot;
       fin.scalars[1] = ce;
       fin.scalars[2] = kld;
       fin.scalars[3] = tot;
-      fin.scalars[4] = fin.accum[1];
+      fin.scalars[4] = acc[1];
       fin.scalars[5] = n_valid;
       fin.scalars[6] = n_terms;
-      fin.scalars[7] = 0.0;
+      fin.scalars[7] = acc[3];
     }
   }
 }

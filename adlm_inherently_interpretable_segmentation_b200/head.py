@@ -8,6 +8,7 @@
 torch is used for device memory, streams and autograd plumbing only; all arithmetic of the path runs
 in libadlm_head.so.  Non-CUDA / non-fp32 inputs raise — there is no fallback.
 """
+import ctypes
 from ctypes import c_float, c_int, c_longlong, c_size_t
 
 import torch
@@ -173,7 +174,7 @@ class _StepResult(dict):
 def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
                weights=(1.0, 0.25, 1e-4), grad_scale=1.0, eps=1e-4, precision=None,
                need_grads=True, want_logits=False, want_argmax=False, workspace=None, global_counts=None,
-               grads_out=None, dz_out=None):
+               grads_out=None, dz_out=None, dp_comm=None):
     """One C-ABI call for module.py:137-222 + :236 on given features.
 
     z (B,K,h,w); target (B,h,w) integer labels already resized to the feature map (dataset.py:23-31);
@@ -183,7 +184,9 @@ def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
     Gradients are those of (loss * grad_scale).  global_counts: (2,) int32 CUDA tensor overriding the
     CE / KLD normalisers (data-parallel shards, see parallel.py), or None.  grads_out: optional flat fp32
     CUDA buffer with at least N*K + C*N elements; dP and dW are then views into it ([dP | dW], one collective).
-    dz_out: optional preallocated contiguous fp32 CUDA tensor shaped like z that receives dz (pipelined callers)."""
+    dz_out: optional preallocated contiguous fp32 CUDA tensor shaped like z that receives dz (pipelined callers).
+    dp_comm: a parallel.DpExchange — the step then runs adlm_step_fwd_bwd_dp: normalisers, dP, dW and the loss
+    sums are exchanged with the peer GPUs inside the step's own kernels (no collective call afterwards)."""
     lib = _lib.load()
     _check_cuda_f32("conv_features", z)
     _check_cuda_f32("prototype_vectors", prototypes)
@@ -223,13 +226,27 @@ def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
             dW = torch.empty((C, N), device=dev, dtype=torch.float32) if need_grads else None
         logits = torch.empty((B, h, w, C), device=dev, dtype=torch.float32) if want_logits else None
         amax = torch.empty((B, h, w), device=dev, dtype=torch.int32) if want_argmax else None
-        rc = lib.adlm_step_fwd_bwd(_lib.ptr(z), B, K, HW, _lib.ptr(P), _lib.ptr(W), N, C, c_float(eps),
-                                   _prec(precision or DEFAULT_PRECISION), _lib.ptr(tgt), _lib.ptr(pc),
-                                   c_int(1 if ignore_void else 0), c_float(w_ce), c_float(w_kld),
-                                   c_float(w_l1), c_float(grad_scale), _lib.ptr(global_counts),
-                                   _lib.ptr(logits), _lib.ptr(amax),
-                                   _lib.ptr(dz), _lib.ptr(dP), _lib.ptr(dW), _lib.ptr(scalars),
-                                   _lib.ptr(workspace), c_size_t(workspace.numel()), _lib.stream_ptr())
+        if dp_comm is not None:
+            if global_counts is not None:
+                raise ValueError("dp_comm and global_counts are mutually exclusive")
+            comm = dp_comm.next_comm(K, N, C)
+            rc = lib.adlm_step_fwd_bwd_dp(_lib.ptr(z), B, K, HW, _lib.ptr(P), _lib.ptr(W), N, C, c_float(eps),
+                                          _prec(precision or DEFAULT_PRECISION), _lib.ptr(tgt), _lib.ptr(pc),
+                                          c_int(1 if ignore_void else 0), c_float(w_ce), c_float(w_kld),
+                                          c_float(w_l1), c_float(grad_scale),
+                                          _lib.ptr(logits), _lib.ptr(amax),
+                                          _lib.ptr(dz), _lib.ptr(dP), _lib.ptr(dW), _lib.ptr(scalars),
+                                          _lib.ptr(workspace), c_size_t(workspace.numel()), ctypes.byref(comm),
+                                          _lib.stream_ptr())
+            _lib.check(rc, "adlm_step_fwd_bwd_dp")
+        else:
+            rc = lib.adlm_step_fwd_bwd(_lib.ptr(z), B, K, HW, _lib.ptr(P), _lib.ptr(W), N, C, c_float(eps),
+                                       _prec(precision or DEFAULT_PRECISION), _lib.ptr(tgt), _lib.ptr(pc),
+                                       c_int(1 if ignore_void else 0), c_float(w_ce), c_float(w_kld),
+                                       c_float(w_l1), c_float(grad_scale), _lib.ptr(global_counts),
+                                       _lib.ptr(logits), _lib.ptr(amax),
+                                       _lib.ptr(dz), _lib.ptr(dP), _lib.ptr(dW), _lib.ptr(scalars),
+                                       _lib.ptr(workspace), c_size_t(workspace.numel()), _lib.stream_ptr())
     _lib.check(rc, "adlm_step_fwd_bwd")
     if dP is not None:
         dP = dP.reshape(prototypes.shape)

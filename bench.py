@@ -18,8 +18,9 @@ Prints ONE JSON line (rank 0):
   push       secondary metric of BASELINE.json: push imgs/s over a resident synthetic shard
 
 --impl reference times the CPU port alone on the same config (bounded sample per step).
-Under torchrun (N > 1): batch-sharded weak scaling, one all-reduce of the loss normalisers and one of
-[dP | dW | scalars] per step (parallel.dp_fused_step).
+Under torchrun (N > 1): batch-sharded weak scaling; the loss normalisers and [dP | dW | loss sums] are exchanged
+inside the step's own kernels over peer-mapped memory (adlm_step_fwd_bwd_dp via parallel.dp_fused_step; NCCL
+all-reduces only if symmetric memory cannot be set up, or with ADLM_DP_TRANSPORT=nccl).
 """
 import argparse
 import json
@@ -194,7 +195,7 @@ def config_dict(prec, ring):
                         "batch 16 of 64x65x65 features (513x513 crops), 190 prototypes x 64-d, 19 classes; "
                         "backbone out of scope",
             "global_batch_per_gpu": c["B"], "pixels_per_step_per_gpu": c["B"] * c["h"] * c["w"],
-            "precision": prec, "parallelism": "dp (batch-sharded, prototype-gradient all-reduce)",
+            "precision": prec, "parallelism": "dp (batch-sharded; normalisers + prototype/last-layer gradients summed in-kernel over NVLink peer memory)",
             "l2_policy": (f"ring of {ring} distinct resident batches ({ring * c['B'] * c['K'] * c['h'] * c['w'] * 4 / 2**20:.0f} MiB "
                           "> 2x L2) so every step reads inputs evicted from L2") if ring else "n/a"}
 

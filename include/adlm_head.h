@@ -17,6 +17,10 @@
  *   adlm_head_bwd          autograd backward of the above, invoked at segmentation/module.py:236
  *   adlm_step_fwd_bwd      segmentation/module.py:137-222 + :236 (forward, CE on non-void patches,
  *                          KLD prototype-diversity loss on distances, masked L1, backward)
+ *   adlm_step_fwd_bwd_dp   the same step with the batch sharded over GPUs (the reference trains with
+ *                          Trainer.gpus = 1, segmentation/configs/cityscapes_kld_imnet.gin:1; raising it makes
+ *                          Lightning wrap the module in DDP, whose gradient all-reduce this entry point
+ *                          performs inside the step's own kernels over peer-mapped memory)
  *   adlm_patch_class_mask  segmentation/push.py:201-230 (pixel -> patch class sets)
  *   adlm_push_scan         segmentation/push.py:249-280 (class-filtered per-prototype argmin,
  *                          strict '<' against the global minimum)
@@ -32,7 +36,7 @@
 extern "C" {
 #endif
 
-#define ADLM_ABI_VERSION 4
+#define ADLM_ABI_VERSION 5
 
 #if defined(__GNUC__)
 #define ADLM_API __attribute__((visibility("default")))
@@ -61,11 +65,12 @@ extern "C" {
 #define ADLM_MAX_C 128            /* classes */
 #define ADLM_MAX_PROTOS_PER_CLASS 16
 #define ADLM_MAX_PUSH_CLASSES 32  /* patch class mask is one uint32 per patch */
+#define ADLM_DP_MAX_WORLD 16       /* ranks of one NVLink domain in adlm_step_fwd_bwd_dp */
 
 /* number of doubles adlm_step_fwd_bwd writes to `scalars` */
 #define ADLM_STEP_NSCALARS 8
 /* scalars[0] loss  [1] cross_entropy  [2] kld_loss  [3] l1  [4] n_correct  [5] n_patches (non-void)
- * [6] n_kld_terms  [7] reserved */
+ * [6] n_kld_terms  [7] 0, or > 0 when a peer exchange of adlm_step_fwd_bwd_dp timed out (results are NaN) */
 
 ADLM_API const char* adlm_last_error(void);
 ADLM_API int adlm_abi_version(void);
@@ -153,6 +158,45 @@ ADLM_API int adlm_step_fwd_bwd(const float* z, int B, int K, int HW,
 ADLM_API int adlm_step_counts(const int32_t* target, int B, int HW,
                      const int32_t* proto_class, int N, int C, int ignore_void,
                      int32_t* counts_out, void* workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * Data-parallel fused step over peer-mapped memory (one process per GPU, all GPUs of one NVLink domain).
+ * Same arguments and results as adlm_step_fwd_bwd on this rank's image shard, except that
+ *   - the two loss normalisers are summed over ranks inside the step's prologue kernel,
+ *   - dP, dW and the loss sums are summed over ranks inside the dP/dW partials-reduction kernel:
+ *     every rank stores its partial result into its slot of every peer's exchange buffer (NVLink stores),
+ *     release-stores a sequence flag, waits for its peers' flags and adds the slots in rank order,
+ * so dP, dW and scalars come out bit-identical on all ranks and equal to the single-GPU step on the whole
+ * batch; dz is this shard's.  No NCCL call, no extra launch.
+ *   comm->peers: HOST array of `world` DEVICE pointers; peers[r] is rank r's exchange buffer as mapped into
+ *     this process (CUDA IPC / VMM / torch symmetric memory), each adlm_dp_exchange_bytes(K,N,C,world) bytes,
+ *     256-byte aligned, zero-filled once before the first step and never touched by the caller afterwards;
+ *   comm->seq: step counter, identical on all ranks, 1 for the first step and +1 per step on this buffer.
+ * Requires ADLM_PREC_TF32, K <= 64, N <= 192, C <= 32 and non-NULL dz/dP/dW (else ADLM_E_UNSUPPORTED: use
+ * adlm_step_counts + adlm_step_fwd_bwd(global_counts) + a library all-reduce).  A peer that never arrives
+ * makes the waits time out after about 3 s: the outputs are then NaN and scalars[7] > 0.
+ */
+typedef struct adlm_dp_comm {
+  int rank;
+  int world;
+  unsigned long long seq;
+  void* const* peers;
+} adlm_dp_comm;
+ADLM_API size_t adlm_dp_exchange_bytes(int K, int N, int C, int world);
+/* diagnostics / tests: byte offsets inside one exchange buffer, HOST array of 8:
+ * [0] normalisers int32[2][world][2]  [1] their flags u32[2][world]  [2] loss sums f64[2][world][4]
+ * [3] gradient flags u32[2][world][n_blocks]  [4] gradients f32[2][world][n_grad_pad]  [5] total bytes
+ * [6] n_grad_pad  [7] n_blocks.  First index = seq & 1, second = publishing rank. */
+ADLM_API int adlm_dp_exchange_layout(int K, int N, int C, int world, size_t* out8);
+ADLM_API int adlm_step_fwd_bwd_dp(const float* z, int B, int K, int HW,
+                         const float* P, const float* W, int N, int C,
+                         float eps, int prec_mode,
+                         const int32_t* target, const int32_t* proto_class, int ignore_void,
+                         float w_ce, float w_kld, float w_l1, float grad_scale,
+                         float* logits_out, int32_t* argmax_out,
+                         float* dz, float* dP, float* dW,
+                         double* scalars, void* workspace, size_t workspace_bytes,
+                         const adlm_dp_comm* comm, void* stream);
 
 /*
  * Push, step 1: per-patch class bitmask from full-resolution labels.

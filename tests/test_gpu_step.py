@@ -189,3 +189,108 @@ def test_step_flat_gradient_buffer_and_optional_logits(prec):
     assert int(res.scalars[4]) == n_correct
     with pytest.raises(ValueError):
         head.fused_step(z, P, W, target, pc, precision=prec, grads_out=flat[:10])
+
+
+# ------------------------------------------------------------------ peer-memory data-parallel step (one device)
+def _dp_case(seed=71):
+    B, K, h, w, N, C = 4, 64, 13, 17, 190, 19
+    zn, Pn, Wn = synth.head_inputs(B, K, h, w, N, C, w_noise=0.1, seed=seed)
+    target = torch.from_numpy(synth.block_labels(B, h, w, C, block=3, seed=seed + 1).astype(np.int32)).cuda()
+    z, P, W = cuda(zn, Pn, Wn)
+    pc = torch.arange(N, dtype=torch.int32, device="cuda") // (N // C)
+    return z, P, W, target, pc, (K, N, C)
+
+
+def _replay_publish(bufs, lay, world_size, seq, src, counts, grads, acc4):
+    """store what rank `src` publishes during step `seq` into every buffer (stands in for an absent peer)"""
+    par, n_grad = seq & 1, grads.numel()
+    for buf in bufs:
+        i32, f32, f64 = buf.view(torch.int32), buf.view(torch.float32), buf.view(torch.float64)
+        o = lay["cnt"] // 4 + (par * world_size + src) * 2
+        i32[o:o + 2] = counts.to(torch.int32)
+        i32[lay["cflag"] // 4 + par * world_size + src] = seq
+        o = lay["grad"] // 4 + (par * world_size + src) * lay["n_grad_pad"]
+        f32[o:o + n_grad] = grads
+        o = lay["acc"] // 8 + (par * world_size + src) * 4
+        f64[o:o + 4] = acc4
+        o = lay["gflag"] // 4 + (par * world_size + src) * lay["n_blocks"]
+        i32[o:o + lay["n_blocks"]] = seq
+
+
+def test_dp_exchange_two_ranks_replayed_on_one_device():
+    """adlm_step_fwd_bwd_dp on rank 1 of 2, with rank 0's publications replayed into the exchange buffers from the
+    global_counts API: reduced dP / dW / scalars equal the whole-batch step, and what rank 1 published into rank
+    0's buffer is exactly its own shard's partial result.  Two consecutive steps cover both slot parities."""
+    if not available("tf32"):
+        pytest.skip("tf32 kernels not built")
+    z, P, W, target, pc, (K, N, C) = _dp_case()
+    wts = (1.0, 0.25, 1e-4)
+    full = head.fused_step(z, P, W, target, pc, weights=wts, precision="tf32")
+    shards = ((0, 2), (2, 4))
+    local_counts = [head.step_counts(target[lo:hi], pc, C) for lo, hi in shards]
+    counts = (local_counts[0] + local_counts[1]).to(torch.int32)
+    # each shard's partial sums with the global normalisers and no L1 term
+    parts = [head.fused_step(z[lo:hi], P, W, target[lo:hi], pc, weights=(wts[0], wts[1], 0.0), global_counts=counts,
+                             precision="tf32") for lo, hi in shards]
+    flat = [torch.cat([p.dP.reshape(-1), p.dW.reshape(-1)]) for p in parts]
+    acc = [torch.stack([p.scalars[1] * p.scalars[5], p.scalars[4], p.scalars[2] * p.scalars[6],
+                        torch.zeros((), dtype=torch.float64, device="cuda")]) for p in parts]
+    exs = parallel.DpExchange.local(K, N, C, z.device, 2)
+    lay = exs[1].layout()
+    assert lay["total"] == exs[1].buf[0].numel()
+    for seq in (1, 2):
+        _replay_publish(exs[1].buf, lay, 2, seq, 0, local_counts[0], flat[0], acc[0])
+        res = head.fused_step(z[2:4], P, W, target[2:4], pc, weights=wts, precision="tf32", dp_comm=exs[1])
+        assert exs[1].seq == seq
+        sc = res.scalars.cpu().numpy()
+        assert sc[7] == 0.0, "exchange timed out"
+        assert [int(sc[5]), int(sc[6])] == [int(full.scalars[5]), int(full.scalars[6])]
+        for k in range(4):
+            assert sc[k] == pytest.approx(float(full.scalars[k]), rel=1e-6), k
+        assert int(sc[4]) == int(full.scalars[4])
+        assert parity.rel_err(res.dP.cpu().numpy(), full.dP.cpu().numpy()) <= 1e-3
+        assert parity.rel_err(res.dW.cpu().numpy(), full.dW.cpu().numpy()) <= 1e-3
+        assert parity.rel_err(res.dz.cpu().numpy(), full.dz[2:4].cpu().numpy()) <= 1e-3
+        # rank 1's publication, as found in rank 0's buffer
+        par, b0 = seq & 1, exs[1].buf[0]
+        o = lay["cnt"] // 4 + (par * 2 + 1) * 2
+        assert b0.view(torch.int32)[o:o + 2].tolist() == local_counts[1].tolist()
+        assert int(b0.view(torch.int32)[lay["cflag"] // 4 + par * 2 + 1]) == seq
+        o = lay["gflag"] // 4 + (par * 2 + 1) * lay["n_blocks"]
+        assert bool((b0.view(torch.int32)[o:o + lay["n_blocks"]] == seq).all())
+        o = lay["grad"] // 4 + (par * 2 + 1) * lay["n_grad_pad"]
+        pub = b0.view(torch.float32)[o:o + flat[1].numel()]
+        assert parity.rel_err(pub.cpu().numpy(), flat[1].cpu().numpy()) <= 1e-3
+        o = lay["acc"] // 8 + (par * 2 + 1) * 4
+        assert torch.allclose(b0.view(torch.float64)[o:o + 3], acc[1][:3], rtol=1e-6)
+
+
+def test_dp_exchange_world_of_one_and_limits():
+    if not available("tf32"):
+        pytest.skip("tf32 kernels not built")
+    z, P, W, target, pc, (K, N, C) = _dp_case(seed=81)
+    full = head.fused_step(z, P, W, target, pc, precision="tf32")
+    (ex,) = parallel.DpExchange.local(K, N, C, z.device, 1)
+    for _ in range(3):                                   # sequence numbers 1..3, both parities
+        res = head.fused_step(z, P, W, target, pc, precision="tf32", dp_comm=ex)
+        assert torch.allclose(res.scalars, full.scalars, rtol=1e-6)
+        assert parity.rel_err(res.dP.cpu().numpy(), full.dP.cpu().numpy()) <= 1e-3
+        assert parity.rel_err(res.dW.cpu().numpy(), full.dW.cpu().numpy()) <= 1e-3
+    with pytest.raises(NotImplementedError):            # the fp32 / 3xTF32 steps take the library all-reduce
+        head.fused_step(z, P, W, target, pc, precision="fp32", dp_comm=ex)
+    with pytest.raises(NotImplementedError):
+        head.fused_step(z, P, W, target, pc, precision="tf32", need_grads=False, dp_comm=ex)
+    with pytest.raises(ValueError):
+        ex.next_comm(K, N + 1, C)
+
+
+def test_dp_exchange_dead_peer_times_out_with_nan():
+    """a peer that never publishes: the bounded waits expire (~3 s each), gradients are NaN, scalars[7] > 0"""
+    if not available("tf32"):
+        pytest.skip("tf32 kernels not built")
+    z, P, W, target, pc, (K, N, C) = _dp_case(seed=91)
+    exs = parallel.DpExchange.local(K, N, C, z.device, 2)
+    res = head.fused_step(z[:2], P, W, target[:2], pc, precision="tf32", dp_comm=exs[0])
+    torch.cuda.synchronize()
+    assert float(res.scalars[7]) > 0.0
+    assert bool(torch.isnan(res.dP).all()) and bool(torch.isnan(res.dW).all())
