@@ -61,6 +61,38 @@ def peaks():
     return dict(hbm=6650.0, source="fallback (B200_PROFILING.md)")
 
 
+# ------------------------------------------------------------------------------------------------ host placement
+def bind_near_gpu(index):
+    """Pin this process (and, by first touch, its pinned staging buffers) to the CPU cores of the NUMA node the
+    GPU hangs off: with one process per GPU, eight ranks staging through one node's memory controller is what
+    limits the end-to-end leg.  Returns a short description for the JSON line; a box that hides the topology
+    (numa_node = -1, no sysfs) is left alone."""
+    if os.environ.get("ADLM_BENCH_BIND", "1") == "0":
+        return "off"
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        dom, rest = bus.split(":", 1)
+        dev = f"{int(dom, 16):04x}:{rest.lower()}"
+        node = int(open(f"/sys/bus/pci/devices/{dev}/numa_node").read())
+        if node < 0:
+            return f"gpu {dev}: numa_node -1 (not bound)"
+        cpulist = open(f"/sys/devices/system/node/node{node}/cpulist").read().strip()
+        cpus = set()
+        for part in cpulist.split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return f"gpu {dev}: node {node} has no allowed cpus (not bound)"
+        os.sched_setaffinity(0, cpus)
+        return f"gpu {dev}: node {node}, {len(cpus)} cpus"
+    except Exception as e:  # noqa: BLE001 - placement is best effort
+        return f"not bound ({type(e).__name__}: {e})"
+
+
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
     """samples SM clock + throttle reasons with NVML while the timed region runs"""
@@ -215,6 +247,7 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    binding = bind_near_gpu(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     prec = args.precision or "tf32"
@@ -355,6 +388,7 @@ def main():
         raise RuntimeError("e2e leg: non-finite results on the host")
     e2e = {"value": world * M * K_steps / (ms_e2e * 1e-3) / 1e6, "unit": "Mpixels/s",
            "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / K_steps,
+           "host_binding": binding,
            "pipeline": "3 buffers, 3 streams (H2D | kernels | D2H); results of step i-2 are on the host when step i has been issued"}
 
     # ---- secondary metric: push imgs/s over a resident synthetic shard (configs[2] per-GPU slice)
