@@ -38,6 +38,9 @@ CFG = dict(B=16, K=64, h=65, w=65, N=190, C=19)          # BASELINE configs[1], 
 WEIGHTS = (1.0, 0.25, 1e-4)                              # cityscapes_kld_imnet.gin:35,38-39
 BYTES_FWD = lambda K, C: 4 * K + 4 * C                   # z in, logits out
 BYTES_BWD = lambda K, C: 4 * K + 4 * C + 4 * K           # z + dlogits in, dz out
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of this
+# workload in tf32 (profiles/r1_ncu_full_step_tf32.txt, in-step launches): dz 27.2 + dp 27.2 + reduce 10.9 MB; fwd 17.8 MB
+NCU_TRAFFIC_TF32 = {"head_bwd": 65.3e6, "head_fwd": 17.8e6}
 PUSH_CFG = dict(n_img=372, K=64, h=129, w=257, H=1024, W=2048, N=190, C=19)  # configs[2]: 2975 images / 8 GPUs per GPU
 
 
@@ -320,7 +323,8 @@ def main():
     if kern:
         dom = max(kern, key=lambda k: kern[k]["avg_ms"])
         roof = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["achieved_gbs"], "peak": pk["hbm"],
-                "unit": "GB/s", "frac": kern[dom]["achieved_gbs"] / pk["hbm"], "traffic": None,
+                "unit": "GB/s", "frac": kern[dom]["achieved_gbs"] / pk["hbm"],
+                "traffic": NCU_TRAFFIC_TF32.get(dom) if prec == "tf32" else None,
                 "peak_source": pk["source"], "kernels": kern,
                 "share_of_step": kern[dom]["avg_ms"] / (ms / K_steps)}
 
