@@ -66,3 +66,28 @@ def test_argument_errors_are_reported_without_a_gpu(lib):
     with pytest.raises(NotImplementedError):
         _lib.check(rc, "adlm_head_fwd")
     assert lib.adlm_step_workspace_bytes(16, 64, 4225, 190, 19) > 16 * 4225 * 16 * 4
+
+
+def test_dp_exchange_layout_is_consistent(lib):
+    """host-only entry points of the peer-memory data-parallel step (no GPU needed)"""
+    assert int(re.search(r"#define ADLM_DP_MAX_WORLD (\d+)", open(HEADER).read()).group(1)) == _lib.DP_MAX_WORLD
+    K, N, C = 64, 190, 19
+    for world_size in (1, 2, 8, _lib.DP_MAX_WORLD):
+        out = (ctypes.c_size_t * 8)()
+        assert lib.adlm_dp_exchange_layout(K, N, C, world_size, ctypes.cast(out, ctypes.c_void_p)) == 0
+        cnt, cflag, acc, gflag, grad, total, n_grad_pad, n_blocks = (int(x) for x in out)
+        assert total == lib.adlm_dp_exchange_bytes(K, N, C, world_size)
+        assert 0 == cnt < cflag < acc < gflag < grad < total and all(o % 256 == 0 for o in (cflag, acc, gflag, grad, total))
+        assert n_grad_pad >= N * K + C * N and n_grad_pad % 64 == 0
+        assert n_blocks * 64 >= N * K + C * N                        # 64 outputs per 256-thread block
+        # regions hold [2 parities][world][...] without overlap
+        assert cflag - cnt >= 2 * world_size * 2 * 4 and acc - cflag >= 2 * world_size * 4
+        assert gflag - acc >= 2 * world_size * 4 * 8 and grad - gflag >= 2 * world_size * n_blocks * 4
+        assert total - grad >= 2 * world_size * n_grad_pad * 4
+    assert lib.adlm_dp_exchange_bytes(K, N, C, _lib.DP_MAX_WORLD + 1) == 0
+    assert lib.adlm_dp_exchange_layout(K, N, C, 0, None) == _lib.E_INVALID
+    comm = _lib.DpComm(0, 1, 0, None)
+    rc = lib.adlm_step_fwd_bwd_dp(None, 1, 64, 16, None, None, 10, 2, ctypes.c_float(1e-4), 1, None, None, 1,
+                                  ctypes.c_float(1), ctypes.c_float(1), ctypes.c_float(1), ctypes.c_float(1),
+                                  None, None, None, None, None, None, None, 0, ctypes.byref(comm), None)
+    assert rc == _lib.E_INVALID
