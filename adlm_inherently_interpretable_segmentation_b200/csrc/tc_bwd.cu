@@ -127,39 +127,10 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
   prefetch(tile);
 
   stage_rows_kmajor<KP, false>(Pk, Pk, p.P, N, K, Npad, CENTRE, tid, 256);
-  // Wt: rows = prototypes, K index = class: [C8/4][Npad][4]; padding first, then W [C][N] streamed coalesced
-  for (int idx = tid; idx < C8 * Npad; idx += 256) {
-    const int c = idx / Npad, n = idx - c * Npad;
-    if (!(c < C && n < N && p.dlogits != nullptr)) Wt[(size_t)(c >> 2) * Npad * 4 + n * 4 + (c & 3)] = 0.f;
-  }
-  if (p.dlogits != nullptr) {
-    const int CN = C * N;
-    for (int i0 = 0; i0 < CN; i0 += 256 * 4) {
-      float v[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int idx = i0 + u * 256 + tid;
-        v[u] = idx < CN ? __ldg(p.W + idx) : 0.f;
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int idx = i0 + u * 256 + tid;
-        if (idx < CN) {
-          const int c = idx / N, n = idx - c * N;
-          Wt[(size_t)(c >> 2) * Npad * 4 + n * 4 + (c & 3)] = rna_tf32_mask(v[u]);
-        }
-      }
-    }
-  }
-  __syncthreads();
-  // Pt: the same rounded prototypes transposed (rows k, K index n): [Npad/4][KP][4], built from Pk
-  for (int idx = tid; idx < (Npad / 4) * KP; idx += 256) {
-    const int k = idx % KP, n4 = idx / KP;
-    float v[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) v[j] = Pk[((size_t)(k >> 2) * Npad + n4 * 4 + j) * 4 + (k & 3)];
-    *reinterpret_cast<float4*>(Pt + (size_t)idx * 4) = make_float4(v[0], v[1], v[2], v[3]);
-  }
+  // Wt: rows = prototypes, K index = class: [C8/4][Npad][4]
+  stage_wt_kmajor(Wt, p.W, C, N, C8, Npad, 1.f, p.dlogits != nullptr, tid, 256);
+  // Pt: the same rounded prototypes transposed (rows k, K index n): [Npad/4][KP][4]
+  stage_pt_kmajor<KP>(Pt, p.P, N, K, Npad, CENTRE, tid, 256);
   __syncthreads();
   for (int n = tid; n < Npad; n += 256) {
     float a = 0.f;
@@ -365,6 +336,7 @@ struct DpSmem {
 };
 
 template <int KP, int NB, bool GENERIC>
+// 13 warps: the sub-partition that hosts four of them caps the kernel at 16384 / (4 * 32) = 128 registers
 __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p) {
   using L = DpSmem<KP>;
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -390,6 +362,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const bool kld = p.own_grad != nullptr;
   const bool has_dl = p.dlogits != nullptr;
+  if (warp == 0) DP_PHASE(2, 60);
 
   if (warp == 12) tmem_alloc(smem_u32(tmem_base_s), 512);
   if (tid == 0) {
@@ -399,31 +372,42 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
     mbar_init(smem_u32(&bars[3]), 1);     // free: every MMA of the tile done
     mbar_init_fence();
   }
-  stage_rows_kmajor<KP, false>(PkA, PkA, p.P, N, K, Npad2, CENTRE, tid, DP_THREADS);
-  for (int idx = tid; idx < C8 * Npad2; idx += DP_THREADS) {
-    const int c = idx / Npad2, n = idx - c * Npad2;
-    if (!(c < C && n < N && has_dl)) WtA[(size_t)(c >> 2) * Npad2 * 4 + n * 4 + (c & 3)] = 0.f;
-  }
-  if (has_dl) {
-    const int CN = C * N;
-    for (int i0 = 0; i0 < CN; i0 += DP_THREADS * 4) {
-      float v[4];
+  // the builder warps fetch their first tile before the one-time operand staging
+  const int iters = (p.num_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1;
+  const bool is_builder = warp >= 8 && warp < 12;
+  const int cw = tid - 256;
+  float zr[KP];
+  float dlr[32];
+  const int Mi = (int)p.M;
+  auto prefetch = [&](int it) {
+    const int m = ((int)blockIdx.x + it * (int)gridDim.x) * TILE + cw;
+    if (it < iters && m < Mi) {
+      const int b = m / HW;
+      const float* src = p.z + ((size_t)b * K) * HW + (m - b * HW);
+      if (K == KP) {
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int idx = i0 + u * DP_THREADS + tid;
-        v[u] = idx < CN ? __ldg(p.W + idx) : 0.f;
-      }
+        for (int k = 0; k < KP; ++k) { zr[k] = __ldg(src); src += HW; }
+      } else {
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int idx = i0 + u * DP_THREADS + tid;
-        if (idx < CN) {
-          const int c = idx / N, n = idx - c * N;
-          WtA[(size_t)(c >> 2) * Npad2 * 4 + n * 4 + (c & 3)] = rna_tf32_mask(v[u]);
-        }
+        for (int k = 0; k < KP; ++k) zr[k] = (k < K) ? __ldg(src + (size_t)k * HW) : CENTRE;
       }
+      const float* dl = p.dlogits + (size_t)m * C;
+#pragma unroll
+      for (int c = 0; c < 32; ++c) dlr[c] = (has_dl && c < C) ? __ldg(dl + c) : 0.f;
+    } else {
+#pragma unroll
+      for (int k = 0; k < KP; ++k) zr[k] = CENTRE;
+#pragma unroll
+      for (int c = 0; c < 32; ++c) dlr[c] = 0.f;
     }
+  };
+  if (warp < 8) {
+    // one-time operands, staged by the eight epilogue warps only: the builder warps have their loads in flight
+    // and the MMA warp is allocating TMEM
+    stage_rows_kmajor<KP, false, 4>(PkA, PkA, p.P, N, K, Npad2, CENTRE, tid, 256);
+    stage_wt_kmajor(WtA, p.W, C, N, C8, Npad2, 1.f, has_dl, tid, 256);
+    smem_zero4(dLtB, 32 * TILE / 4, tid, 256);
   }
-  for (int idx = tid; idx < 32 * TILE; idx += DP_THREADS) dLtB[idx] = 0.f;
   fence_async_smem();
   fence_before();
   __syncthreads();
@@ -436,37 +420,10 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
   const uint32_t tD1 = tmem_base, tGl = tmem_base + 128, tP0 = tmem_base + 256, tW0 = tmem_base + 256 + NB * KP;
   const uint32_t bar_full = smem_u32(&bars[0]), bar_acc = smem_u32(&bars[1]), bar_gs = smem_u32(&bars[2]),
                  bar_free = smem_u32(&bars[3]);
-  const int iters = (p.num_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1;
 
-  if (warp >= 8 && warp < 12) {
-    // ================= pixel-side operand builder: thread = pixel =================
-    const int cw = tid - 256;
-    float zr[KP];
-    float dlr[32];
-    const int Mi = (int)p.M;
-    auto prefetch = [&](int it) {
-      const int m = ((int)blockIdx.x + it * (int)gridDim.x) * TILE + cw;
-      if (it < iters && m < Mi) {
-        const int b = m / HW;
-        const float* src = p.z + ((size_t)b * K) * HW + (m - b * HW);
-        if (K == KP) {
-#pragma unroll
-          for (int k = 0; k < KP; ++k) { zr[k] = __ldg(src); src += HW; }
-        } else {
-#pragma unroll
-          for (int k = 0; k < KP; ++k) zr[k] = (k < K) ? __ldg(src + (size_t)k * HW) : CENTRE;
-        }
-        const float* dl = p.dlogits + (size_t)m * C;
-#pragma unroll
-        for (int c = 0; c < 32; ++c) dlr[c] = (has_dl && c < C) ? __ldg(dl + c) : 0.f;
-      } else {
-#pragma unroll
-        for (int k = 0; k < KP; ++k) zr[k] = CENTRE;
-#pragma unroll
-        for (int c = 0; c < 32; ++c) dlr[c] = 0.f;
-      }
-    };
+  if (is_builder) {
     prefetch(0);
+    // ================= pixel-side operand builder: thread = pixel =================
     for (int it = 0; it < iters; ++it) {
       const int m = ((int)blockIdx.x + it * (int)gridDim.x) * TILE + cw;
       const bool valid = m < Mi;
@@ -668,37 +625,73 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
     named_bar_sync(1, 256);
     const float s_scale = act_log ? LN2 : 1.f;
     float* part = p.partials + (size_t)blockIdx.x * ((size_t)Npad2 * KP + (size_t)Npad2 * 32);
+    // Every MMA has retired (bar_free), so the pixel-operand buffers serve as per-warp transpose scratch:
+    // a thread owns one prototype row in TMEM, but the stores should cover whole rows of the partials.
+    constexpr int HK = KP / 2, PITCH = HK + 4;                      // 16-byte aligned, conflict-free float4 rows
+    static_assert(8 * 32 * PITCH * 4 <= (KP + 32) * TILE * 4, "transpose scratch exceeds ZtB + dLtB");
+    float* scr = ZtB + (size_t)warp * 32 * PITCH;
     for (int blk = 0; blk < NB; ++blk) {
-      const int n = blk * 128 + lane_n;
+      const int n = blk * 128 + lane_n, n_base = blk * 128 + (warp & 3) * 32;
       const float cst = css[blk * 128 + lane_n] + css[(2 + blk) * 128 + lane_n];
-      if (blk * 128 + (warp & 3) * 32 < N) {
+      if (n_base < N) {
 #pragma unroll
         for (int ch = 0; ch < KP / 32; ++ch) {
-          const int k0 = half * (KP / 2) + ch * 16;
+          const int k0 = half * HK + ch * 16;
           uint32_t r[16];
           tmem_ld16(tP0 + blk * KP + lane_field + k0, r);
           tmem_ld_wait();
-          if (n < N) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              const int k = k0 + i;
+          for (int i4 = 0; i4 < 4; ++i4) {
+            float o[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int k = k0 + i4 * 4 + j;
               const float pc = PkA[(size_t)(k >> 2) * Npad2 * 4 + n * 4 + (k & 3)];
-              part[(size_t)n * KP + k] = 2.f * (cst * pc - __uint_as_float(r[i]));
+              o[j] = 2.f * (cst * pc - __uint_as_float(r[i4 * 4 + j]));
             }
+            *reinterpret_cast<float4*>(scr + lane * PITCH + ch * 16 + i4 * 4) = make_float4(o[0], o[1], o[2], o[3]);
           }
         }
+        __syncwarp();
+        {
+          constexpr int V = HK / 4, RPI = 32 / V;                   // float4s per row, rows per store instruction
+          const int col4 = lane % V, rsub = lane / V;
+#pragma unroll
+          for (int i = 0; i < 32 / RPI; ++i) {
+            const int row = i * RPI + rsub;
+            if (n_base + row < N)
+              *reinterpret_cast<float4*>(part + (size_t)(n_base + row) * KP + half * HK + col4 * 4) =
+                  *reinterpret_cast<const float4*>(scr + row * PITCH + col4 * 4);
+          }
+        }
+        __syncwarp();
         uint32_t r[16];
         tmem_ld16(tW0 + blk * 32 + lane_field + half * 16, r);
         tmem_ld_wait();
-        if (n < N) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i) part[(size_t)Npad2 * KP + (size_t)n * 32 + half * 16 + i] = s_scale * __uint_as_float(r[i]);
+        for (int i4 = 0; i4 < 4; ++i4)
+          *reinterpret_cast<float4*>(scr + lane * PITCH + i4 * 4) =
+              make_float4(s_scale * __uint_as_float(r[i4 * 4]), s_scale * __uint_as_float(r[i4 * 4 + 1]),
+                          s_scale * __uint_as_float(r[i4 * 4 + 2]), s_scale * __uint_as_float(r[i4 * 4 + 3]));
+        __syncwarp();
+        {
+          const int col4 = lane & 3, rsub = lane >> 2;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int row = i * 8 + rsub;
+            if (n_base + row < N)
+              *reinterpret_cast<float4*>(part + (size_t)Npad2 * KP + (size_t)(n_base + row) * 32 + half * 16 + col4 * 4) =
+                  *reinterpret_cast<const float4*>(scr + row * PITCH + col4 * 4);
+          }
         }
+        __syncwarp();
       }
     }
     fence_before();
   }
+  if (warp == 0) DP_PHASE(2, 61);
   __syncthreads();
+  if (warp == 0) DP_PHASE(2, 62);
   if (warp == 12) tmem_dealloc(tmem_base, 512);
 }
 

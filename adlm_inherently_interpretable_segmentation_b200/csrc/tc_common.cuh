@@ -153,27 +153,32 @@ __device__ __forceinline__ float rna_tf32_mask(float x) {
 // Stage a row-major [rows_valid x K] fp32 matrix (prototypes) as a canonical K-major operand
 // [KP/4][rows_pad][4]: value = rna(x - centre) (hi) and, for 3xTF32, lo = rna((x - centre) - hi).
 // Rows >= rows_valid and columns >= K are zero.  Fast path (K == KP, 16-byte aligned base): every thread
-// streams float4s of the flat array — fully coalesced, four loads in flight per thread.
-template <int KP, bool X3>
+// reads float4s, four loads in flight per thread.
+template <int KP, bool X3, int BATCH = 4>
 __device__ __forceinline__ void stage_rows_kmajor(float* __restrict__ hi, float* __restrict__ lo,
                                                   const float* __restrict__ src, int rows_valid, int K,
                                                   int rows_pad, float centre, int tid, int nthreads) {
   constexpr int Q = KP / 4;
   const int total = rows_pad * Q;
   if (K == KP && (reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
+    // a warp covers 8 consecutive rows x 4 consecutive 4-column groups: each quarter-warp's 16-byte
+    // shared-memory stores are 128 contiguous bytes (conflict-free) and the global side reads 64 contiguous
+    // bytes per row (8 lines per warp load instead of 32)
     const float4* src4 = reinterpret_cast<const float4*>(src);
-    for (int f0 = 0; f0 < total; f0 += nthreads * 4) {
-      float4 v[4];
+    const int n8 = rows_pad >> 3;                             // rows_pad is a multiple of 32, Q of 4
+    for (int f0 = 0; f0 < total; f0 += nthreads * BATCH) {
+      float4 v[BATCH];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < BATCH; ++u) {
         const int f = f0 + u * nthreads + tid;
-        v[u] = (f < rows_valid * Q) ? __ldg(src4 + f) : make_float4(centre, centre, centre, centre);
+        const int g = f >> 5, l = f & 31;                     // group of 32 = 8 rows x 4 column groups
+        const int k4 = (g / n8) * 4 + (l >> 3), n = (g % n8) * 8 + (l & 7);
+        v[u] = (f < total && n < rows_valid) ? __ldg(src4 + (size_t)n * Q + k4) : make_float4(centre, centre, centre, centre);
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < BATCH; ++u) {
         const int f = f0 + u * nthreads + tid;
         if (f < total) {
-          const int n = f / Q, k4 = f - n * Q;
           const float x[4] = {v[u].x - centre, v[u].y - centre, v[u].z - centre, v[u].w - centre};
           float h[4], l[4];
 #pragma unroll
@@ -181,8 +186,10 @@ __device__ __forceinline__ void stage_rows_kmajor(float* __restrict__ hi, float*
             h[j] = rna_tf32_mask(x[j]);
             l[j] = X3 ? rna_tf32_mask(x[j] - h[j]) : 0.f;
           }
-          *reinterpret_cast<float4*>(hi + ((size_t)k4 * rows_pad + n) * 4) = make_float4(h[0], h[1], h[2], h[3]);
-          if (X3) *reinterpret_cast<float4*>(lo + ((size_t)k4 * rows_pad + n) * 4) = make_float4(l[0], l[1], l[2], l[3]);
+          const int g = f >> 5, li = f & 31;
+          const size_t o = ((size_t)((g / n8) * 4 + (li >> 3)) * rows_pad + (g % n8) * 8 + (li & 7)) * 4;
+          *reinterpret_cast<float4*>(hi + o) = make_float4(h[0], h[1], h[2], h[3]);
+          if (X3) *reinterpret_cast<float4*>(lo + o) = make_float4(l[0], l[1], l[2], l[3]);
         }
       }
     }
@@ -199,6 +206,97 @@ __device__ __forceinline__ void stage_rows_kmajor(float* __restrict__ hi, float*
       }
       *reinterpret_cast<float4*>(hi + (size_t)idx * 4) = make_float4(h[0], h[1], h[2], h[3]);
       if (X3) *reinterpret_cast<float4*>(lo + (size_t)idx * 4) = make_float4(l[0], l[1], l[2], l[3]);
+    }
+  }
+}
+
+// Stage W [C x N] (row-major) TRANSPOSED as a K-major operand: rows = prototypes n, K index = class c,
+// layout [C8/4][rows_pad][4]; value = rna(scale * W[c][n]), zero beyond C / N or when !valid.  Consecutive
+// threads take consecutive n: coalesced global reads, contiguous 16-byte shared-memory stores.
+__device__ __forceinline__ void stage_wt_kmajor(float* __restrict__ dst, const float* __restrict__ W, int C, int N,
+                                                int C8, int rows_pad, float scale, bool valid, int tid,
+                                                int nthreads) {
+  const int total = (C8 >> 2) * rows_pad;
+  for (int f0 = 0; f0 < total; f0 += nthreads * 4) {
+    float v[4][4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int f = f0 + u * nthreads + tid;
+      const int c4 = f / rows_pad, n = f - c4 * rows_pad;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int c = c4 * 4 + j;
+        v[u][j] = (valid && f < total && c < C && n < N) ? __ldg(W + (size_t)c * N + n) : 0.f;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int f = f0 + u * nthreads + tid;
+      if (f < total)
+        *reinterpret_cast<float4*>(dst + (size_t)f * 4) =
+            make_float4(rna_tf32_mask(scale * v[u][0]), rna_tf32_mask(scale * v[u][1]),
+                        rna_tf32_mask(scale * v[u][2]), rna_tf32_mask(scale * v[u][3]));
+    }
+  }
+}
+
+// Stage W [C x N] as a K-major operand with rows = classes c, K index = prototype n: [Npad/4][Cpad][4];
+// value = rna(scale * W[c][n]), zero beyond C / N.  A warp covers 8 classes x 4 prototype quads: conflict-free
+// 16-byte shared-memory stores, 64 contiguous bytes per class row on the global side.
+__device__ __forceinline__ void stage_w_kmajor(float* __restrict__ dst, const float* __restrict__ W, int C, int N,
+                                               int Cpad, int Npad, float scale, int tid, int nthreads) {
+  const int total = (Npad >> 2) * Cpad;
+  const int c8 = Cpad >> 3;                                   // Cpad is a multiple of 8, Npad of 16
+  for (int f0 = 0; f0 < total; f0 += nthreads * 4) {
+    float v[4][4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int f = f0 + u * nthreads + tid;
+      const int g = f >> 5, l = f & 31;                       // group of 32 = 8 classes x 4 prototype quads
+      const int n4 = (g / c8) * 4 + (l >> 3), c = (g % c8) * 8 + (l & 7);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int n = n4 * 4 + j;
+        v[u][j] = (f < total && c < C && n < N) ? __ldg(W + (size_t)c * N + n) : 0.f;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int f = f0 + u * nthreads + tid;
+      const int g = f >> 5, l = f & 31;
+      if (f < total)
+        *reinterpret_cast<float4*>(dst + ((size_t)((g / c8) * 4 + (l >> 3)) * Cpad + (g % c8) * 8 + (l & 7)) * 4) =
+            make_float4(rna_tf32_mask(scale * v[u][0]), rna_tf32_mask(scale * v[u][1]),
+                        rna_tf32_mask(scale * v[u][2]), rna_tf32_mask(scale * v[u][3]));
+    }
+  }
+}
+
+// Stage P [N x K] TRANSPOSED (rows = depth k, K index = prototype n): [Npad/4][KP][4], same centring and
+// rounding as stage_rows_kmajor.  Consecutive threads take consecutive k: coalesced reads, contiguous stores.
+template <int KP>
+__device__ __forceinline__ void stage_pt_kmajor(float* __restrict__ dst, const float* __restrict__ P, int N, int K,
+                                                int Npad, float centre, int tid, int nthreads) {
+  const int total = (Npad >> 2) * KP;
+  for (int f0 = 0; f0 < total; f0 += nthreads * 4) {
+    float v[4][4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int f = f0 + u * nthreads + tid;
+      const int n4 = f / KP, k = f - n4 * KP;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int n = n4 * 4 + j;
+        v[u][j] = (f < total && n < N && k < K) ? __ldg(P + (size_t)n * K + k) : centre;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int f = f0 + u * nthreads + tid;
+      if (f < total)
+        *reinterpret_cast<float4*>(dst + (size_t)f * 4) =
+            make_float4(rna_tf32_mask(v[u][0] - centre), rna_tf32_mask(v[u][1] - centre),
+                        rna_tf32_mask(v[u][2] - centre), rna_tf32_mask(v[u][3] - centre));
     }
   }
 }

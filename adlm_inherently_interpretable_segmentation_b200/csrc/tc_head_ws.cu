@@ -64,6 +64,7 @@ struct WsSmem {
 };
 
 template <int KP>
+// 13 warps: the sub-partition that hosts four of them caps the kernel at 16384 / (4 * 32) = 128 registers
 __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p) {
   using L = WsSmem<KP>;
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -126,16 +127,9 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
 
   // ---- one-time operand staging (all 13 warps) ----
   stage_rows_kmajor<KP, false>(Pk, Pk, p.P, N, K, Npad, CENTRE, tid, WS_THREADS);
-  smem_zero4(Wk, Npad * Cpad / 4, tid, WS_THREADS);
+  // Wk: B operand of MMA2, rows = classes, K index = prototype: [Npad/4][Cpad][4]; ln 2 folded in
+  stage_w_kmajor(Wk, p.W, C, N, Cpad, Npad, p.act_mode == ADLM_ACT_LOG ? LN2 : 1.f, tid, WS_THREADS);
   __syncthreads();
-  {
-    // Wk: B operand of MMA2, rows = classes, K index = prototype: [Npad/4][Cpad][4]; ln 2 folded in.
-    // One warp per class row: coalesced along n, no integer division.
-    const float wscale = p.act_mode == ADLM_ACT_LOG ? LN2 : 1.f;
-    for (int c = warp; c < C; c += WS_THREADS / 32)
-      for (int n = lane; n < N; n += 32)
-        Wk[(size_t)(n >> 2) * Cpad * 4 + c * 4 + (n & 3)] = rna_tf32_mask(wscale * __ldg(p.W + (size_t)c * N + n));
-  }
   for (int n = tid; n < Npad; n += WS_THREADS) {
     // |p|^2 of the ROUNDED vector, so that z == p gives d == 0
     float a = 0.f;
