@@ -355,7 +355,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
   int* pixs = reinterpret_cast<int*>(misc + 1536);
   float* css = reinterpret_cast<float*>(misc + 2048);           // [half][blk][128]
   uint64_t* bars = reinterpret_cast<uint64_t*>(misc + 2048 + 2048);
-  uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 4);
+  uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 7);   // six barriers, then the TMEM base
   uint32_t* clsm = reinterpret_cast<uint32_t*>(misc + 2048 + 2048 + 64);   // [32 classes][4 words]: pixels of the tile
   float* ogs = reinterpret_cast<float*>(smem + L::ogs(Npad2, C8));           // [128 px][16]: dL/d(own distances)
 
@@ -367,9 +367,11 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
   if (warp == 12) tmem_alloc(smem_u32(tmem_base_s), 512);
   if (tid == 0) {
     mbar_init(smem_u32(&bars[0]), 128);   // full: pixel operands written
-    mbar_init(smem_u32(&bars[1]), 1);     // acc: D^T and Gl^T of a block ready
-    mbar_init(smem_u32(&bars[2]), 256);   // gs: G and S of a block written back to TMEM
-    mbar_init(smem_u32(&bars[3]), 1);     // free: every MMA of the tile done
+    mbar_init(smem_u32(&bars[1]), 1);     // free: every MMA of the tile done
+    mbar_init(smem_u32(&bars[2]), 1);     // acc[b]: D^T and Gl^T of a unit ready in TMEM buffer b
+    mbar_init(smem_u32(&bars[3]), 1);
+    mbar_init(smem_u32(&bars[4]), 256);   // gs[b]: G and S of the unit written back to TMEM buffer b
+    mbar_init(smem_u32(&bars[5]), 256);
     mbar_init_fence();
   }
   // the builder warps fetch their first tile before the one-time operand staging
@@ -417,9 +419,13 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
   if (warp == 8) DP_PHASE(0, 0);
   if (warp == 12) DP_PHASE(1, 0);
   if (warp == 0) DP_PHASE(2, 0);
-  const uint32_t tD1 = tmem_base, tGl = tmem_base + 128, tP0 = tmem_base + 256, tW0 = tmem_base + 256 + NB * KP;
-  const uint32_t bar_full = smem_u32(&bars[0]), bar_acc = smem_u32(&bars[1]), bar_gs = smem_u32(&bars[2]),
-                 bar_free = smem_u32(&bars[3]);
+  // A unit = (prototype block, 64-pixel half of the tile).  Two TMEM buffers of 128 columns (D^T | Gl^T, 64 each)
+  // let the tensor pipe produce unit u+1 and consume unit u-1 while the epilogue warps work on unit u.
+  constexpr int UW = 64, NU = 2 * NB;
+  const uint32_t tP0 = tmem_base + 256, tW0 = tmem_base + 256 + NB * KP;
+  auto tDb = [&](int b) { return tmem_base + (uint32_t)b * 128u; };
+  const uint32_t bar_full = smem_u32(&bars[0]), bar_free = smem_u32(&bars[1]), bar_acc0 = smem_u32(&bars[2]),
+                 bar_gs0 = smem_u32(&bars[4]);
 
   if (is_builder) {
     prefetch(0);
@@ -481,34 +487,44 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
   } else if (warp == 12) {
     // ================= MMA issuer =================
     if (lane == 0) {
-      const uint32_t idesc_t = make_idesc_tf32(128, 128), idesc_p = make_idesc_tf32(128, KP), idesc_w = make_idesc_tf32(128, 32);
+      const uint32_t idesc_t = make_idesc_tf32(128, UW), idesc_p = make_idesc_tf32(128, KP), idesc_w = make_idesc_tf32(128, 32);
       const int ksteps = (K + 7) >> 3;
-      uint32_t g = 0;
+      // unit j of a tile: block j >> 1, pixel half j & 1
+      auto issue_d = [&](int j) {
+        const int blk = j >> 1, h = j & 1, b = j & 1;
+        const uint32_t a0 = smem_u32(PkA) + blk * 128 * 16, b0 = smem_u32(ZkB) + h * UW * 16;
+        for (int ks = 0; ks < ksteps; ++ks)
+          mma_ss(tDb(b), make_desc(a0 + ks * 2 * Npad2 * 16, Npad2 * 16, 128), make_desc(b0 + ks * 2 * TILE * 16, TILE * 16, 128),
+                 idesc_t, ks > 0 ? 1u : 0u);
+        const uint32_t w0 = smem_u32(WtA) + blk * 128 * 16, l0 = smem_u32(dLkB) + h * UW * 16;
+        for (int ks = 0; ks < C8 / 8; ++ks)
+          mma_ss(tDb(b) + UW, make_desc(w0 + ks * 2 * Npad2 * 16, Npad2 * 16, 128), make_desc(l0 + ks * 2 * TILE * 16, TILE * 16, 128),
+                 idesc_t, ks > 0 ? 1u : 0u);
+        mma_commit(bar_acc0 + b * 8);
+      };
+      uint32_t gcnt[2] = {0u, 0u};
       for (int it = 0; it < iters; ++it) {
         mbar_wait(bar_full, (uint32_t)it & 1u);
         fence_after();
         DP_PHASE(1, 1 + it * 8);
-        for (int blk = 0; blk < NB; ++blk) {
-          const uint32_t a0 = smem_u32(PkA) + blk * 128 * 16, b0 = smem_u32(ZkB);
-          for (int ks = 0; ks < ksteps; ++ks)
-            mma_ss(tD1, make_desc(a0 + ks * 2 * Npad2 * 16, Npad2 * 16, 128), make_desc(b0 + ks * 2 * TILE * 16, TILE * 16, 128),
-                   idesc_t, ks > 0 ? 1u : 0u);
-          const uint32_t w0 = smem_u32(WtA) + blk * 128 * 16, l0 = smem_u32(dLkB);
-          for (int ks = 0; ks < C8 / 8; ++ks)
-            mma_ss(tGl, make_desc(w0 + ks * 2 * Npad2 * 16, Npad2 * 16, 128), make_desc(l0 + ks * 2 * TILE * 16, TILE * 16, 128),
-                   idesc_t, ks > 0 ? 1u : 0u);
-          mma_commit(bar_acc);
-          DP_PHASE(1, 2 + it * 8 + blk * 3);
-          mbar_wait(bar_gs, g & 1u);
-          DP_PHASE(1, 3 + it * 8 + blk * 3);
-          ++g;
+        issue_d(0);
+        issue_d(1);
+        DP_PHASE(1, 2 + it * 8);
+#pragma unroll
+        for (int j = 0; j < NU; ++j) {
+          const int blk = j >> 1, h = j & 1, b = j & 1;
+          mbar_wait(bar_gs0 + b * 8, gcnt[b] & 1u);
+          ++gcnt[b];
           fence_after();
+          if (j == 0) DP_PHASE(1, 3 + it * 8);
           const uint32_t zt0 = smem_u32(ZtB), lt0 = smem_u32(dLtB);
-          for (int ks = 0; ks < TILE / 8; ++ks) {
+          for (int k8 = 0; k8 < UW / 8; ++k8) {
+            const int ks = h * (UW / 8) + k8;
             const uint32_t acc = (it > 0 || ks > 0) ? 1u : 0u;
-            mma_ts(tP0 + blk * KP, tD1 + ks * 8, make_desc_sw128(zt0 + (ks >> 2) * KP * 128 + (ks & 3) * 32), idesc_p, acc);
-            mma_ts(tW0 + blk * 32, tGl + ks * 8, make_desc_sw128(lt0 + (ks >> 2) * 32 * 128 + (ks & 3) * 32), idesc_w, acc);
+            mma_ts(tP0 + blk * KP, tDb(b) + k8 * 8, make_desc_sw128(zt0 + (ks >> 2) * KP * 128 + (ks & 3) * 32), idesc_p, acc);
+            mma_ts(tW0 + blk * 32, tDb(b) + UW + k8 * 8, make_desc_sw128(lt0 + (ks >> 2) * 32 * 128 + (ks & 3) * 32), idesc_w, acc);
           }
+          if (j + 2 < NU) issue_d(j + 2);      // same buffer: executes after the accumulate MMAs just issued
         }
         mma_commit(bar_free);
         DP_PHASE(1, 8 + it * 8);
@@ -537,26 +553,29 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
     }
     const float eps = p.eps, epsm1 = p.eps - 1.f;
     const bool act_log = p.act_mode == ADLM_ACT_LOG;
-    uint32_t g = 0;
+    uint32_t acnt[2] = {0u, 0u};
     for (int it = 0; it < iters; ++it) {
       const long long m0 = ((long long)blockIdx.x + (long long)it * gridDim.x) * TILE;
       const int npx = (int)((p.M - m0) < TILE ? (p.M - m0) : TILE);   // valid pixel columns of this tile
       if (warp == 0) DP_PHASE(2, 1 + it * 8);
       mbar_wait(bar_full, (uint32_t)it & 1u);
 #pragma unroll
-      for (int blk = 0; blk < NB; ++blk) {
+      for (int j = 0; j < NU; ++j) {
+        const int blk = j >> 1, h = j & 1, b = j & 1;
         const int n = blk * 128 + lane_n;
-        if (warp == 0) DP_PHASE(2, 2 + it * 8 + blk * 3);
-        mbar_wait(bar_acc, g & 1u);
-        if (warp == 0) DP_PHASE(2, 3 + it * 8 + blk * 3);
-        ++g;
+        const uint32_t tD1 = tDb(b), tGl = tDb(b) + UW;
+        if (warp == 0 && h == 0) DP_PHASE(2, 2 + it * 8 + blk * 3);
+        mbar_wait(bar_acc0 + b * 8, acnt[b] & 1u);
+        if (warp == 0 && h == 0) DP_PHASE(2, 3 + it * 8 + blk * 3);
+        ++acnt[b];
         fence_after();
         if (blk * 128 + (warp & 3) * 32 < N) {       // warps whose 32 prototypes are all padding skip the math
-          for (int ch = 0; ch < 4; ++ch) {
-            const int c0 = half * 64 + ch * 16;
+          for (int ch = 0; ch < 2; ++ch) {
+            const int cl = half * 32 + ch * 16;       // column inside the unit's TMEM buffer
+            const int c0 = h * UW + cl;               // pixel column of the tile
             uint32_t ra[16], rg[16], og[16], os[16];
-            tmem_ld16(tD1 + lane_field + c0, ra);
-            tmem_ld16(tGl + lane_field + c0, rg);
+            tmem_ld16(tD1 + lane_field + cl, ra);
+            tmem_ld16(tGl + lane_field + cl, rg);
             float xp[16];
 #pragma unroll
             for (int v4 = 0; v4 < 4; ++v4) {
@@ -606,14 +625,14 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
               og[i] = __float_as_uint(rna_tf32_fast(gv));
               os[i] = __float_as_uint(rna_tf32_fast(((vmask >> i) & 1u) ? sv[i] : 0.f));
             }
-            tmem_st16(tD1 + lane_field + c0, og);
-            tmem_st16(tGl + lane_field + c0, os);
+            tmem_st16(tD1 + lane_field + cl, og);
+            tmem_st16(tGl + lane_field + cl, os);
           }
           tmem_st_wait();
         }
         fence_before();
-        mbar_arrive(bar_gs);
-        if (warp == 0) DP_PHASE(2, 4 + it * 8 + blk * 3);
+        mbar_arrive(bar_gs0 + b * 8);
+        if (warp == 0 && h == 1) DP_PHASE(2, 4 + it * 8 + blk * 3);
       }
     }
     // ---- flush this CTA's partial sums ----
