@@ -329,10 +329,12 @@ struct DpSmem {
   static __host__ __device__ size_t zk(int Npad2, int C8) { return wt(Npad2) + (size_t)C8 * Npad2 * 4; }
   static __host__ __device__ size_t dlk(int Npad2, int C8) { return zk(Npad2, C8) + (size_t)KP * TILE * 4; }
   static __host__ __device__ size_t misc(int Npad2, int C8) { return dlk(Npad2, C8) + (size_t)C8 * TILE * 4; }
-  // x2 [128] f32, lab [128] i32, img [128] i32, pix [128] i32, cs [2][2][128] f32, barriers
-  // ... + own-class KLD gradients of the tile [128 px][16] f32 (cp.async by the builder warps)
-  static __host__ __device__ size_t ogs(int Npad2, int C8) { return misc(Npad2, C8) + 128 * 16 + 512 * 4 + 128 + 512; }
-  static __host__ __device__ size_t total(int Npad2, int C8) { return ogs(Npad2, C8) + 128 * 16 * 4; }
+  // per-tile metadata in two slots (tile parity): x2 [2][128] f32, img [2][128] i32, pix [2][128] i32,
+  // class pixel masks [2][32][4] u32; then cs [2][2][128] f32, barriers + TMEM base (128 B)
+  // ... + own-class KLD gradients of the tile [2][128 px][16] f32 (cp.async by the builder warps)
+  static constexpr size_t MISC_BYTES = 3 * 1024 + 1024 + 2048 + 128;
+  static __host__ __device__ size_t ogs(int Npad2, int C8) { return misc(Npad2, C8) + MISC_BYTES; }
+  static __host__ __device__ size_t total(int Npad2, int C8) { return ogs(Npad2, C8) + 2 * 128 * 16 * 4; }
 };
 
 template <int KP, int NB, bool GENERIC>
@@ -349,15 +351,14 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
   float* ZkB = reinterpret_cast<float*>(smem + L::zk(Npad2, C8));
   float* dLkB = reinterpret_cast<float*>(smem + L::dlk(Npad2, C8));
   uint8_t* misc = smem + L::misc(Npad2, C8);
-  float* x2s = reinterpret_cast<float*>(misc);
-  int* labs = reinterpret_cast<int*>(misc + 512);
-  int* imgs = reinterpret_cast<int*>(misc + 1024);
-  int* pixs = reinterpret_cast<int*>(misc + 1536);
-  float* css = reinterpret_cast<float*>(misc + 2048);           // [half][blk][128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(misc + 2048 + 2048);
-  uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 7);   // six barriers, then the TMEM base
-  uint32_t* clsm = reinterpret_cast<uint32_t*>(misc + 2048 + 2048 + 64);   // [32 classes][4 words]: pixels of the tile
-  float* ogs = reinterpret_cast<float*>(smem + L::ogs(Npad2, C8));           // [128 px][16]: dL/d(own distances)
+  float* x2s = reinterpret_cast<float*>(misc);                      // [slot][128]
+  int* imgs = reinterpret_cast<int*>(misc + 1024);                   // [slot][128]
+  int* pixs = reinterpret_cast<int*>(misc + 2048);                   // [slot][128]
+  uint32_t* clsm = reinterpret_cast<uint32_t*>(misc + 3072);         // [slot][32 classes][4 words]: pixels of the tile
+  float* css = reinterpret_cast<float*>(misc + 4096);                // [half][blk][128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(misc + 4096 + 2048);
+  uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 8);     // seven barriers, then the TMEM base
+  float* ogs = reinterpret_cast<float*>(smem + L::ogs(Npad2, C8));   // [slot][128 px][16]: dL/d(own distances)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const bool kld = p.own_grad != nullptr;
@@ -366,12 +367,13 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
 
   if (warp == 12) tmem_alloc(smem_u32(tmem_base_s), 512);
   if (tid == 0) {
-    mbar_init(smem_u32(&bars[0]), 128);   // full: pixel operands written
+    mbar_init(smem_u32(&bars[0]), 128);   // full_k: K-major pixel operands (distance MMAs) + tile metadata written
     mbar_init(smem_u32(&bars[1]), 1);     // free: every MMA of the tile done
     mbar_init(smem_u32(&bars[2]), 1);     // acc[b]: D^T and Gl^T of a unit ready in TMEM buffer b
     mbar_init(smem_u32(&bars[3]), 1);
     mbar_init(smem_u32(&bars[4]), 256);   // gs[b]: G and S of the unit written back to TMEM buffer b
     mbar_init(smem_u32(&bars[5]), 256);
+    mbar_init(smem_u32(&bars[6]), 128);   // full_t: transposed pixel operands (accumulate MMAs) written
     mbar_init_fence();
   }
   // the builder warps fetch their first tile before the one-time operand staging
@@ -424,8 +426,11 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
   constexpr int UW = 64, NU = 2 * NB;
   const uint32_t tP0 = tmem_base + 256, tW0 = tmem_base + 256 + NB * KP;
   auto tDb = [&](int b) { return tmem_base + (uint32_t)b * 128u; };
+  // The units of consecutive tiles form one stream.  The builder writes a tile in two steps: the K-major operands
+  // and the metadata as soon as the previous tile's last distance MMA has retired (they are consumed two units
+  // ahead of the epilogue), the transposed operands once the previous tile's accumulate MMAs are done.
   const uint32_t bar_full = smem_u32(&bars[0]), bar_free = smem_u32(&bars[1]), bar_acc0 = smem_u32(&bars[2]),
-                 bar_gs0 = smem_u32(&bars[4]);
+                 bar_gs0 = smem_u32(&bars[4]), bar_full_t = smem_u32(&bars[6]);
 
   if (is_builder) {
     prefetch(0);
@@ -433,21 +438,26 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
     for (int it = 0; it < iters; ++it) {
       const int m = ((int)blockIdx.x + it * (int)gridDim.x) * TILE + cw;
       const bool valid = m < Mi;
+      const int slot = it & 1;
+      uint32_t* clsm_s = clsm + slot * 128;
+      float* ogs_s = ogs + slot * 128 * JMAX;
       if (warp == 8) DP_PHASE(0, 1 + it * 8);
-      if (it > 0) mbar_wait(bar_free, (uint32_t)(it - 1) & 1u);
+      // ---- step K: wait until the last distance MMA of the previous tile has read ZkB / dLkB
+      //      (completion number it * NU/2 of acc[1]; the next one needs this step's full_k, so no aliasing)
+      if (it > 0) mbar_wait(bar_acc0 + 8, (uint32_t)(it * (NU / 2) - 1) & 1u);
       if (warp == 8) DP_PHASE(0, 2 + it * 8);
-      clsm[cw] = 0u;
+      clsm_s[cw] = 0u;
       if (kld && valid) {
         // the tile's own-class KLD gradients travel straight into shared memory while the operands are converted
         const float* src = p.own_grad + (size_t)m * JMAX;
-        const uint32_t dst = smem_u32(ogs + cw * JMAX);
+        const uint32_t dst = smem_u32(ogs_s + cw * JMAX);
 #pragma unroll
         for (int v = 0; v < JMAX / 4; ++v)
           asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst + v * 16), "l"(src + v * 4) : "memory");
       }
       named_bar_sync(2, 128);
       const int mylab = (valid && kld) ? p.target[m] : -1;
-      if (mylab >= 0 && mylab < 32) atomicOr(&clsm[mylab * 4 + (cw >> 5)], 1u << (cw & 31));
+      if (mylab >= 0 && mylab < 32) atomicOr(&clsm_s[mylab * 4 + (cw >> 5)], 1u << (cw & 31));
       float x2 = 0.f;
 #pragma unroll
       for (int k4 = 0; k4 < KP / 4; ++k4) {
@@ -455,8 +465,8 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           v[j] = rna_tf32_mask(zr[k4 * 4 + j] - CENTRE);
+          zr[k4 * 4 + j] = v[j];
           x2 = fmaf(v[j], v[j], x2);
-          ZtB[off_sw128(k4 * 4 + j, cw, KP)] = v[j];
         }
         *reinterpret_cast<float4*>(ZkB + ((size_t)k4 * TILE + cw) * 4) = make_float4(v[0], v[1], v[2], v[3]);
       }
@@ -467,20 +477,28 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             v[j] = rna_tf32_fast(dlr[c4 * 4 + j]);
-            if (c4 * 4 + j < C) dLtB[off_sw128(c4 * 4 + j, cw, 32)] = v[j];
+            dlr[c4 * 4 + j] = v[j];
           }
           *reinterpret_cast<float4*>(dLkB + ((size_t)c4 * TILE + cw) * 4) = make_float4(v[0], v[1], v[2], v[3]);
         }
       }
-      x2s[cw] = x2;
+      x2s[slot * 128 + cw] = x2;
       const int b = valid ? m / HW : 0;
-      imgs[cw] = b;
-      pixs[cw] = valid ? m - b * HW : 0;
-      labs[cw] = valid ? mylab : -2;
+      imgs[slot * 128 + cw] = b;
+      pixs[slot * 128 + cw] = valid ? m - b * HW : 0;
       asm volatile("cp.async.wait_all;" ::: "memory");
       fence_async_smem();
       mbar_arrive(bar_full);
       if (warp == 8) DP_PHASE(0, 3 + it * 8);
+      // ---- step T: the transposed operands, once the previous tile's accumulate MMAs have retired
+      if (it > 0) mbar_wait(bar_free, (uint32_t)(it - 1) & 1u);
+#pragma unroll
+      for (int k = 0; k < KP; ++k) ZtB[off_sw128(k, cw, KP)] = zr[k];
+#pragma unroll
+      for (int c = 0; c < 32; ++c)
+        if (c < C) dLtB[off_sw128(c, cw, 32)] = dlr[c];
+      fence_async_smem();
+      mbar_arrive(bar_full_t);
       prefetch(it + 1);
       if (warp == 8) DP_PHASE(0, 4 + it * 8);
     }
@@ -503,18 +521,18 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
         mma_commit(bar_acc0 + b * 8);
       };
       uint32_t gcnt[2] = {0u, 0u};
+      mbar_wait(bar_full, 0u);
+      fence_after();
+      issue_d(0);
+      issue_d(1);
       for (int it = 0; it < iters; ++it) {
-        mbar_wait(bar_full, (uint32_t)it & 1u);
-        fence_after();
         DP_PHASE(1, 1 + it * 8);
-        issue_d(0);
-        issue_d(1);
-        DP_PHASE(1, 2 + it * 8);
 #pragma unroll
         for (int j = 0; j < NU; ++j) {
           const int blk = j >> 1, h = j & 1, b = j & 1;
           mbar_wait(bar_gs0 + b * 8, gcnt[b] & 1u);
           ++gcnt[b];
+          if (j == 0) mbar_wait(bar_full_t, (uint32_t)it & 1u);
           fence_after();
           if (j == 0) DP_PHASE(1, 3 + it * 8);
           const uint32_t zt0 = smem_u32(ZtB), lt0 = smem_u32(dLtB);
@@ -524,9 +542,18 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
             mma_ts(tP0 + blk * KP, tDb(b) + k8 * 8, make_desc_sw128(zt0 + (ks >> 2) * KP * 128 + (ks & 3) * 32), idesc_p, acc);
             mma_ts(tW0 + blk * 32, tDb(b) + UW + k8 * 8, make_desc_sw128(lt0 + (ks >> 2) * 32 * 128 + (ks & 3) * 32), idesc_w, acc);
           }
-          if (j + 2 < NU) issue_d(j + 2);      // same buffer: executes after the accumulate MMAs just issued
+          if (j == NU - 1) mma_commit(bar_free);
+          // the distance MMAs two units ahead go into the buffer the accumulate MMAs above read: issue order
+          if (j + 2 < NU) {
+            issue_d(j + 2);
+          } else if (it + 1 < iters) {
+            if (j + 2 - NU == 0) {
+              mbar_wait(bar_full, (uint32_t)(it + 1) & 1u);
+              fence_after();
+            }
+            issue_d(j + 2 - NU);
+          }
         }
-        mma_commit(bar_free);
         DP_PHASE(1, 8 + it * 8);
       }
     }
@@ -559,6 +586,12 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
       const int npx = (int)((p.M - m0) < TILE ? (p.M - m0) : TILE);   // valid pixel columns of this tile
       if (warp == 0) DP_PHASE(2, 1 + it * 8);
       mbar_wait(bar_full, (uint32_t)it & 1u);
+      const int slot = it & 1;
+      const float* x2s_s = x2s + slot * 128;
+      const uint32_t* clsm_s = clsm + slot * 128;
+      const float* ogs_s = ogs + slot * 128 * JMAX;
+      const int* imgs_s = imgs + slot * 128;
+      const int* pixs_s = pixs + slot * 128;
 #pragma unroll
       for (int j = 0; j < NU; ++j) {
         const int blk = j >> 1, h = j & 1, b = j & 1;
@@ -579,11 +612,11 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
             float xp[16];
 #pragma unroll
             for (int v4 = 0; v4 < 4; ++v4) {
-              const float4 q = *reinterpret_cast<const float4*>(x2s + c0 + v4 * 4);
+              const float4 q = *reinterpret_cast<const float4*>(x2s_s + c0 + v4 * 4);
               xp[v4 * 4] = q.x + p2[blk]; xp[v4 * 4 + 1] = q.y + p2[blk]; xp[v4 * 4 + 2] = q.z + p2[blk]; xp[v4 * 4 + 3] = q.w + p2[blk];
             }
             // own-class pixels of this prototype among the 16 columns (KLD term), and the valid columns
-            const uint32_t hit = pcl[blk] >= 0 ? ((clsm[pcl[blk] * 4 + (c0 >> 5)] >> (c0 & 31)) & 0xffffu) : 0u;
+            const uint32_t hit = pcl[blk] >= 0 ? ((clsm_s[pcl[blk] * 4 + (c0 >> 5)] >> (c0 & 31)) & 0xffffu) : 0u;
             const int nv = npx - c0;
             const uint32_t vmask = (n < N && nv > 0) ? (nv >= 16 ? 0xffffu : ((1u << nv) - 1u)) : 0u;
             tmem_ld_wait();
@@ -608,7 +641,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
               }
               if (GENERIC) {
                 if (p.ddist != nullptr && ((vmask >> i) & 1u))
-                  gv += __ldg(p.ddist + ((size_t)imgs[c0 + i] * N + n) * HW + pixs[c0 + i]);
+                  gv += __ldg(p.ddist + ((size_t)imgs_s[c0 + i] * N + n) * HW + pixs_s[c0 + i]);
               }
               pos |= (pre > 0.f ? 1u : 0u) << i;
               gvv[i] = gv;
@@ -616,7 +649,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
             if (hit) {
 #pragma unroll
               for (int i = 0; i < 16; ++i)
-                if ((hit >> i) & 1u) gvv[i] += ogs[(c0 + i) * JMAX + prk[blk]];
+                if ((hit >> i) & 1u) gvv[i] += ogs_s[(c0 + i) * JMAX + prk[blk]];
             }
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
