@@ -18,7 +18,7 @@ MAX_PROTOS_PER_CLASS = 16
 MAX_PUSH_CLASSES = 32
 STEP_NSCALARS = 8
 PUSH_NONE = 0x7FFFFFFFFFFFFFFF
-ABI_VERSION = 5
+ABI_VERSION = 6
 DP_MAX_WORLD = 16
 
 # name -> (restype, argtypes); kept next to include/adlm_head.h (tests check they agree)
@@ -64,6 +64,15 @@ SIGNATURES["adlm_step_fwd_bwd_dp"] = (c_int, [c_void_p, c_int, c_int, c_int, c_v
                                               c_float, c_float, c_float, c_float,
                                               c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                               c_void_p, c_void_p, c_size_t, ctypes.POINTER(DpComm), c_void_p])
+
+SIGNATURES["adlm_head_fwd_pre"] = (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int,
+                                           c_float, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                           c_void_p])
+SIGNATURES["adlm_step_fwd_bwd_pre"] = (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int,
+                                               c_float, c_int, c_void_p, c_void_p, c_int,
+                                               c_float, c_float, c_float, c_float, c_void_p,
+                                               c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                               c_void_p, c_void_p, c_size_t, c_void_p])
 
 _lib = None
 

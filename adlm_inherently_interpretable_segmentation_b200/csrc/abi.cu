@@ -84,6 +84,10 @@ bool head_bwd_fuses_finalize(const HeadShape& s, int prec_mode, const float* dP,
   return prec_mode == ADLM_PREC_TF32 && s.K <= 64 && s.N <= 192 && s.C <= 32 && dW != nullptr && dP != nullptr;
 }
 
+bool head_fuses_sigmoid(const HeadShape& s, int prec_mode) {
+  return prec_mode == ADLM_PREC_TF32 && s.K <= 64 && s.N <= 192 && s.C <= 32;
+}
+
 size_t head_bwd_workspace_bytes(int prec_mode, int K, int N) {
   if (prec_mode != ADLM_PREC_TF32 || K > 64 || N > 192) return 0;
   return tc_bwd_workspace_bytes(K, N);
@@ -177,7 +181,7 @@ int adlm_step_fwd_bwd(const float* z, int B, int K, int HW, const float* P, cons
   HeadShape s{B, K, HW, N, C, eps, ADLM_ACT_LOG};
   return step_fwd_bwd_impl(s, prec_mode, z, P, W, target, proto_class, ignore_void, w_ce, w_kld, w_l1,
                            grad_scale, global_counts, logits_out, argmax_out, dz, dP, dW, scalars, workspace,
-                           nullptr, (cudaStream_t)stream);
+                           nullptr, nullptr, (cudaStream_t)stream);
 }
 
 size_t adlm_dp_exchange_bytes(int K, int N, int C, int world) {
@@ -227,7 +231,44 @@ int adlm_step_fwd_bwd_dp(const float* z, int B, int K, int HW, const float* P, c
   HeadShape s{B, K, HW, N, C, eps, ADLM_ACT_LOG};
   return step_fwd_bwd_impl(s, prec_mode, z, P, W, target, proto_class, ignore_void, w_ce, w_kld, w_l1,
                            grad_scale, nullptr, logits_out, argmax_out, dz, dP, dW, scalars, workspace,
-                           &cm, (cudaStream_t)stream);
+                           &cm, nullptr, (cudaStream_t)stream);
+}
+
+int adlm_head_fwd_pre(const float* pre, int B, int K, int HW, const float* P, const float* W, int N, int C,
+                      float eps, int act_mode, int prec_mode, float* z_out, float* logits, float* dist, float* sim,
+                      int32_t* argmax, void* stream) {
+  int rc = check_shape(__func__, B, K, HW, N, C);
+  if (rc != ADLM_OK) return rc;
+  ADLM_CHECK_ARG(pre && P && W && logits && z_out, "pre, P, W, z_out and logits must be non-null");
+  ADLM_CHECK_ARG(act_mode == ADLM_ACT_LOG || act_mode == ADLM_ACT_LINEAR, "unknown act_mode");
+  HeadShape s{B, K, HW, N, C, eps, act_mode};
+  if (!head_fuses_sigmoid(s, prec_mode)) {
+    set_error("%s: unsupported: needs ADLM_PREC_TF32, K <= 64, N <= 192, C <= 32", __func__);
+    return ADLM_E_UNSUPPORTED;
+  }
+  StepExtras ex;
+  ex.z_out = z_out;
+  return head_fwd_dispatch(s, prec_mode, pre, P, W, logits, dist, sim, argmax, ex, (cudaStream_t)stream);
+}
+
+int adlm_step_fwd_bwd_pre(const float* pre, int B, int K, int HW, const float* P, const float* W, int N, int C,
+                          float eps, int prec_mode, const int32_t* target, const int32_t* proto_class,
+                          int ignore_void, float w_ce, float w_kld, float w_l1, float grad_scale,
+                          const int32_t* global_counts, float* z_out, float* logits_out, int32_t* argmax_out,
+                          float* dpre, float* dP, float* dW, double* scalars, void* workspace,
+                          size_t workspace_bytes, void* stream) {
+  int rc = check_shape(__func__, B, K, HW, N, C);
+  if (rc != ADLM_OK) return rc;
+  ADLM_CHECK_ARG(pre && P && W && target && proto_class && scalars && workspace && z_out, "null pointer argument");
+  ADLM_CHECK_ARG(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  if (workspace_bytes < step_workspace_bytes(B, K, HW, N, C)) {
+    set_error("%s: workspace too small (%zu < %zu)", __func__, workspace_bytes, step_workspace_bytes(B, K, HW, N, C));
+    return ADLM_E_WORKSPACE;
+  }
+  HeadShape s{B, K, HW, N, C, eps, ADLM_ACT_LOG};
+  return step_fwd_bwd_impl(s, prec_mode, pre, P, W, target, proto_class, ignore_void, w_ce, w_kld, w_l1,
+                           grad_scale, global_counts, logits_out, argmax_out, dpre, dP, dW, scalars, workspace,
+                           nullptr, z_out, (cudaStream_t)stream);
 }
 
 int adlm_step_counts(const int32_t* target, int B, int HW, const int32_t* proto_class, int N, int C,

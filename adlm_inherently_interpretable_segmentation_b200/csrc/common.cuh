@@ -167,6 +167,11 @@ struct StepExtras {
   double* ce_accum = nullptr;            // [0] += loss sum, [1] += correct
   float ce_scale = 0.f;                  // w_ce * grad_scale
   int ignore_void = 0;
+  // fused add-on activation (model.py:124-128,174: add_on_layers = Sigmoid): the forward reads PRE-sigmoid
+  // features, applies the sigmoid while staging the tile and writes z to z_out; the dZ kernel multiplies by
+  // z (1 - z).  Honoured by the tensor-core kernels only — callers must check head_fuses_sigmoid()
+  float* z_out = nullptr;                // fwd: [B,K,HW] sigmoid(input); null = input already is z
+  int dz_sigmoid = 0;                    // bwd: dz <- dz * z (1 - z)
   // fused step epilogue (L1 term of dW, L1 value, the 8 scalars; module.py:213-222) inside the partials
   // reduction of the tensor-core backward — callers must check head_bwd_fuses_finalize()
   StepFinalize fin;
@@ -174,6 +179,7 @@ struct StepExtras {
 // true when head_fwd_dispatch(prec_mode, shape) runs the kernel that honours the ce_* extras
 bool head_fwd_fuses_ce(const HeadShape& s, int prec_mode);
 bool head_bwd_fuses_finalize(const HeadShape& s, int prec_mode, const float* dP, const float* dW);
+bool head_fuses_sigmoid(const HeadShape& s, int prec_mode);
 
 int simt_head_fwd(const HeadShape& s, const float* z, const float* P, const float* W,
                   float* logits, float* dist, float* sim, int32_t* argmax,
@@ -198,7 +204,7 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
                       const int32_t* target, const int32_t* proto_class, int ignore_void,
                       float w_ce, float w_kld, float w_l1, float grad_scale, const int32_t* global_counts,
                       float* logits_out, int32_t* argmax_out, float* dz, float* dP, float* dW,
-                      double* scalars, void* workspace, const DpComm* comm, cudaStream_t st);
+                      double* scalars, void* workspace, const DpComm* comm, float* z_out, cudaStream_t st);
 int step_counts_impl(const int32_t* target, int B, int HW, const int32_t* proto_class, int N, int C,
                      int ignore_void, int32_t* counts_out, void* workspace, cudaStream_t st);
 

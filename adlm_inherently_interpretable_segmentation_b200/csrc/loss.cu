@@ -423,7 +423,9 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
                       const int32_t* target, const int32_t* proto_class, int ignore_void,
                       float w_ce, float w_kld, float w_l1, float grad_scale, const int32_t* global_counts,
                       float* logits_out, int32_t* argmax_out, float* dz, float* dP, float* dW,
-                      double* scalars, void* workspace, const DpComm* comm, cudaStream_t st) {
+                      double* scalars, void* workspace, const DpComm* comm, float* z_out, cudaStream_t st) {
+  // z_out != null: `z` holds PRE-sigmoid features; the forward writes z = sigmoid(z) to z_out and dz is the gradient
+  // wrt the pre-sigmoid features (fused add-on layer, model.py:124-128,174)
   const int B = s.B, HW = s.HW, N = s.N, C = s.C;
   const long long M = (long long)B * HW;
   StepWorkspace ws = carve_step_workspace(workspace, B, s.K, HW, N, C);
@@ -454,6 +456,13 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
   ex.proto_rank = ws.rank;
   ex.own_dist = ws.own;
   const bool fuse_ce = head_fwd_fuses_ce(s, prec_mode);
+  if (z_out != nullptr) {
+    if (!head_fuses_sigmoid(s, prec_mode) || !fuse_ce) {
+      set_error("fused sigmoid prologue needs ADLM_PREC_TF32, K <= 64, N <= 192, C <= 32");
+      return ADLM_E_UNSUPPORTED;
+    }
+    ex.z_out = z_out;
+  }
   if (fuse_ce) {
     // CE, accuracy and dlogits come out of the forward kernel's logits registers; logits touch HBM only on request
     ex.ce_counts = counts;
@@ -484,6 +493,8 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
     StepExtras exb = ex;
     exb.own_dist = nullptr;
     exb.own_grad = ws.own_grad;
+    exb.z_out = nullptr;
+    exb.dz_sigmoid = z_out != nullptr ? 1 : 0;
     if (head_bwd_fuses_finalize(s, prec_mode, dP, dW)) {
       exb.fin.scalars = scalars;
       exb.fin.counts = counts;
@@ -495,7 +506,7 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
       }
       fin_fused = true;
     }
-    if ((rc = head_bwd_dispatch(s, prec_mode, z, P, W, ws.dlogits, nullptr, nullptr, dz, dP, dW, exb, ws.bwd_scratch,
+    if ((rc = head_bwd_dispatch(s, prec_mode, z_out ? z_out : z, P, W, ws.dlogits, nullptr, nullptr, dz, dP, dW, exb, ws.bwd_scratch,
                                 ws.bwd_scratch_bytes, st)) != ADLM_OK)
       return rc;
   }

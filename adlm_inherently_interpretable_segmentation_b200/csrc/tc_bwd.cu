@@ -48,6 +48,7 @@ struct TcBwdParams {
   const int32_t* proto_rank;
   const float* own_grad;  // [M, JMAX] | null
   float* dz;              // [B, K, HW]
+  int dz_sigmoid;         // dz <- dz * z (1 - z): gradient wrt the pre-sigmoid features
   float* partials;        // [grid][Npad2*KP + Npad2*32]
   int B, K, HW, N, C;
   float eps;
@@ -303,7 +304,13 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           const int k = ch * 16 + i;
-          if (k < K) dst[(size_t)k * HW] = 2.f * fmaf(rs, zc[i], -__uint_as_float(r[i]));
+          if (k < K) {
+            float gz = 2.f * fmaf(rs, zc[i], -__uint_as_float(r[i]));
+            if (p.dz_sigmoid) {                       // z = zc + 1/2 (tf32-rounded): z (1 - z) = 1/4 - zc^2
+              gz *= fmaf(-zc[i], zc[i], 0.25f);
+            }
+            dst[(size_t)k * HW] = gz;
+          }
         }
       }
     }
@@ -947,6 +954,10 @@ int tc_head_bwd(const HeadShape& s, int prec_mode, const float* z, const float* 
   if (!tc_bwd_supported(s, prec_mode)) {
     // 3xTF32 (fp32-class) and shapes beyond the tensor-core backward's operand budget take the fp32
     // CUDA-core backward: same mathematics, tighter arithmetic
+    if (ex.dz_sigmoid) {
+      set_error("tc_head_bwd: the fused sigmoid backward needs ADLM_PREC_TF32, K <= 64, N <= 192, C <= 32");
+      return ADLM_E_UNSUPPORTED;
+    }
     return simt_head_bwd(s, z, P, W, dlogits, ddist, dsim, dz, dP, dW, ex, st);
   }
   TcBwdParams prm;
@@ -955,6 +966,7 @@ int tc_head_bwd(const HeadShape& s, int prec_mode, const float* z, const float* 
   prm.target = ex.own_grad ? ex.target : nullptr;
   prm.proto_class = ex.proto_class; prm.proto_rank = ex.proto_rank; prm.own_grad = ex.own_grad;
   prm.dz = dz; prm.partials = nullptr;
+  prm.dz_sigmoid = ex.dz_sigmoid;
   prm.B = s.B; prm.K = s.K; prm.HW = s.HW; prm.N = s.N; prm.C = s.C;
   prm.eps = s.eps; prm.act_mode = s.act_mode;
   prm.Npad = (s.N + 31) & ~31;

@@ -22,6 +22,7 @@ struct TcFwdParams {
   double* ce_accum;           // [0] += sum of losses, [1] += correct patches
   float ce_scale;             // w_ce * grad_scale
   int ignore_void;
+  float* z_out;               // [B,K,HW] | null: input is pre-sigmoid, z = sigmoid(input) is written here
   int B, K, HW, N, C;
   float eps;
   int act_mode;

@@ -172,6 +172,20 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
       if (warp == 8) WS_PHASE(2, 1 + it * 4);
       if (j > 0) mbar_wait(bar(B_SFREE + a), (uint32_t)(j - 1) & 1u);    // MMA1 of tile it-2 has read the stage
       if (warp == 8) WS_PHASE(2, 2 + it * 4);
+      if (p.z_out != nullptr) {
+        // fused add-on activation: the tile holds pre-sigmoid features; z is needed again by the backward
+        // kernels and by the callers (forward_with_features, push), so it is written out once from here
+        const int m = tile_of(it) * TILE + cw;
+        const bool ok = m < Mi;
+        const int bi = ok ? m / HW : 0;
+        float* zo = p.z_out + ((size_t)bi * K) * HW + (m - bi * HW);
+#pragma unroll
+        for (int k = 0; k < KP; ++k) {
+          const float zv = rcp_approx(1.f + ex2_approx(-1.4426950408889634f * zr[k]));
+          if (ok && k < K) zo[(size_t)k * HW] = zv;
+          zr[k] = (ok && k < K) ? zv : CENTRE;
+        }
+      }
       float x2 = 0.f;
 #pragma unroll
       for (int k4 = 0; k4 < KP / 4; ++k4) {

@@ -58,9 +58,11 @@ def _proto_2d(prototype_vectors):
 
 
 def head_forward(z, prototypes, weight, eps=1e-4, activation="log", precision=None,
-                 want_dist=True, want_sim=False, want_argmax=False):
+                 want_dist=True, want_sim=False, want_argmax=False, pre_sigmoid=False):
     """z (B,K,h,w) -> dict(logits (B,h,w,C), dist (B,N,h,w)|None, sim (B*h*w,N)|None, argmax (B,h,w)|None).
-    Mirrors model.py:259-283 (patch-classification branch)."""
+    Mirrors model.py:259-283 (patch-classification branch).
+    pre_sigmoid: `z` holds the features BEFORE the add-on Sigmoid (model.py:124-128,174); the kernel applies it while
+    staging the tiles and the result carries z = sigmoid(input) under key "z" (adlm_head_fwd_pre; tf32 only)."""
     lib = _lib.load()
     _check_cuda_f32("conv_features", z)
     _check_cuda_f32("prototype_vectors", prototypes)
@@ -81,6 +83,14 @@ def head_forward(z, prototypes, weight, eps=1e-4, activation="log", precision=No
         dist = torch.empty((B, N, h, w), device=dev, dtype=torch.float32) if want_dist else None
         sim = torch.empty((B * HW, N), device=dev, dtype=torch.float32) if want_sim else None
         amax = torch.empty((B, h, w), device=dev, dtype=torch.int32) if want_argmax else None
+        if pre_sigmoid:
+            z_out = torch.empty_like(z)
+            rc = lib.adlm_head_fwd_pre(_lib.ptr(z), B, K, HW, _lib.ptr(P), _lib.ptr(W), N, C,
+                                       c_float(eps), _act(activation), _prec(precision or DEFAULT_PRECISION),
+                                       _lib.ptr(z_out), _lib.ptr(logits), _lib.ptr(dist), _lib.ptr(sim),
+                                       _lib.ptr(amax), _lib.stream_ptr())
+            _lib.check(rc, "adlm_head_fwd_pre")
+            return dict(logits=logits, dist=dist, sim=sim, argmax=amax, z=z_out)
         rc = lib.adlm_head_fwd(_lib.ptr(z), B, K, HW, _lib.ptr(P), _lib.ptr(W), N, C,
                                c_float(eps), _act(activation), _prec(precision or DEFAULT_PRECISION),
                                _lib.ptr(logits), _lib.ptr(dist), _lib.ptr(sim), _lib.ptr(amax),
@@ -174,7 +184,7 @@ class _StepResult(dict):
 def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
                weights=(1.0, 0.25, 1e-4), grad_scale=1.0, eps=1e-4, precision=None,
                need_grads=True, want_logits=False, want_argmax=False, workspace=None, global_counts=None,
-               grads_out=None, dz_out=None, dp_comm=None):
+               grads_out=None, dz_out=None, dp_comm=None, pre_sigmoid=False):
     """One C-ABI call for module.py:137-222 + :236 on given features.
 
     z (B,K,h,w); target (B,h,w) integer labels already resized to the feature map (dataset.py:23-31);
@@ -186,7 +196,10 @@ def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
     CUDA buffer with at least N*K + C*N elements; dP and dW are then views into it ([dP | dW], one collective).
     dz_out: optional preallocated contiguous fp32 CUDA tensor shaped like z that receives dz (pipelined callers).
     dp_comm: a parallel.DpExchange — the step then runs adlm_step_fwd_bwd_dp: normalisers, dP, dW and the loss
-    sums are exchanged with the peer GPUs inside the step's own kernels (no collective call afterwards)."""
+    sums are exchanged with the peer GPUs inside the step's own kernels (no collective call afterwards).
+    pre_sigmoid: `z` holds the features BEFORE the add-on Sigmoid; the step applies it in the forward kernel,
+    returns z = sigmoid(input) under "z" and dz is the gradient wrt the pre-sigmoid input
+    (adlm_step_fwd_bwd_pre; tf32 only, not combined with dp_comm)."""
     lib = _lib.load()
     _check_cuda_f32("conv_features", z)
     _check_cuda_f32("prototype_vectors", prototypes)
@@ -226,7 +239,20 @@ def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
             dW = torch.empty((C, N), device=dev, dtype=torch.float32) if need_grads else None
         logits = torch.empty((B, h, w, C), device=dev, dtype=torch.float32) if want_logits else None
         amax = torch.empty((B, h, w), device=dev, dtype=torch.int32) if want_argmax else None
-        if dp_comm is not None:
+        z_feat = None
+        if pre_sigmoid:
+            if dp_comm is not None:
+                raise NotImplementedError("pre_sigmoid and dp_comm are not combined (apply torch.sigmoid first)")
+            z_feat = torch.empty_like(z)
+            rc = lib.adlm_step_fwd_bwd_pre(_lib.ptr(z), B, K, HW, _lib.ptr(P), _lib.ptr(W), N, C, c_float(eps),
+                                           _prec(precision or DEFAULT_PRECISION), _lib.ptr(tgt), _lib.ptr(pc),
+                                           c_int(1 if ignore_void else 0), c_float(w_ce), c_float(w_kld),
+                                           c_float(w_l1), c_float(grad_scale), _lib.ptr(global_counts),
+                                           _lib.ptr(z_feat), _lib.ptr(logits), _lib.ptr(amax),
+                                           _lib.ptr(dz), _lib.ptr(dP), _lib.ptr(dW), _lib.ptr(scalars),
+                                           _lib.ptr(workspace), c_size_t(workspace.numel()), _lib.stream_ptr())
+            _lib.check(rc, "adlm_step_fwd_bwd_pre")
+        elif dp_comm is not None:
             if global_counts is not None:
                 raise ValueError("dp_comm and global_counts are mutually exclusive")
             comm = dp_comm.next_comm(K, N, C)
@@ -250,7 +276,8 @@ def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
     _lib.check(rc, "adlm_step_fwd_bwd")
     if dP is not None:
         dP = dP.reshape(prototypes.shape)
-    return _StepResult(scalars=scalars, dz=dz, dP=dP, dW=dW, logits=logits, argmax=amax, workspace=workspace)
+    return _StepResult(scalars=scalars, dz=dz, dP=dP, dW=dW, logits=logits, argmax=amax, workspace=workspace,
+                       z=z_feat)
 
 
 def step_counts(target, proto_class, num_classes, ignore_void=True, workspace=None, K=1):

@@ -21,6 +21,7 @@
  *                          Trainer.gpus = 1, segmentation/configs/cityscapes_kld_imnet.gin:1; raising it makes
  *                          Lightning wrap the module in DDP, whose gradient all-reduce this entry point
  *                          performs inside the step's own kernels over peer-mapped memory)
+ *   adlm_head_fwd_pre, adlm_step_fwd_bwd_pre   the same with model.py:124-128,174 (Sigmoid add-on layer) fused in
  *   adlm_patch_class_mask  segmentation/push.py:201-230 (pixel -> patch class sets)
  *   adlm_push_scan         segmentation/push.py:249-280 (class-filtered per-prototype argmin,
  *                          strict '<' against the global minimum)
@@ -36,7 +37,7 @@
 extern "C" {
 #endif
 
-#define ADLM_ABI_VERSION 5
+#define ADLM_ABI_VERSION 6
 
 #if defined(__GNUC__)
 #define ADLM_API __attribute__((visibility("default")))
@@ -148,6 +149,31 @@ ADLM_API int adlm_step_fwd_bwd(const float* z, int B, int K, int HW,
                       float* dz, float* dP, float* dW,
                       double* scalars, void* workspace, size_t workspace_bytes,
                       void* stream);
+
+/*
+ * The same two entry points with the add-on activation fused in (model.py:124-128,174: add_on_layers =
+ * Sequential(Sigmoid())).  `pre` [B,K,HW] holds the PRE-sigmoid features; the forward
+ * applies the sigmoid while it stages a tile and writes z = sigmoid(pre) to z_out [B,K,HW] (the reference hands z to
+ * forward_with_features / push, and the backward kernels re-read it); `dpre` receives the gradient wrt `pre`
+ * (dz * z * (1 - z), applied in the dZ kernel's store).  Saves the two elementwise passes around the head.
+ * Tensor-core path only: ADLM_PREC_TF32, K <= 64, N <= 192, C <= 32, else ADLM_E_UNSUPPORTED (apply the sigmoid
+ * with stock code and call the plain entry points).
+ */
+ADLM_API int adlm_head_fwd_pre(const float* pre, int B, int K, int HW,
+                      const float* P, const float* W, int N, int C,
+                      float eps, int act_mode, int prec_mode,
+                      float* z_out, float* logits, float* dist, float* sim, int32_t* argmax,
+                      void* stream);
+ADLM_API int adlm_step_fwd_bwd_pre(const float* pre, int B, int K, int HW,
+                          const float* P, const float* W, int N, int C,
+                          float eps, int prec_mode,
+                          const int32_t* target, const int32_t* proto_class, int ignore_void,
+                          float w_ce, float w_kld, float w_l1, float grad_scale,
+                          const int32_t* global_counts,
+                          float* z_out, float* logits_out, int32_t* argmax_out,
+                          float* dpre, float* dP, float* dW,
+                          double* scalars, void* workspace, size_t workspace_bytes,
+                          void* stream);
 
 /*
  * Loss normalisers of a batch shard: counts_out[0] = number of CE patches (module.py:156-165),

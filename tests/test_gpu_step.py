@@ -294,3 +294,51 @@ def test_dp_exchange_dead_peer_times_out_with_nan():
     torch.cuda.synchronize()
     assert float(res.scalars[7]) > 0.0
     assert bool(torch.isnan(res.dP).all()) and bool(torch.isnan(res.dW).all())
+
+
+# ------------------------------------------------------------------ fused add-on Sigmoid
+def test_fused_sigmoid_prologue_matches_separate_sigmoid_and_oracle():
+    """pre-sigmoid features in: the forward applies model.py:124-128's Sigmoid while staging the tile, returns z,
+    and dz comes back as the gradient wrt the pre-sigmoid input (dz * z * (1 - z))."""
+    if not available("tf32"):
+        pytest.skip("tf32 kernels not built")
+    B, K, h, w, N, C = 3, 64, 33, 29, 190, 19
+    _, Pn, Wn = synth.head_inputs(B, K, h, w, N, C, w_noise=0.1, seed=411)
+    rng = np.random.default_rng(412)
+    pre_n = rng.normal(0.0, 1.5, size=(B, K, h, w)).astype(np.float32)
+    target_n = synth.block_labels(B, h, w, C, block=4, seed=413).astype(np.int64)
+    pre, P, W = cuda(pre_n, Pn, Wn)
+    target = torch.from_numpy(target_n.astype(np.int32)).cuda()
+    pc = torch.arange(N, dtype=torch.int32, device="cuda") // (N // C)
+    z = torch.sigmoid(pre)
+    ref = head.fused_step(z, P, W, target, pc, precision="tf32", want_logits=True)
+    fus = head.fused_step(pre, P, W, target, pc, precision="tf32", want_logits=True, pre_sigmoid=True)
+    assert torch.allclose(fus.z, z, rtol=2e-6, atol=2e-7)                       # ex2.approx + rcp.approx sigmoid
+    assert torch.allclose(fus.scalars[:4], ref.scalars[:4], rtol=1e-4)
+    assert int(fus.scalars[5]) == int(ref.scalars[5]) and int(fus.scalars[6]) == int(ref.scalars[6])
+    assert parity.rel_err(fus.logits.cpu().numpy(), ref.logits.cpu().numpy()) <= 1e-3
+    assert parity.rel_err(fus.dP.cpu().numpy(), ref.dP.cpu().numpy()) <= 1e-3
+    assert parity.rel_err(fus.dW.cpu().numpy(), ref.dW.cpu().numpy()) <= 1e-3
+    chain = (ref.dz * z * (1 - z)).cpu().numpy()
+    assert parity.rel_err(fus.dz.cpu().numpy(), chain) <= 1e-3                  # z(1-z) from the tf32-rounded z
+    # float64 oracle on z = sigmoid(pre), chain rule applied in float64
+    z64 = 1.0 / (1.0 + np.exp(-pre_n.astype(np.float64)))
+    o = orc.step_loss(z64.astype(np.float32), Pn, Wn, target_n)
+    s = PREC_SCALE["tf32"]
+    assert float(fus.scalars[0]) == pytest.approx(o["loss"], rel=2e-5 * s)
+    assert parity.rel_err(fus.dz.cpu().numpy(), o["dz"] * z64 * (1 - z64)) <= 2e-4 * s
+    assert parity.rel_err(fus.dP.cpu().numpy().reshape(N, K), o["dP"]) <= 2e-4 * s
+    # forward only
+    f = head.head_forward(pre, P, W, precision="tf32", want_dist=True, want_argmax=True, pre_sigmoid=True)
+    g = head.head_forward(z, P, W, precision="tf32", want_dist=True, want_argmax=True)
+    assert torch.allclose(f["z"], z, rtol=2e-6, atol=2e-7)
+    assert parity.rel_err(f["logits"].cpu().numpy(), g["logits"].cpu().numpy()) <= 1e-3
+    assert float((f["argmax"] != g["argmax"]).float().mean()) <= 1e-3
+    # loss-only call still returns the features; other precisions refuse
+    v = head.fused_step(pre, P, W, target, pc, precision="tf32", need_grads=False, pre_sigmoid=True)
+    assert v.dz is None and torch.allclose(v.z, z, rtol=2e-6, atol=2e-7)
+    for prec in ("fp32", "tf32x3"):
+        with pytest.raises(NotImplementedError):
+            head.fused_step(pre, P, W, target, pc, precision=prec, pre_sigmoid=True)
+        with pytest.raises(NotImplementedError):
+            head.head_forward(pre, P, W, precision=prec, pre_sigmoid=True)
