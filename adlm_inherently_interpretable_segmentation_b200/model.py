@@ -147,6 +147,28 @@ class PrototypeHeadMixin:
         return _head.FusedStepFunction.apply(conv_features, self.prototype_vectors, self.last_layer.weight,
                                              target, self.proto_class(), cfg)
 
+    def add_on_is_sigmoid(self):
+        """True when add_on_layers is exactly Sequential(Sigmoid()) — the 'deeplab_simple' add-on of every
+        segmentation config (model.py:124-128)"""
+        mods = list(self.add_on_layers.children()) if isinstance(self.add_on_layers, nn.Sequential) else None
+        return mods is not None and len(mods) == 1 and isinstance(mods[0], nn.Sigmoid)
+
+    def fused_step_from_backbone(self, backbone_features, target, ignore_void_class=True,
+                                 loss_weights=(1.0, 0.25, 1e-4), grad_scale=1.0):
+        """fused_step on the output of self.features(x), i.e. BEFORE the add-on layers (model.py:164-175).
+        With the Sigmoid-only add-on and head_precision 'tf32' the sigmoid and its backward run inside the head
+        kernels (adlm_step_fwd_bwd_pre); otherwise the add-on layers run as stock torch first."""
+        eps, act, prec = self._head_cfg()
+        K, N, C = self.prototype_shape[1], self.num_prototypes, self.num_classes
+        if (self.add_on_is_sigmoid() and prec == 'tf32' and act == 'log' and K <= 64 and N <= 192 and C <= 32
+                and not isinstance(backbone_features, list)):
+            cfg = dict(ignore_void=ignore_void_class, weights=tuple(loss_weights), grad_scale=grad_scale,
+                       eps=eps, precision=prec, pre_sigmoid=True)
+            return _head.FusedStepFunction.apply(backbone_features, self.prototype_vectors, self.last_layer.weight,
+                                                 target, self.proto_class(), cfg)
+        return self.fused_step(self.add_on_layers(backbone_features), target, ignore_void_class, loss_weights,
+                               grad_scale)
+
 
 def _first_add_on_in_channels(features):
     """channel count entering the add-on layers, by backbone family (model.py:81-95)"""

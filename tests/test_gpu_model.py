@@ -114,6 +114,36 @@ def test_fused_step_method_trains_the_head(golden):
     assert parity.rel_err(net.last_layer.weight.grad.cpu().numpy(), g["dW"]) <= 2e-4
 
 
+def test_fused_step_from_backbone_fuses_the_sigmoid_add_on():
+    """features(x) -> [Sigmoid add-on + head step] in the kernels == add_on_layers(features(x)) -> head step"""
+    N, K, C, B, h, w = 190, 64, 19, 2, 17, 21
+    net = make_net(N, K, C).cuda()
+    net.head_precision = 'tf32'
+    assert net.add_on_is_sigmoid()
+    target = torch.from_numpy(synth.block_labels(B, h, w, C, block=4, seed=77).astype(np.int32)).cuda()
+    feats = (torch.randn(B, K, h, w, device="cuda") * 1.5)
+    grads = []
+    losses = []
+    for fused in (True, False):
+        f = feats.clone().requires_grad_(True)
+        net.zero_grad()
+        if fused:
+            loss, scalars = net.fused_step_from_backbone(f, target)
+        else:
+            loss, scalars = net.fused_step(net.add_on_layers(f), target)
+        (loss / 5).backward()
+        losses.append(float(loss))
+        grads.append((f.grad.clone(), net.prototype_vectors.grad.clone(), net.last_layer.weight.grad.clone()))
+    assert losses[0] == pytest.approx(losses[1], rel=1e-4)
+    for a, b in zip(grads[0], grads[1]):
+        assert parity.rel_err(a.cpu().numpy(), b.cpu().numpy()) <= 1e-3
+    # any other add-on stack or precision runs the add-on layers as stock torch first
+    net.head_precision = 'tf32x3'
+    f = feats.clone().requires_grad_(True)
+    loss, _ = net.fused_step_from_backbone(f, target)
+    assert float(loss) == pytest.approx(losses[1], rel=1e-3)
+
+
 class _DiskDataset:
     """the slice of PatchClassificationDataset that push_prototypes touches (push.py:101-115)"""
     image_margin_size = 0
