@@ -18,7 +18,8 @@ MAX_PROTOS_PER_CLASS = 16
 MAX_PUSH_CLASSES = 32
 STEP_NSCALARS = 8
 PUSH_NONE = 0x7FFFFFFFFFFFFFFF
-ABI_VERSION = 6
+ABI_VERSION = 7
+EVAL_TILE_X, EVAL_TILE_Y = 64, 16
 DP_MAX_WORLD = 16
 
 # name -> (restype, argtypes); kept next to include/adlm_head.h (tests check they agree)
@@ -73,6 +74,10 @@ SIGNATURES["adlm_step_fwd_bwd_pre"] = (c_int, [c_void_p, c_int, c_int, c_int, c_
                                                c_float, c_float, c_float, c_float, c_void_p,
                                                c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                                c_void_p, c_void_p, c_size_t, c_void_p])
+
+SIGNATURES["adlm_eval_upsample"] = (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                            c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                            c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p])
 
 _lib = None
 

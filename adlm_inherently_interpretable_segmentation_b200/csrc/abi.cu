@@ -286,6 +286,21 @@ int adlm_step_counts(const int32_t* target, int B, int HW, const int32_t* proto_
                           (cudaStream_t)stream);
 }
 
+int adlm_eval_upsample(const float* logits, const float* dist, int B, int h, int w, int C, int N, int H, int Wimg,
+                       const int32_t* y0, const float* ly, const int32_t* x0, const float* lx, int patch_rows,
+                       int patch_cols, uint8_t* pred, int16_t* nearest, const uint8_t* labels,
+                       const int32_t* proto_class, unsigned long long* counters, void* stream) {
+  ADLM_CHECK_ARG(logits && y0 && ly && x0 && lx, "null pointer argument");
+  ADLM_CHECK_ARG(B > 0 && h > 0 && w > 0 && C > 0 && H > 0 && Wimg > 0, "non-positive size");
+  ADLM_CHECK_ARG(dist == nullptr || N > 0, "N must be positive when distances are given");
+  ADLM_CHECK_ARG(patch_rows > 0 && patch_cols > 0 && patch_rows <= h && patch_cols <= w, "bad source patch size");
+  ADLM_CHECK_SUPPORTED(C <= 256 && N <= 32767, "C > 256 or N > 32767");
+  ADLM_CHECK_SUPPORTED(B <= 65535, "B > 65535 per call");
+  if (dist == nullptr) N = 0;
+  return eval_upsample_impl(logits, dist, B, h, w, C, N, H, Wimg, y0, ly, x0, lx, patch_rows, patch_cols, pred,
+                            nearest, labels, proto_class, counters, (cudaStream_t)stream);
+}
+
 int adlm_patch_class_mask(const uint8_t* labels, int n_img, int H, int Wimg, const int32_t* row_lut,
                           const int32_t* col_lut, int h, int w, uint32_t* mask_out, void* stream) {
   ADLM_CHECK_ARG(labels && row_lut && col_lut && mask_out, "null pointer argument");

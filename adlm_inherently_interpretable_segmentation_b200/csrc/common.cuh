@@ -217,4 +217,9 @@ int simt_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mas
 int push_gather_impl(const float* z, int n_img, int K, int HW, long long patch_base,
                      const unsigned long long* packed_min, int N, float* proto_out, cudaStream_t st);
 
+int eval_upsample_impl(const float* logits, const float* dist, int B, int h, int w, int C, int N, int H, int Wimg,
+                       const int32_t* y0l, const float* lyl, const int32_t* x0l, const float* lxl, int patch_rows,
+                       int patch_cols, uint8_t* pred, int16_t* nearest, const uint8_t* labels,
+                       const int32_t* proto_class, unsigned long long* counters, cudaStream_t st);
+
 }  // namespace adlm

@@ -22,6 +22,8 @@
  *                          Lightning wrap the module in DDP, whose gradient all-reduce this entry point
  *                          performs inside the step's own kernels over peer-mapped memory)
  *   adlm_head_fwd_pre, adlm_step_fwd_bwd_pre   the same with model.py:124-128,174 (Sigmoid add-on layer) fused in
+ *   adlm_eval_upsample     segmentation/eval_valid.py:171-199, eval_test.py:105-106, push.py:243-247 (bilinear
+ *                          upsampling of logits / distances to image size + argmax / argmin + IoU counters)
  *   adlm_patch_class_mask  segmentation/push.py:201-230 (pixel -> patch class sets)
  *   adlm_push_scan         segmentation/push.py:249-280 (class-filtered per-prototype argmin,
  *                          strict '<' against the global minimum)
@@ -37,7 +39,7 @@
 extern "C" {
 #endif
 
-#define ADLM_ABI_VERSION 6
+#define ADLM_ABI_VERSION 7
 
 #if defined(__GNUC__)
 #define ADLM_API __attribute__((visibility("default")))
@@ -223,6 +225,31 @@ ADLM_API int adlm_step_fwd_bwd_dp(const float* z, int B, int K, int HW,
                          float* dz, float* dP, float* dW,
                          double* scalars, void* workspace, size_t workspace_bytes,
                          const adlm_dp_comm* comm, void* stream);
+
+/*
+ * Evaluation epilogue: F.interpolate(mode='bilinear', align_corners=False) of the
+ * logits and of the prototype distances to the image size, fused with torch.argmax / torch.argmin over the planes
+ * and with the reference's counters; the upsampled stacks are never materialised.
+ *   logits [B,h,w,C] (adlm_head_fwd layout), dist [B,N,h,w] | NULL (then nearest / prototype counts are skipped);
+ *   y0 [H] int32, ly [H] fp32, x0 [Wimg] int32, lx [Wimg] fp32: source index and lambda of every output row /
+ *     column, computed by the caller in FLOAT32 as torch does: src = max(scale * (dst + 0.5) - 0.5, 0) with
+ *     scale = (float)in / out, index = (int)src, lambda = src - index  (device arrays);
+ *   patch_rows / patch_cols: the largest number of source rows / columns any ADLM_EVAL_TILE_Y x ADLM_EVAL_TILE_X
+ *     output tile touches: max over tiles of min(y0[last row of tile] + 1, h - 1) - y0[first row] + 1 (same for x);
+ *   pred [B,H,Wimg] uint8 | NULL: argmax class; nearest [B,H,Wimg] int16 | NULL: argmin prototype;
+ *   labels [B,H,Wimg] uint8 | NULL: ground truth, 0 = void, class + 1 otherwise;
+ *   proto_class [N] int32 | NULL; counters | NULL: 2 + 2C + N unsigned 64-bit, ACCUMULATED (caller zeroes):
+ *     [0] correct pixels, [1] non-void pixels, [2..2+C) per-class intersection, [2+C..2+2C) per-class union
+ *     (eval_valid.py:178-189), [2+2C..) pixels whose nearest prototype n belongs to the predicted class (:192-197).
+ */
+#define ADLM_EVAL_TILE_X 64
+#define ADLM_EVAL_TILE_Y 16
+ADLM_API int adlm_eval_upsample(const float* logits, const float* dist, int B, int h, int w, int C, int N,
+                       int H, int Wimg,
+                       const int32_t* y0, const float* ly, const int32_t* x0, const float* lx,
+                       int patch_rows, int patch_cols,
+                       uint8_t* pred, int16_t* nearest, const uint8_t* labels,
+                       const int32_t* proto_class, unsigned long long* counters, void* stream);
 
 /*
  * Push, step 1: per-patch class bitmask from full-resolution labels.

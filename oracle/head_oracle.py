@@ -254,3 +254,57 @@ def push_finalize(gpatch):
     _, unique_index = np.unique(gpatch, axis=0, return_index=True)
     dup = [i for i in range(gpatch.shape[0]) if i not in unique_index]
     return np.sort(unique_index), np.array(dup, dtype=np.int64)
+
+
+# ---------------------------------------------------------------- evaluation epilogue
+def bilinear_tables(in_size, out_size):
+    """torch upsample_bilinear2d, align_corners=False (area_pixel_compute_source_index), float32:
+    src = max(scale * (dst + 0.5) - 0.5, 0), scale = in / out  ->  (i0, i1, lambda1)"""
+    scale = np.float32(in_size) / np.float32(out_size)
+    dst = np.arange(out_size, dtype=np.float32)
+    src = np.maximum(scale * (dst + np.float32(0.5)) - np.float32(0.5), np.float32(0)).astype(np.float32)
+    i0 = np.minimum(src.astype(np.int64), in_size - 1)
+    i1 = np.minimum(i0 + 1, in_size - 1)
+    return i0, i1, (src - i0.astype(np.float32)).astype(np.float32)
+
+
+def bilinear_upsample(planes, size):
+    """planes (P,h,w) float32 -> (P,H,W): F.interpolate(mode='bilinear', align_corners=False)
+    (eval_valid.py:171-172): h0 * (w0 * v00 + w1 * v01) + h1 * (w0 * v10 + w1 * v11)"""
+    planes = np.asarray(planes, dtype=np.float32)
+    _, h, w = planes.shape
+    y0, y1, ly = bilinear_tables(h, size[0])
+    x0, x1, lx = bilinear_tables(w, size[1])
+    h1 = ly[None, :, None]
+    h0 = (np.float32(1) - ly)[None, :, None]
+    w1 = lx[None, None, :]
+    w0 = (np.float32(1) - lx)[None, None, :]
+    top = w0 * planes[:, y0][:, :, x0] + w1 * planes[:, y0][:, :, x1]
+    bot = w0 * planes[:, y1][:, :, x0] + w1 * planes[:, y1][:, :, x1]
+    return (h0 * top + h1 * bot).astype(np.float32)
+
+
+def eval_image(logits_hwc, dist_nhw, ann, proto_class, C):
+    """one image of eval_valid.py:165-199: upsample, argmax / argmin, counters.
+    logits (h,w,C), dist (N,h,w) | None, ann (H,W) uint8 (0 = void) -> dict"""
+    size = ann.shape
+    up = bilinear_upsample(np.transpose(logits_hwc, (2, 0, 1)), size)
+    pred = np.argmax(up, axis=0)                                       # eval_valid.py:176
+    out = dict(pred=pred, up_logits=up)
+    out["correct_pixels"] = int(np.sum(((pred + 1) == ann) & (ann != 0)))   # :178
+    out["total_pixels"] = int(np.sum(ann != 0))                            # :180
+    I, U = np.zeros(C, np.int64), np.zeros(C, np.int64)
+    for c in range(C):                                                  # :182-189
+        pr, gt = pred == c, ann == c + 1
+        I[c] = np.sum(pr & gt)
+        U[c] = np.sum((pr | gt) & (ann != 0))
+    out["CLS_I"], out["CLS_U"] = I, U
+    if dist_nhw is not None:
+        upd = bilinear_upsample(dist_nhw, size)
+        nearest = np.argmin(upd, axis=0)                                # :174
+        out["nearest"], out["up_dist"] = nearest, upd
+        counts = np.zeros(len(proto_class), np.int64)
+        ok = np.asarray(proto_class)[nearest] == pred                   # :192-197
+        np.add.at(counts, nearest[ok], 1)
+        out["proto_counts"] = counts
+    return out

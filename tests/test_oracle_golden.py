@@ -138,3 +138,21 @@ def test_torch_port_push_matches_reference(golden):
         tp.push_image(torch.from_numpy(g["z"][i:i + 1]), P4, g["labels"][i], C, gmin, gpatch, i)
     assert np.allclose(gmin, g["gmin"], atol=1e-6)
     assert (np.all(gpatch == g["gpatch"], axis=1)).mean() >= 0.95   # set-order ties (push.py:230) may differ
+
+
+def test_eval_epilogue_oracle_matches_torch_fixture(golden):
+    """bilinear upsampling + argmax / argmin + counters of eval_valid.py:165-199 (fixture: oracle/make_golden_eval.py,
+    the reference's own torch calls)"""
+    g = golden("eval_small")
+    C = g["logits"].shape[-1]
+    tot = dict(correct_pixels=0, total_pixels=0, CLS_I=0, CLS_U=0, proto_counts=0)
+    for i in range(g["logits"].shape[0]):
+        o = orc.eval_image(g["logits"][i], g["dist"][i], g["ann"][i], g["proto_class"], C)
+        assert np.abs(o["up_logits"] - g["up_logits"][i]).max() <= 1e-5
+        assert np.abs(o["up_dist"] - g["up_dist"][i]).max() <= 2e-5
+        assert np.array_equal(o["pred"], g["pred"][i]) and np.array_equal(o["nearest"], g["nearest"][i])
+        for k in tot:
+            tot[k] = tot[k] + o[k]
+    assert tot["correct_pixels"] == int(g["correct_pixels"]) and tot["total_pixels"] == int(g["total_pixels"])
+    for k in ("CLS_I", "CLS_U", "proto_counts"):
+        assert np.array_equal(tot[k], g[k]), k
