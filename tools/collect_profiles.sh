@@ -9,4 +9,6 @@ timeout 200 python tools/kernel_sweep.py --batches 16,64,256 > $O/r1_kernel_swee
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/r1_launches_tf32_step.csv python bench.py --steps 10 --warmup 3 --no-cpu --no-push > $O/ncu_l.log 2>&1
 timeout 400 ncu --set full --clock-control none --import-source on -k regex:'k_tc_|k_kld|k_step_prepare|k_reduce' -c 12 -o $O/r1_step_full -f python tools/kernel_sweep.py --once --batches 16 > $O/ncu_f.log 2>&1
 timeout 400 ncu --set full --clock-control none --import-source on -k regex:'k_tc_push|k_patch_class_mask' -c 4 -o $O/r1_push_full -f python tools/push_once.py 64 tf32x3 > $O/ncu_p.log 2>&1
-ls -la $O | tail -20
+timeout 200 python tools/sigmoid_fusion_bench.py > $O/r1_sigmoid_fusion.log 2>&1
+(echo '# python tools/eval_bench.py (B200, 4 images, CUDA events)'; timeout 300 python tools/eval_bench.py) > $O/r1_eval_upsample.log 2>&1
+ls -la $O | tail -24
