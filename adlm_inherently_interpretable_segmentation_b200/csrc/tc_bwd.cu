@@ -127,11 +127,26 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
   };
   prefetch(tile);
 
-  stage_rows_kmajor<KP, false>(Pk, Pk, p.P, N, K, Npad, CENTRE, tid, 256);
-  // Wt: rows = prototypes, K index = class: [C8/4][Npad][4]
-  stage_wt_kmajor(Wt, p.W, C, N, C8, Npad, 1.f, p.dlogits != nullptr, tid, 256);
-  // Pt: the same rounded prototypes transposed (rows k, K index n): [Npad/4][KP][4]
-  stage_pt_kmajor<KP>(Pt, p.P, N, K, Npad, CENTRE, tid, 256);
+  // Pk: rows = prototypes [KP/4][Npad][4]; Wt: rows = prototypes, K index = class [C8/4][Npad][4];
+  // Pt: the same rounded prototypes transposed (rows k, K index n) [Npad/4][KP][4]
+  {
+    // raw copies land in the two warpgroups' pixel-operand buffers (unused until the first tile is converted)
+    float* praw = reinterpret_cast<float*>(smem + L::zk(0, Npad, C8));
+    float* wraw = praw + (size_t)N * (KP + 4);
+    const size_t scratch = 2 * ((size_t)KP * TILE * 4 + (size_t)C8 * TILE * 4);
+    if (raw_stage_ok(p.P, p.W, K, KP, C * N) && ((size_t)N * (KP + 4) + (size_t)C * N) * 4 <= scratch) {
+      raw_copy_async(praw, wraw, p.P, p.W, N, K, C * N, tid, 256);
+      raw_copy_wait();
+      __syncthreads();
+      pk_from_raw<KP>(Pk, praw, N, Npad, CENTRE, tid, 256);
+      wt_from_raw(Wt, wraw, C, N, C8, Npad, 1.f, p.dlogits != nullptr, tid, 256);
+      pt_from_raw<KP>(Pt, praw, N, Npad, CENTRE, tid, 256);
+    } else {
+      stage_rows_kmajor<KP, false>(Pk, Pk, p.P, N, K, Npad, CENTRE, tid, 256);
+      stage_wt_kmajor(Wt, p.W, C, N, C8, Npad, 1.f, p.dlogits != nullptr, tid, 256);
+      stage_pt_kmajor<KP>(Pt, p.P, N, K, Npad, CENTRE, tid, 256);
+    }
+  }
   __syncthreads();
   for (int n = tid; n < Npad; n += 256) {
     float a = 0.f;

@@ -306,6 +306,88 @@ __device__ __forceinline__ void stage_pt_kmajor(float* __restrict__ dst, const f
   }
 }
 
+// ---- one-time operands through a raw shared-memory copy --------------------------------------------------
+// cp.async puts every byte of P and W in flight at once (no registers, one global latency); the operand layouts
+// are then produced by shared-to-shared transforms.  P rows get a pitch of K + 4 floats so that both "lanes over
+// rows" and "lanes over columns" reads are conflict-free.  Requirements (else use the stage_* functions above):
+// K == KP, P 16-byte aligned, W 8-byte aligned with an even element count.
+__device__ __forceinline__ bool raw_stage_ok(const float* P, const float* W, int K, int KP, int CN) {
+  return K == KP && (reinterpret_cast<uintptr_t>(P) & 15u) == 0 && (reinterpret_cast<uintptr_t>(W) & 7u) == 0 && (CN & 1) == 0;
+}
+__device__ __forceinline__ void raw_copy_async(float* __restrict__ praw, float* __restrict__ wraw,
+                                               const float* __restrict__ P, const float* __restrict__ W, int N, int K,
+                                               int CN, int tid, int nthreads) {
+  const int cpr = K >> 2, pitch = K + 4;
+  for (int i = tid; i < N * cpr; i += nthreads) {
+    const int r = i / cpr, c = i - r * cpr;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(praw + r * pitch + c * 4)), "l"(P + (size_t)r * K + c * 4) : "memory");
+  }
+  for (int i = tid; i < (CN >> 1); i += nthreads)
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(wraw + i * 2)), "l"(W + i * 2) : "memory");
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void raw_copy_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// Pk [KP/4][rows_pad][4] (rows = prototypes) from the raw copy
+template <int KP>
+__device__ __forceinline__ void pk_from_raw(float* __restrict__ dst, const float* __restrict__ praw, int N, int rows_pad,
+                                            float centre, int tid, int nthreads) {
+  const int total = (KP >> 2) * rows_pad;
+  for (int f = tid; f < total; f += nthreads) {
+    const int k4 = f / rows_pad, n = f - k4 * rows_pad;
+    float4 v = make_float4(centre, centre, centre, centre);
+    if (n < N) v = *reinterpret_cast<const float4*>(praw + n * (KP + 4) + k4 * 4);
+    *reinterpret_cast<float4*>(dst + (size_t)f * 4) =
+        make_float4(rna_tf32_mask(v.x - centre), rna_tf32_mask(v.y - centre), rna_tf32_mask(v.z - centre), rna_tf32_mask(v.w - centre));
+  }
+}
+// Pt [Npad/4][KP][4] (rows = depth k, K index = prototype)
+template <int KP>
+__device__ __forceinline__ void pt_from_raw(float* __restrict__ dst, const float* __restrict__ praw, int N, int Npad,
+                                            float centre, int tid, int nthreads) {
+  const int total = (Npad >> 2) * KP;
+  for (int f = tid; f < total; f += nthreads) {
+    const int n4 = f / KP, k = f - n4 * KP;
+    float v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n4 * 4 + j;
+      v[j] = n < N ? rna_tf32_mask(praw[n * (KP + 4) + k] - centre) : 0.f;
+    }
+    *reinterpret_cast<float4*>(dst + (size_t)f * 4) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+}
+// Wt [C8/4][rows_pad][4] (rows = prototypes, K index = class)
+__device__ __forceinline__ void wt_from_raw(float* __restrict__ dst, const float* __restrict__ wraw, int C, int N, int C8,
+                                            int rows_pad, float scale, bool valid, int tid, int nthreads) {
+  const int total = (C8 >> 2) * rows_pad;
+  for (int f = tid; f < total; f += nthreads) {
+    const int c4 = f / rows_pad, n = f - c4 * rows_pad;
+    float v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = c4 * 4 + j;
+      v[j] = (valid && c < C && n < N) ? rna_tf32_mask(scale * wraw[c * N + n]) : 0.f;
+    }
+    *reinterpret_cast<float4*>(dst + (size_t)f * 4) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+}
+// Wk [Npad/4][Cpad][4] (rows = classes, K index = prototype)
+__device__ __forceinline__ void wk_from_raw(float* __restrict__ dst, const float* __restrict__ wraw, int C, int N, int Cpad,
+                                            int Npad, float scale, int tid, int nthreads) {
+  const int total = (Npad >> 2) * Cpad;
+  for (int f = tid; f < total; f += nthreads) {
+    const int n4 = f / Cpad, c = f - n4 * Cpad;
+    float v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n4 * 4 + j;
+      v[j] = (c < C && n < N) ? rna_tf32_mask(scale * wraw[c * N + n]) : 0.f;
+    }
+    *reinterpret_cast<float4*>(dst + (size_t)f * 4) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+}
+
 // zero a shared-memory region of n4 float4s
 __device__ __forceinline__ void smem_zero4(float* dst, int n4, int tid, int nthreads) {
   for (int i = tid; i < n4; i += nthreads) reinterpret_cast<float4*>(dst)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
