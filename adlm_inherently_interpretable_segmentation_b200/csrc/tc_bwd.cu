@@ -464,9 +464,14 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
       uint32_t* clsm_s = clsm + slot * 128;
       float* ogs_s = ogs + slot * 128 * JMAX;
       if (warp == 8) DP_PHASE(0, 1 + it * 8);
-      // ---- step K: wait until the last distance MMA of the previous tile has read ZkB / dLkB
-      //      (completion number it * NU/2 of acc[1]; the next one needs this step's full_k, so no aliasing)
-      if (it > 0) mbar_wait(bar_acc0 + 8, (uint32_t)(it * (NU / 2) - 1) & 1u);
+      // ---- step K: wait until the last distance MMA of the previous tile has read ZkB / dLkB, i.e. for
+      //      completion number it * NU/2 of acc[1].  A parity wait only tells consecutive phases apart, so every
+      //      completion of the previous tile is observed in order (the next one after them needs this step's
+      //      full_k, so the barrier cannot run ahead of this thread).
+      if (it > 0) {
+#pragma unroll
+        for (int c = 0; c < NU / 2; ++c) mbar_wait(bar_acc0 + 8, (uint32_t)((it - 1) * (NU / 2) + c) & 1u);
+      }
       if (warp == 8) DP_PHASE(0, 2 + it * 8);
       clsm_s[cw] = 0u;
       if (kld && valid) {

@@ -342,3 +342,55 @@ def test_fused_sigmoid_prologue_matches_separate_sigmoid_and_oracle():
             head.fused_step(pre, P, W, target, pc, precision=prec, pre_sigmoid=True)
         with pytest.raises(NotImplementedError):
             head.head_forward(pre, P, W, precision=prec, pre_sigmoid=True)
+
+
+@pytest.mark.parametrize("prec", ["tf32", "fp32"])
+def test_step_many_tiles_per_cta_equals_sum_of_single_image_steps(prec):
+    """The benchmark shape gives every persistent CTA several tiles (16 x 65 x 65 pixels = 529 tiles on 148 SMs); the
+    tile pipelines inside the kernels must not depend on that.  One image (34 tiles) is at most one tile per CTA, so
+    the whole-batch step has to equal the sum of sixteen single-image steps run with the batch's normalisers."""
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    B, K, h, w, N, C = 16, 64, 65, 65, 190, 19
+    g = torch.Generator(device="cuda").manual_seed(5)
+    z = torch.sigmoid(torch.randn(B, K, h, w, device="cuda", generator=g))
+    _, Pn, Wn = synth.head_inputs(1, K, 2, 2, N, C, w_noise=0.1, seed=77)
+    P, W = cuda(Pn, Wn)
+    target = torch.from_numpy(synth.block_labels(B, h, w, C, block=8, seed=78).astype(np.int32)).cuda()
+    pc = torch.arange(N, dtype=torch.int32, device="cuda") // (N // C)
+    wts = (1.0, 0.25, 1e-4)
+    for rep in range(3):                                  # pipeline races are timing dependent: a few repetitions
+        full = head.fused_step(z, P, W, target, pc, weights=wts, precision=prec)
+        counts = torch.stack([full.scalars[5], full.scalars[6]]).to(torch.int32)
+        dP = torch.zeros_like(full.dP)
+        dW = torch.zeros_like(full.dW)
+        dz = []
+        for i in range(B):
+            r = head.fused_step(z[i:i + 1], P, W, target[i:i + 1], pc, weights=(wts[0], wts[1], wts[2] / B),
+                                global_counts=counts, precision=prec)
+            dP += r.dP
+            dW += r.dW
+            dz.append(r.dz)
+        tol = 2e-4 if prec == "tf32" else 2e-5            # same arithmetic, different summation order only
+        assert parity.rel_err(full.dP.cpu().numpy(), dP.cpu().numpy()) <= tol, rep
+        assert parity.rel_err(full.dW.cpu().numpy(), dW.cpu().numpy()) <= tol, rep
+        assert parity.rel_err(full.dz.cpu().numpy(), torch.cat(dz).cpu().numpy()) <= tol, rep
+
+
+def test_backward_many_tiles_per_cta_matches_fp32_path():
+    """head_backward alone (no loss kernels) at 256 images: 57 tiles per CTA through the unit pipeline"""
+    if not available("tf32"):
+        pytest.skip("tf32 kernels not built")
+    B, K, h, w, N, C = 64, 64, 65, 65, 190, 19
+    g = torch.Generator(device="cuda").manual_seed(9)
+    z = torch.sigmoid(torch.randn(B, K, h, w, device="cuda", generator=g))
+    _, Pn, Wn = synth.head_inputs(1, K, 2, 2, N, C, w_noise=0.1, seed=79)
+    P, W = cuda(Pn, Wn)
+    dl = torch.randn(B, h * w, C, device="cuda", generator=g) / (B * h * w)
+    a = head.head_backward(z, P, W, dlogits=dl, precision="tf32")
+    halves = [head.head_backward(z[i:i + 1], P, W, dlogits=dl[i:i + 1], precision="tf32") for i in range(B)]
+    dP = sum(x[1] for x in halves)
+    dW = sum(x[2] for x in halves)
+    assert parity.rel_err(a[1].cpu().numpy(), dP.cpu().numpy()) <= 2e-4
+    assert parity.rel_err(a[2].cpu().numpy(), dW.cpu().numpy()) <= 2e-4
+    assert parity.rel_err(a[0].cpu().numpy(), torch.cat([x[0] for x in halves]).cpu().numpy()) <= 2e-4
