@@ -185,3 +185,24 @@ def test_properties_at_benchmark_size(prec):
     # batch shards (the multi-GPU split) give bit-identical rows
     half = head.head_forward(z[8:], P, W, precision=prec, want_dist=False, want_argmax=True)
     assert torch.equal(half["logits"], out["logits"][8:]) and torch.equal(half["argmax"], out["argmax"][8:])
+
+
+@pytest.mark.parametrize("prec", ["tf32", "tf32x3", "fp32"])
+def test_forward_many_tiles_per_cta_equals_image_by_image(prec):
+    """64 images of 65 x 65 are 2113 tiles (14 per persistent CTA): the tile pipeline (operand stages, TMEM double
+    buffer, metadata slots) wraps many times; one image is at most one tile per CTA.  A pixel's result does not
+    depend on the tile it lands in, so the batched call must equal the image-by-image calls bit for bit."""
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    B, K, h, w, N, C = 64, 64, 65, 65, 190, 19
+    g = torch.Generator(device="cuda").manual_seed(23)
+    z = torch.sigmoid(torch.randn(B, K, h, w, device="cuda", generator=g))
+    _, Pn, Wn = synth.head_inputs(1, K, 2, 2, N, C, w_noise=0.1, seed=24)
+    P, W = cuda(Pn, Wn)
+    for rep in range(2):
+        full = head.head_forward(z, P, W, precision=prec, want_dist=True, want_argmax=True)
+        for i in (0, 1, 31, 63):
+            one = head.head_forward(z[i:i + 1], P, W, precision=prec, want_dist=True, want_argmax=True)
+            assert torch.equal(full["logits"][i:i + 1], one["logits"]), (rep, i)
+            assert torch.equal(full["dist"][i:i + 1], one["dist"]), (rep, i)
+            assert torch.equal(full["argmax"][i:i + 1], one["argmax"]), (rep, i)

@@ -149,3 +149,24 @@ def test_push_single_pass_tf32_only_differs_in_near_ties():
     for j in np.nonzero(found & (id1 != id3))[0]:
         assert flat[j, id1[j]] - flat[j, id3[j]] <= 0.05, f"prototype {j}: not a near-tie"
     assert (id1 == id3)[found].mean() >= 0.8
+
+
+@pytest.mark.parametrize("prec", PRECS)
+def test_push_many_tiles_per_cta_equals_image_by_image(prec):
+    """8 feature maps of 129 x 257 in ONE scan launch are 2073 tiles — 14 per persistent CTA, enough to wrap the
+    operand ring, the TMEM double buffer and the metadata slots several times; one image per launch is at most two
+    tiles per CTA (the regime checked against the oracle above).  Per-patch arithmetic does not depend on the tile a
+    patch lands in, so both ways must agree bit for bit."""
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    n, K, h, w, N, C, H, W = 8, 64, 129, 257, 190, 19, 1024, 2048
+    g = torch.Generator(device="cuda").manual_seed(17)
+    z = torch.sigmoid(torch.randn(n, K, h, w, device="cuda", generator=g))
+    labels = torch.from_numpy(synth.block_labels(2, H, W, C, block=32, seed=18)).cuda().repeat(n // 2, 1, 1).contiguous()
+    P = torch.rand(N, K, device="cuda", generator=g)
+    pc = proto_class(N, C)
+    for rep in range(2):
+        a, pa = push.push_search_tensors(z, labels, P, pc, precision=prec, chunk=n)
+        b, pb = push.push_search_tensors(z, labels, P, pc, precision=prec, chunk=1)
+        assert torch.equal(a.packed, b.packed), rep
+        assert torch.equal(pa, pb), rep
