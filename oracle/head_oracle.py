@@ -308,3 +308,68 @@ def eval_image(logits_hwc, dist_nhw, ann, proto_class, C):
         np.add.at(counts, nearest[ok], 1)
         out["proto_counts"] = counts
     return out
+
+
+# ---------------------------------------------------------------- k nearest patches / pruning
+def pil_nearest_lut(in_size, out_size):
+    """source index of every output pixel of PIL's Image.resize(..., NEAREST) (dataset.py:23-31 resize_label):
+    Pillow's ImagingScaleAffine accumulates the coordinate in double, xo = a/2; xo += a, and truncates"""
+    a = in_size / out_size
+    xo = a * 0.5
+    lut = np.empty(out_size, np.int64)
+    for x in range(out_size):
+        lut[x] = min(int(xo), in_size - 1)
+        xo += a
+    return lut
+
+
+def find_k_nearest(z_imgs, P, labels, proto_class, k, dist=None):
+    """find_nearest.py:92-226,331 (full_save label rule): z_imgs (n,K,h,w), labels (n,H,W) with 0 = void.
+    -> labels_all_prototype (N,k) class ids (-1 = void) of the k nearest patches (ascending distance),
+       distances (N,k), image ids (N,k), patch indices (N,k) (row-major in the h x w map)"""
+    n, K, h, w = z_imgs.shape
+    N = P.shape[0]
+    H, W = labels.shape[1:]
+    rl, cl = pil_nearest_lut(H, h), pil_nearest_lut(W, w)
+    ph, pw = H / h, W / w                                       # find_nearest.py:122-123
+    heaps = [[] for _ in range(N)]                              # entries (distance, image, patch, label) kept sorted
+    for i in range(n):
+        d = l2_distances(z_imgs[i:i + 1], P)[0] if dist is None else dist[i]     # (N,h,w)
+        y = labels[i].astype(np.int64) - 1                      # :118-119
+        void = (y[rl][:, cl] == -1)                             # :128-132 resize_label + void test
+        d = d + 10e6 * void[None]
+        for j in range(N):
+            flat = int(np.argmin(d[j]))                         # :146
+            dj = float(d[j].reshape(-1)[flat])
+            pi, pj = divmod(flat, w)
+            r0, r1, c0, c1 = int(pi * ph), int((pi + 1) * ph), int(pj * pw), int((pj + 1) * pw)   # :163-168
+            lab = y[r0:r1, c0:c1]
+            if lab.size == 0:                                   # :178-179
+                continue
+            tc = int(proto_class[j])
+            if np.any(lab == tc):                               # :199-205
+                label = tc
+            else:
+                vals, cnts = np.unique(lab, return_counts=True)
+                label = int(vals[np.argmax(cnts)])
+            hp = heaps[j]
+            if len(hp) < k:                                     # :217-223 (heap of the k smallest distances;
+                hp.append((dj, i, flat, label))                 #  a tie never displaces an earlier image)
+            else:
+                worst = max(range(k), key=lambda t: (hp[t][0], -t))
+                if dj < hp[worst][0]:
+                    hp[worst] = (dj, i, flat, label)
+    out_l = np.full((N, k), -2, np.int64)
+    out_d = np.full((N, k), np.inf)
+    out_i = np.full((N, k), -1, np.int64)
+    out_p = np.full((N, k), -1, np.int64)
+    for j in range(N):
+        for t, (dj, i, flat, label) in enumerate(sorted(heaps[j], key=lambda e: (e[0], e[1]))):
+            out_l[j, t], out_d[j, t], out_i[j, t], out_p[j, t] = label, dj, i, flat
+    return out_l, out_d, out_i, out_p
+
+
+def prototypes_to_prune(nearest_labels, proto_class, prune_threshold):
+    """prune.py:31-42: prototypes whose k nearest patches hold fewer than prune_threshold of their own class"""
+    return [j for j in range(len(proto_class))
+            if int(np.sum(np.asarray(nearest_labels[j]) == int(proto_class[j]))) < prune_threshold]

@@ -170,3 +170,43 @@ def test_push_many_tiles_per_cta_equals_image_by_image(prec):
         b, pb = push.push_search_tensors(z, labels, P, pc, precision=prec, chunk=1)
         assert torch.equal(a.packed, b.packed), rep
         assert torch.equal(pa, pb), rep
+
+
+# ------------------------------------------------------------------ k nearest patches / pruning
+@pytest.mark.parametrize("prec", PRECS)
+def test_k_nearest_matches_reference_fixture(golden, prec):
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    from adlm_inherently_interpretable_segmentation_b200 import nearest
+    g = golden("nearest_small")
+    n_img, K, h, w, N, C, H, W, k, seed = [int(v) for v in g["meta"]]
+    z, P = cuda(g["z"], g["P"])
+    pc = proto_class(N, C)
+    res = nearest.find_k_nearest_tensors(z, torch.from_numpy(g["labels"]).cuda(), P, pc, k=k, precision=prec)
+    ol, od, oi, op = orc.find_k_nearest(g["z"], g["P"], g["labels"], pc.cpu().numpy(), k)
+    assert np.allclose(res["distances"], od, atol=6 * K * 2.0 ** -21)
+    same = (res["images"] == oi) & (res["patch_i"] * w + res["patch_j"] == op)
+    assert same.mean() >= 0.97                                # order flips only between near-equal distances
+    assert np.array_equal(res["labels"][same], g["nearest_labels"][same])
+    if same.all():
+        assert nearest.prototypes_to_prune(res["labels"], pc, 2) == orc.prototypes_to_prune(g["nearest_labels"], pc.cpu().numpy(), 2)
+
+
+def test_k_nearest_void_and_short_datasets():
+    from adlm_inherently_interpretable_segmentation_b200 import nearest
+    n, K, h, w, N, C, H, W = 3, 64, 17, 19, 190, 19, 136, 152
+    zn, Pn, _ = synth.head_inputs(n, K, h, w, N, C, seed=171)
+    labels = synth.block_labels(n, H, W, C, block=8, seed=172)
+    labels[2] = 0                                             # an all-void image never yields a candidate
+    z, P = cuda(zn, Pn)
+    pc = proto_class(N, C)
+    res = nearest.find_k_nearest_tensors(z, torch.from_numpy(labels).cuda(), P, pc, k=4)
+    assert (res["images"][:, :2] >= 0).all() and (res["images"][:, :2] < 2).all()
+    assert (res["images"][:, 2:] == -1).all() and (res["labels"][:, 2:] == -2).all()
+    assert np.all(np.diff(res["distances"][:, :2], axis=1) >= 0)
+    # the winning patch of every prototype is never a void one (NEAREST-resized label)
+    rl, cl = nearest.pil_nearest_lut(H, h), nearest.pil_nearest_lut(W, w)
+    for j in range(0, N, 17):
+        for t in range(2):
+            i, pi, pj = res["images"][j, t], res["patch_i"][j, t], res["patch_j"][j, t]
+            assert labels[i][rl[pi], cl[pj]] != 0

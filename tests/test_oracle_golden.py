@@ -156,3 +156,30 @@ def test_eval_epilogue_oracle_matches_torch_fixture(golden):
     assert tot["correct_pixels"] == int(g["correct_pixels"]) and tot["total_pixels"] == int(g["total_pixels"])
     for k in ("CLS_I", "CLS_U", "proto_counts"):
         assert np.array_equal(tot[k], g[k]), k
+
+
+def test_k_nearest_oracle_matches_reference_run(golden):
+    """fixture: the unmodified find_nearest.find_k_nearest_patches_to_prototypes (oracle/make_golden_nearest.py)"""
+    g = golden("nearest_small")
+    n_img, K, h, w, N, C, H, W, k, seed = [int(v) for v in g["meta"]]
+    pc = np.arange(N) // (N // C)
+    lab, d, img, patch = orc.find_k_nearest(g["z"], g["P"], g["labels"], pc, k)
+    assert np.array_equal(lab, g["nearest_labels"])
+    assert np.all(np.diff(d, axis=1) >= 0) and np.all(np.isfinite(d))
+    # pruning rule (prune.py:31-42) on the reference's labels
+    pr = orc.prototypes_to_prune(g["nearest_labels"], pc, 2)
+    assert pr == [j for j in range(N) if list(g["nearest_labels"][j]).count(int(pc[j])) < 2]
+
+
+def test_pil_nearest_lut_is_what_pillow_does():
+    """resize_label (dataset.py:23-31) = PIL NEAREST; the LUT restatement must match Pillow itself, including the
+    1024 x 2048 -> 129 x 257 Cityscapes case where the accumulated coordinate rounds down at column 128"""
+    from PIL import Image
+    from adlm_inherently_interpretable_segmentation_b200 import nearest
+    for (H, W, h, w) in [(1024, 2048, 129, 257), (513, 513, 65, 65), (70, 100, 9, 13), (500, 375, 63, 47)]:
+        rows = np.repeat(np.arange(H, dtype=np.float64)[:, None], W, 1)
+        cols = np.repeat(np.arange(W, dtype=np.float64)[None, :], H, 0)
+        rr = np.asarray(Image.fromarray(rows).resize((w, h), resample=Image.NEAREST))[:, 0]
+        cc = np.asarray(Image.fromarray(cols).resize((w, h), resample=Image.NEAREST))[0, :]
+        for f in (orc.pil_nearest_lut, nearest.pil_nearest_lut):
+            assert np.array_equal(rr, f(H, h)) and np.array_equal(cc, f(W, w)), (H, W, h, w)
