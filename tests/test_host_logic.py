@@ -127,3 +127,39 @@ def test_non_onehot_identity_is_rejected():
     ident[0, 1] = 1
     with pytest.raises(NotImplementedError):
         head.proto_class_from_identity(ident)
+
+
+def test_eval_source_tables_match_oracle_and_tile_extent():
+    """host tables of the evaluation epilogue (torch's align_corners=False source index, float32)"""
+    from adlm_inherently_interpretable_segmentation_b200 import evalops, _lib
+    for in_size, out_size in [(129, 1024), (257, 2048), (65, 513), (9, 70), (13, 100), (7, 7), (5, 3)]:
+        idx, lam = evalops.source_tables(in_size, out_size)
+        i0, i1, l1 = orc.bilinear_tables(in_size, out_size)
+        assert np.array_equal(idx, i0) and np.array_equal(lam, l1)
+        assert idx.min() >= 0 and idx.max() <= in_size - 1 and (lam >= 0).all() and (lam < 1).all()
+        ext = evalops.tile_patch_extent(idx, in_size, _lib.EVAL_TILE_Y)
+        # brute force: rows touched by every tile (second tap = min(idx + 1, in - 1))
+        worst = 0
+        for a in range(0, out_size, _lib.EVAL_TILE_Y):
+            rows = set()
+            for y in range(a, min(a + _lib.EVAL_TILE_Y, out_size)):
+                rows.update((int(idx[y]), min(int(idx[y]) + 1, in_size - 1)))
+            worst = max(worst, max(rows) - min(rows) + 1)
+        assert ext == worst
+
+
+def test_nearest_patch_label_rule_and_pruning():
+    """find_nearest.py:196-205 label rule and prune.py:31-42 on hand-made cases"""
+    from adlm_inherently_interpretable_segmentation_b200 import nearest
+    lab = np.zeros((8, 12), np.uint8)                     # 2 x 3 patches of 4 x 4 pixels, 0 = void
+    lab[:4, :4] = 3                                       # patch (0,0): class 2 everywhere
+    lab[:4, 4:8] = 1; lab[0, 4] = 5                       # patch (0,1): class 0 with one pixel of class 4
+    lab[4:, 8:] = 0                                       # patch (1,2): void only
+    assert nearest.patch_label(lab, 0, 0, 2, 3, target_class=7) == 2       # most common
+    assert nearest.patch_label(lab, 0, 1, 2, 3, target_class=4) == 4       # any pixel of the prototype's class wins
+    assert nearest.patch_label(lab, 0, 1, 2, 3, target_class=9) == 0
+    assert nearest.patch_label(lab, 1, 2, 2, 3, target_class=1) == -1      # void
+    labels = np.array([[0, 0, 1], [1, 1, 1], [2, 0, -1], [0, 3, 3]])
+    pc = np.array([0, 1, 2, 3])
+    assert nearest.prototypes_to_prune(labels, pc, 2) == orc.prototypes_to_prune(labels, pc, 2) == [2]
+    assert nearest.prototypes_to_prune(labels, pc, 3) == [0, 2, 3]
