@@ -18,7 +18,7 @@ MAX_PROTOS_PER_CLASS = 16
 MAX_PUSH_CLASSES = 32
 STEP_NSCALARS = 8
 PUSH_NONE = 0x7FFFFFFFFFFFFFFF
-ABI_VERSION = 7
+ABI_VERSION = 8
 EVAL_TILE_X, EVAL_TILE_Y = 64, 16
 DP_MAX_WORLD = 16
 
@@ -55,7 +55,8 @@ SIGNATURES = {
 
 class DpComm(ctypes.Structure):
     """adlm_dp_comm (include/adlm_head.h)"""
-    _fields_ = [("rank", c_int), ("world", c_int), ("seq", c_ulonglong), ("peers", ctypes.POINTER(c_void_p))]
+    _fields_ = [("rank", c_int), ("world", c_int), ("seq", c_ulonglong), ("peers", ctypes.POINTER(c_void_p)),
+                ("timeout_ms", ctypes.c_uint)]
 
 
 SIGNATURES["adlm_dp_exchange_bytes"] = (c_size_t, [c_int, c_int, c_int, c_int])

@@ -219,6 +219,7 @@ int adlm_step_fwd_bwd_dp(const float* z, int B, int K, int HW, const float* P, c
   DpComm cm;
   cm.rank = comm->rank;
   cm.world = comm->world;
+  cm.timeout_ns = (unsigned long long)(comm->timeout_ms ? comm->timeout_ms : 30000u) * 1000000ull;
   // the flags hold the low 32 bits of the counter; 0 is the buffers' initial state, so it is skipped
   cm.seq = (unsigned int)(comm->seq & 0xffffffffull);
   if (cm.seq == 0u) cm.seq = 0x80000000u | (unsigned int)(comm->seq & 1ull);

@@ -102,6 +102,7 @@ constexpr int DP_MAX_WORLD = ADLM_DP_MAX_WORLD;
 struct DpComm {
   int rank = 0, world = 1;
   unsigned int seq = 0;                  // 0 = exchange disabled
+  unsigned long long timeout_ns = 30000000000ull;   // bound of every wait for a peer
   char* peer[DP_MAX_WORLD] = {};
 };
 struct DpLayout {                        // byte offsets inside one rank's exchange buffer
@@ -133,11 +134,17 @@ __device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-// bounded spin (~3 s at 2 GHz): a dead peer turns into NaN results instead of a hung GPU
-__device__ __forceinline__ bool dp_wait_flag(const unsigned int* p, unsigned int v) {
-  const long long t0 = clock64();
+// bounded spin on wall-clock nanoseconds (%globaltimer): a dead peer turns into NaN results instead of a hung GPU
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ bool dp_wait_flag(const unsigned int* p, unsigned int v, unsigned long long timeout_ns) {
+  if (ld_acquire_sys(p) == v) return true;
+  const unsigned long long t0 = global_ns();
   while (ld_acquire_sys(p) != v) {
-    if (clock64() - t0 > 6000000000LL) return false;
+    if (global_ns() - t0 > timeout_ns) return false;
     __nanosleep(40);
   }
   return true;

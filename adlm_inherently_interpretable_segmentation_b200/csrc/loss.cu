@@ -322,7 +322,8 @@ k_step_prepare(const int32_t* __restrict__ target, const int32_t* __restrict__ p
     __threadfence_system();
     st_release_sys(reinterpret_cast<unsigned int*>(pb + lay.cflag) + par * Wd + comm.rank, comm.seq);
     char* me = comm.peer[comm.rank];
-    const bool ok = dp_wait_flag(reinterpret_cast<const unsigned int*>(me + lay.cflag) + par * Wd + tid, comm.seq);
+    const bool ok = dp_wait_flag(reinterpret_cast<const unsigned int*>(me + lay.cflag) + par * Wd + tid, comm.seq,
+                                 comm.timeout_ns);
     const volatile int* slot_in = reinterpret_cast<const volatile int*>(me + lay.cnt) + (par * Wd + tid) * 2;
     s_all[tid][0] = slot_in[0];
     s_all[tid][1] = slot_in[1];

@@ -841,7 +841,7 @@ k_reduce_partials(const float* __restrict__ partials, int n_parts, int Npad2, in
       st_release_sys(reinterpret_cast<unsigned int*>(cm.peer[r] + lay.gflag) +
                          (size_t)(par * Wd + cm.rank) * lay.n_blocks + blockIdx.x, cm.seq);
       const bool ok = dp_wait_flag(reinterpret_cast<const unsigned int*>(cm.peer[cm.rank] + lay.gflag) +
-                                       (size_t)(par * Wd + r) * lay.n_blocks + blockIdx.x, cm.seq);
+                                       (size_t)(par * Wd + r) * lay.n_blocks + blockIdx.x, cm.seq, cm.timeout_ns);
       if (!ok) s_timeout = 1;
     }
     __syncthreads();

@@ -105,6 +105,10 @@ class DpExchange:
     DpExchange.local(device, world) builds `world` plain buffers on ONE device instead — the single-process
     form used by the tests and by N "ranks" sharing a GPU on separate streams."""
 
+    #: wall-clock bound of every in-kernel wait for a peer (a stalled data loader on one rank is normal; a dead
+    #: rank should not hang the others for ever): results are NaN and scalars[7] > 0 after it expires
+    timeout_ms = 30000
+
     def __init__(self, K, N, C, device, group=None):
         import torch.distributed._symmetric_memory as symm_mem
         lib = _lib_mod().load()
@@ -157,7 +161,8 @@ class DpExchange:
             raise ValueError(f"DpExchange was built for (K,N,C)={self.shape}, step has {(K, N, C)}")
         self.seq += 1
         L = _lib_mod()
-        return L.DpComm(self.rank, self.world, self.seq, ctypes.cast(self._ptrs, ctypes.POINTER(ctypes.c_void_p)))
+        return L.DpComm(self.rank, self.world, self.seq, ctypes.cast(self._ptrs, ctypes.POINTER(ctypes.c_void_p)),
+                        int(self.timeout_ms))
 
 
 def _lib_mod():

@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define ADLM_ABI_VERSION 7
+#define ADLM_ABI_VERSION 8
 
 #if defined(__GNUC__)
 #define ADLM_API __attribute__((visibility("default")))
@@ -202,13 +202,14 @@ ADLM_API int adlm_step_counts(const int32_t* target, int B, int HW,
  *   comm->seq: step counter, identical on all ranks, 1 for the first step and +1 per step on this buffer.
  * Requires ADLM_PREC_TF32, K <= 64, N <= 192, C <= 32 and non-NULL dz/dP/dW (else ADLM_E_UNSUPPORTED: use
  * adlm_step_counts + adlm_step_fwd_bwd(global_counts) + a library all-reduce).  A peer that never arrives
- * makes the waits time out after about 3 s: the outputs are then NaN and scalars[7] > 0.
+ * makes the waits time out after comm->timeout_ms (wall clock): the outputs are then NaN and scalars[7] > 0.
  */
 typedef struct adlm_dp_comm {
   int rank;
   int world;
   unsigned long long seq;
   void* const* peers;
+  unsigned int timeout_ms; /* bound of every in-kernel wait for a peer; 0 = 30000 */
 } adlm_dp_comm;
 ADLM_API size_t adlm_dp_exchange_bytes(int K, int N, int C, int world);
 /* diagnostics / tests: byte offsets inside one exchange buffer, HOST array of 8:

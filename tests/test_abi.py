@@ -86,7 +86,7 @@ def test_dp_exchange_layout_is_consistent(lib):
         assert total - grad >= 2 * world_size * n_grad_pad * 4
     assert lib.adlm_dp_exchange_bytes(K, N, C, _lib.DP_MAX_WORLD + 1) == 0
     assert lib.adlm_dp_exchange_layout(K, N, C, 0, None) == _lib.E_INVALID
-    comm = _lib.DpComm(0, 1, 0, None)
+    comm = _lib.DpComm(0, 1, 0, None, 0)
     rc = lib.adlm_step_fwd_bwd_dp(None, 1, 64, 16, None, None, 10, 2, ctypes.c_float(1e-4), 1, None, None, 1,
                                   ctypes.c_float(1), ctypes.c_float(1), ctypes.c_float(1), ctypes.c_float(1),
                                   None, None, None, None, None, None, None, 0, ctypes.byref(comm), None)

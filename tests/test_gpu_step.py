@@ -1,6 +1,8 @@
 """GPU parity of the fused training step (adlm_step_fwd_bwd: forward + CE + KLD + masked L1 + backward,
 segmentation/module.py:137-222,236) against fixtures produced by the reference's own _step and against the
 oracle, plus the data-parallel split on one device."""
+import time
+
 import numpy as np
 import pytest
 import torch
@@ -285,13 +287,16 @@ def test_dp_exchange_world_of_one_and_limits():
 
 
 def test_dp_exchange_dead_peer_times_out_with_nan():
-    """a peer that never publishes: the bounded waits expire (~3 s each), gradients are NaN, scalars[7] > 0"""
+    """a peer that never publishes: the bounded waits expire (timeout_ms each), gradients are NaN, scalars[7] > 0"""
     if not available("tf32"):
         pytest.skip("tf32 kernels not built")
     z, P, W, target, pc, (K, N, C) = _dp_case(seed=91)
     exs = parallel.DpExchange.local(K, N, C, z.device, 2)
+    exs[0].timeout_ms = 300
+    t0 = time.perf_counter()
     res = head.fused_step(z[:2], P, W, target[:2], pc, precision="tf32", dp_comm=exs[0])
     torch.cuda.synchronize()
+    assert 0.5 <= time.perf_counter() - t0 <= 5.0        # two waits of 300 ms, not the 30 s default
     assert float(res.scalars[7]) > 0.0
     assert bool(torch.isnan(res.dP).all()) and bool(torch.isnan(res.dW).all())
 
