@@ -19,16 +19,6 @@
 namespace adlm {
 
 constexpr int JMAX = ADLM_MAX_PROTOS_PER_CLASS;
-// per-group table written by k_kld_stats and read by k_kld_grad
-constexpr int GT_LSE = 0;                  // [JMAX] log-sum-exp of each prototype's distances
-constexpr int GT_CSUM = JMAX;              // [JMAX] C_a = sum_b c_ab
-constexpr int GT_R = 2 * JMAX;             // [JMAX] R_a = sum_b c_ab (A[a][a] - A[a][b])
-constexpr int GT_C = 3 * JMAX;             // [JMAX][JMAX] c_ab
-constexpr int GT_VALID = 3 * JMAX + JMAX * JMAX;
-constexpr int GT_SIZE = GT_VALID + 8;      // floats per group (multiple of 8)
-
-int group_table_floats() { return GT_SIZE; }
-
 namespace {
 
 // One thread per pixel: CE contribution, correctness, dlogits (module.py:156-165,210-211).
@@ -384,7 +374,6 @@ struct StepWorkspace {  // carved out of the caller's workspace buffer
   float* dlogits;    // [M, C]
   float* own;        // [M, JMAX]
   float* own_grad;   // [M, JMAX]
-  float* gtab;       // [B*C, GT_SIZE]
   int* hist;         // [B, C+1]
   int* cls_count;    // [C]
   int* counts;       // [2]
@@ -404,7 +393,6 @@ StepWorkspace carve_step_workspace(void* base, int B, int K, int HW, int N, int 
   w.dlogits = (float*)take(M * C * sizeof(float));
   w.own = (float*)take(M * JMAX * sizeof(float));
   w.own_grad = (float*)take(M * JMAX * sizeof(float));
-  w.gtab = (float*)take((size_t)B * C * GT_SIZE * sizeof(float));
   w.hist = (int*)take((size_t)B * (C + 1) * sizeof(int));
   w.cls_count = (int*)take((size_t)C * sizeof(int));
   w.counts = (int*)take(2 * sizeof(int));

@@ -58,12 +58,6 @@ struct TcBwdParams {
   int num_tiles;
 };
 
-// ds/dd of model.py:233 / :235
-__device__ __forceinline__ float dsdd_of(float d, float eps, int act_mode) {
-  if (act_mode == ADLM_ACT_LOG) return (eps - 1.f) * rcp_approx((d + 1.f) * (d + eps));
-  return -1.f;
-}
-
 // ------------------------------------------------------------------------------------------------ dZ
 // smem: Pk [KP/4][Npad][4] | Pt [Npad/4][KP][4] | Wt [C8/4][Npad][4] | per WG: Zk [KP/4][128][4], dLk [C8/4][128][4]
 template <int KP>
