@@ -99,3 +99,24 @@ def test_eval_upsample_at_cityscapes_size_against_torch():
     assert only["nearest"] is None and only["counters"] is None and torch.equal(only["pred"], res["pred"])
     with pytest.raises(ValueError):
         evalops.upsample_argmax(logits.cpu(), (H, W))
+
+
+@pytest.mark.parametrize("hw,HW", [((17, 23), (40, 61)), ((17, 23), (70, 92)), ((9, 13), (33, 53)), ((12, 16), (12, 16))])
+def test_eval_upsample_both_kernels_against_torch(hw, HW):
+    """x factors below 4 take the per-pixel kernel (torch's association), factors >= 4 the strip kernel; both must
+    agree with torch's interpolate + argmax / argmin except at near-ties, for widths that are no multiple of 4"""
+    (h, w), (H, W) = hw, HW
+    B, C, N = 2, 19, 190
+    g = torch.Generator(device="cuda").manual_seed(h * 100 + W)
+    logits = torch.randn(B, h, w, C, device="cuda", generator=g)
+    dist = torch.rand(B, N, h, w, device="cuda", generator=g) * 10
+    res = evalops.upsample_argmax(logits, (H, W), distances=dist)
+    up_l = F.interpolate(logits.permute(0, 3, 1, 2), size=(H, W), mode="bilinear", align_corners=False)
+    up_d = F.interpolate(dist, size=(H, W), mode="bilinear", align_corners=False)
+    got_p, got_n = res["pred"].long(), res["nearest"].long()
+    a = up_l.gather(1, got_p[:, None])[:, 0]
+    assert float((a - up_l.max(1).values).abs().max()) <= 1e-5
+    b = up_d.gather(1, got_n[:, None])[:, 0]
+    assert float((b - up_d.min(1).values).abs().max()) <= 1e-4
+    assert float((got_p != torch.argmax(up_l, 1)).float().mean()) <= 2e-3
+    assert float((got_n != torch.argmin(up_d, 1)).float().mean()) <= 2e-3
