@@ -18,7 +18,7 @@ MAX_PROTOS_PER_CLASS = 16
 MAX_PUSH_CLASSES = 32
 STEP_NSCALARS = 8
 PUSH_NONE = 0x7FFFFFFFFFFFFFFF
-ABI_VERSION = 8
+ABI_VERSION = 9
 EVAL_TILE_X, EVAL_TILE_Y = 64, 16
 DP_MAX_WORLD = 16
 
@@ -79,6 +79,13 @@ SIGNATURES["adlm_step_fwd_bwd_pre"] = (c_int, [c_void_p, c_int, c_int, c_int, c_
 SIGNATURES["adlm_eval_upsample"] = (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                             c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                             c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p])
+
+SIGNATURES["adlm_push_scan_images"] = (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p,
+                                               c_int, c_void_p, c_void_p])
+SIGNATURES["adlm_min_pool_fwd"] = (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_int,
+                                           c_void_p, c_void_p, c_void_p, c_void_p])
+SIGNATURES["adlm_min_pool_bwd"] = (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_int,
+                                           c_void_p, c_void_p, c_void_p, c_void_p, c_void_p])
 
 _lib = None
 

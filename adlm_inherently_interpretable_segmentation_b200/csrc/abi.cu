@@ -320,15 +320,53 @@ int adlm_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mas
   ADLM_CHECK_SUPPORTED(patch_base + (long long)n_img * HW < (1ll << 32), "global patch id needs more than 32 bits");
   switch (prec_mode) {
     case ADLM_PREC_FP32:
-      return simt_push_scan(z, n_img, K, HW, mask, P, N, proto_class, patch_base, packed_min, (cudaStream_t)stream);
+      return simt_push_scan(z, n_img, K, HW, mask, P, N, proto_class, patch_base, packed_min, 0,
+                            (cudaStream_t)stream);
     case ADLM_PREC_TF32:
     case ADLM_PREC_TF32X3:
-      return tc_push_scan(z, n_img, K, HW, mask, P, N, proto_class, patch_base, prec_mode, packed_min,
+      return tc_push_scan(z, n_img, K, HW, mask, P, N, proto_class, patch_base, prec_mode, packed_min, 0,
                           (cudaStream_t)stream);
     default:
       set_error("unknown prec_mode %d", prec_mode);
       return ADLM_E_INVALID;
   }
+}
+
+int adlm_push_scan_images(const float* z, int n_img, int K, int HW, const uint32_t* mask, const float* P, int N,
+                          const int32_t* proto_class, int prec_mode, unsigned long long* packed_min, void* stream) {
+  ADLM_CHECK_ARG(z && P && packed_min, "null pointer argument");
+  ADLM_CHECK_ARG(n_img > 0 && K > 0 && HW > 0 && N > 0, "bad size");
+  ADLM_CHECK_SUPPORTED(K <= ADLM_MAX_K, "K > 256");
+  ADLM_CHECK_SUPPORTED((long long)n_img * HW < (1ll << 31), "more than 2^31 patches per call (split the batch)");
+  switch (prec_mode) {
+    case ADLM_PREC_FP32:
+      return simt_push_scan(z, n_img, K, HW, mask, P, N, proto_class, 0, packed_min, 1, (cudaStream_t)stream);
+    case ADLM_PREC_TF32:
+    case ADLM_PREC_TF32X3:
+      return tc_push_scan(z, n_img, K, HW, mask, P, N, proto_class, 0, prec_mode, packed_min, 1,
+                          (cudaStream_t)stream);
+    default:
+      set_error("unknown prec_mode %d", prec_mode);
+      return ADLM_E_INVALID;
+  }
+}
+
+int adlm_min_pool_fwd(const float* z, int B, int K, int HW, const float* P, int N, int prec_mode,
+                      unsigned long long* packed, float* min_dist, int32_t* argmin, void* stream) {
+  ADLM_CHECK_ARG(min_dist != nullptr, "null pointer argument");
+  ADLM_CHECK_SUPPORTED((long long)B * N < (1ll << 31), "B*N too large");
+  const int rc = adlm_push_scan_images(z, B, K, HW, nullptr, P, N, nullptr, prec_mode, packed, stream);
+  if (rc != ADLM_OK) return rc;
+  return min_pool_unpack_impl(packed, B, N, min_dist, argmin, (cudaStream_t)stream);
+}
+
+int adlm_min_pool_bwd(const float* z, int B, int K, int HW, const float* P, int N,
+                      const unsigned long long* packed, const float* grad_min, float* dz, float* dP, void* stream) {
+  ADLM_CHECK_ARG(z && P && packed && grad_min, "null pointer argument");
+  ADLM_CHECK_ARG(B > 0 && K > 0 && HW > 0 && N > 0, "bad size");
+  ADLM_CHECK_SUPPORTED(B <= 65535, "B > 65535 per call");
+  if (!dz && !dP) return ADLM_OK;
+  return min_pool_bwd_impl(z, B, K, HW, P, N, packed, grad_min, dz, dP, (cudaStream_t)stream);
 }
 
 int adlm_push_gather(const float* z, int n_img, int K, int HW, long long patch_base,

@@ -220,7 +220,11 @@ int patch_class_mask_impl(const uint8_t* labels, int n_img, int H, int Wimg, con
                           const int32_t* col_lut, int h, int w, uint32_t* mask_out, cudaStream_t st);
 int simt_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mask, const float* P, int N,
                    const int32_t* proto_class, long long patch_base, unsigned long long* packed_min,
-                   cudaStream_t st);
+                   int per_image, cudaStream_t st);
+int min_pool_unpack_impl(const unsigned long long* packed, int B, int N, float* min_dist, int32_t* argmin,
+                         cudaStream_t st);
+int min_pool_bwd_impl(const float* z, int B, int K, int HW, const float* P, int N,
+                      const unsigned long long* packed, const float* gmin, float* dz, float* dP, cudaStream_t st);
 int push_gather_impl(const float* z, int n_img, int K, int HW, long long patch_base,
                      const unsigned long long* packed_min, int N, float* proto_out, cudaStream_t st);
 

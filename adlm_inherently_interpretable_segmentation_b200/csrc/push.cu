@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(NT)
 k_simt_push_scan(const float* __restrict__ z, int K, int HW, const uint32_t* __restrict__ mask,
                  const float* __restrict__ P, int N, const int32_t* __restrict__ proto_class,
                  unsigned long long patch_base, unsigned long long* __restrict__ packed_min,
-                 int tiles_per_img) {
+                 int tiles_per_img, int per_image) {
   extern __shared__ __align__(16) float smem[];
   const int Kq = (K + 63) & ~63;
   float* zs = smem;
@@ -128,7 +128,7 @@ k_simt_push_scan(const float* __restrict__ z, int K, int HW, const uint32_t* __r
     const int k = idx >> 6, px = idx & 63, p = p0 + px;
     zs[idx] = (k < K && p < HW) ? __ldg(zb + (size_t)k * HW + p) : 0.f;
   }
-  if (tid < TM) ms[tid] = (p0 + tid < HW) ? mask[(size_t)img * HW + p0 + tid] : 0u;
+  if (tid < TM) ms[tid] = (p0 + tid < HW) ? (mask ? mask[(size_t)img * HW + p0 + tid] : 0xffffffffu) : 0u;
   __syncthreads();
   if (tid < TM) {
     float a = 0.f;
@@ -150,7 +150,7 @@ k_simt_push_scan(const float* __restrict__ z, int K, int HW, const uint32_t* __r
     }
     if (tid < TN) {
       best[tid] = ADLM_PUSH_NONE;
-      pcs[tid] = (n0 + tid < N) ? proto_class[n0 + tid] : -1;
+      pcs[tid] = (n0 + tid < N) ? (proto_class ? proto_class[n0 + tid] : 0) : -1;
     }
     __syncthreads();
     if (tid >= 64 && tid < 128) {
@@ -190,7 +190,8 @@ k_simt_push_scan(const float* __restrict__ z, int K, int HW, const uint32_t* __r
             const float d = fmaxf(x2s[px] + fmaf(-2.f, acc[i][j], p2s[nl]), 0.f);
             const unsigned long long kk =
                 ((unsigned long long)__float_as_uint(d) << 32) |
-                (patch_base + (unsigned long long)img * HW + (unsigned long long)(p0 + px));
+                (per_image ? (unsigned long long)(p0 + px)
+                           : patch_base + (unsigned long long)img * HW + (unsigned long long)(p0 + px));
             key = kk < key ? kk : key;
           }
         }
@@ -204,7 +205,8 @@ k_simt_push_scan(const float* __restrict__ z, int K, int HW, const uint32_t* __r
       if (tx == 0 && key != ADLM_PUSH_NONE) best[nl] = key;   // one writer per prototype
     }
     __syncthreads();
-    if (tid < TN && n0 + tid < N && best[tid] != ADLM_PUSH_NONE) atomicMin(packed_min + n0 + tid, best[tid]);
+    if (tid < TN && n0 + tid < N && best[tid] != ADLM_PUSH_NONE)
+      atomicMin(packed_min + (per_image ? (size_t)img * N : (size_t)0) + n0 + tid, best[tid]);
   }
 }
 
@@ -221,7 +223,57 @@ __global__ void k_push_gather(const float* __restrict__ z, int n_img, int K, int
   for (int k = threadIdx.x; k < K; k += blockDim.x) out[(size_t)n * K + k] = z[(img * K + k) * HW + p];
 }
 
+// Legacy min-pool classification branch (model.py:284-299): the (B,N) minima come from the per-image scan;
+// these two kernels are its (B*N*K)-sized ends.
+// forward tail: unpack the per-image minima into min_distances [B,N] (+inf -> never happens without a mask)
+__global__ void k_min_pool_unpack(const unsigned long long* __restrict__ packed, int total,
+                                  float* __restrict__ min_dist, int32_t* __restrict__ argmin) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const unsigned long long key = packed[i];
+  const bool none = key == ADLM_PUSH_NONE;
+  min_dist[i] = none ? __int_as_float(0x7f800000) : __uint_as_float((uint32_t)(key >> 32));
+  if (argmin) argmin[i] = none ? -1 : (int32_t)(key & 0xffffffffULL);
+}
+
+// backward: the gradient of min_distances[b,n] lands on the single patch that attains the minimum
+// (max_pool2d backward) and passes the relu only where d > 0 (model.py:218):
+//   dz[b,:,patch] += 2 g (z - p),  dP[n,:] -= 2 g (z - p)
+__global__ void k_min_pool_bwd(const float* __restrict__ z, int K, int HW, const float* __restrict__ P, int N,
+                               const unsigned long long* __restrict__ packed, const float* __restrict__ gmin,
+                               float* __restrict__ dz, float* __restrict__ dP) {
+  const int n = blockIdx.x, b = blockIdx.y;
+  const unsigned long long key = packed[(size_t)b * N + n];
+  if (key == ADLM_PUSH_NONE) return;
+  const float d = __uint_as_float((uint32_t)(key >> 32));
+  const float g = gmin[(size_t)b * N + n];
+  if (!(d > 0.f) || g == 0.f) return;
+  const size_t patch = (size_t)(key & 0xffffffffULL);
+  for (int k = threadIdx.x; k < K; k += blockDim.x) {
+    const size_t zi = ((size_t)b * K + k) * HW + patch;
+    const float t = 2.f * g * (__ldg(z + zi) - __ldg(P + (size_t)n * K + k));
+    if (dz) atomicAdd(dz + zi, t);
+    if (dP) atomicAdd(dP + (size_t)n * K + k, -t);
+  }
+}
+
 }  // namespace
+
+int min_pool_unpack_impl(const unsigned long long* packed, int B, int N, float* min_dist, int32_t* argmin,
+                         cudaStream_t st) {
+  const int total = B * N;
+  k_min_pool_unpack<<<cdiv(total, 256), 256, 0, st>>>(packed, total, min_dist, argmin);
+  ADLM_LAUNCH_CHECK();
+  return ADLM_OK;
+}
+
+int min_pool_bwd_impl(const float* z, int B, int K, int HW, const float* P, int N,
+                      const unsigned long long* packed, const float* gmin, float* dz, float* dP, cudaStream_t st) {
+  dim3 grid(N, B);
+  k_min_pool_bwd<<<grid, 64, 0, st>>>(z, K, HW, P, N, packed, gmin, dz, dP);
+  ADLM_LAUNCH_CHECK();
+  return ADLM_OK;
+}
 
 int patch_class_mask_impl(const uint8_t* labels, int n_img, int H, int Wimg, const int32_t* row_lut,
                           const int32_t* col_lut, int h, int w, uint32_t* mask_out, cudaStream_t st) {
@@ -238,7 +290,7 @@ int patch_class_mask_impl(const uint8_t* labels, int n_img, int H, int Wimg, con
 
 int simt_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mask, const float* P, int N,
                    const int32_t* proto_class, long long patch_base, unsigned long long* packed_min,
-                   cudaStream_t st) {
+                   int per_image, cudaStream_t st) {
   const int Kq = (K + 63) & ~63;
   const int tiles_per_img = cdiv(HW, TM);
   const long long grid = (long long)n_img * tiles_per_img;
@@ -248,7 +300,8 @@ int simt_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mas
   ADLM_CUDA(cudaFuncSetAttribute(k_simt_push_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
   KernelTimer timer(ADLM_K_PUSH_SCAN, st);
   k_simt_push_scan<<<(unsigned)grid, NT, bytes, st>>>(z, K, HW, mask, P, N, proto_class,
-                                                      (unsigned long long)patch_base, packed_min, tiles_per_img);
+                                                      (unsigned long long)patch_base, packed_min, tiles_per_img,
+                                                      per_image);
   ADLM_LAUNCH_CHECK();
   return ADLM_OK;
 }

@@ -43,6 +43,6 @@ int tc_head_bwd(const HeadShape& s, int prec_mode, const float* z, const float* 
 size_t tc_bwd_workspace_bytes(int K, int N);
 int tc_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mask, const float* P, int N,
                  const int32_t* proto_class, long long patch_base, int prec_mode,
-                 unsigned long long* packed_min, cudaStream_t st);
+                 unsigned long long* packed_min, int per_image, cudaStream_t st);
 
 }  // namespace adlm

@@ -39,6 +39,27 @@ struct TcPushParams {
   int K, HW, N;
   int M;          // n_img * HW
   int num_tiles;
+  // per-image minima (adlm_push_scan_images): tiles never straddle images (tiles_per_img each, the last one
+  // partly empty), every CTA owns a contiguous tile range so that an image change is rare, packed_min is
+  // [n_img][N] and the stored id is the patch index inside its image
+  int per_image;
+  int tiles_per_img;
+};
+
+// tile `it` of this CTA -> first global patch m0 and the number of real patches in the tile
+struct TileMap {
+  int first, stride, tpi, HW, M, per_image;
+  __device__ __forceinline__ void get(int it, int& m0, int& valid) const {
+    const int t = first + it * stride;
+    if (per_image) {
+      const int img = t / tpi, off = (t - img * tpi) * TILE;
+      m0 = img * HW + off;
+      valid = min(TILE, HW - off);
+    } else {
+      m0 = t * TILE;
+      valid = min(TILE, M - m0);
+    }
+  }
 };
 
 template <int KP, bool X3>
@@ -94,7 +115,17 @@ __global__ void __launch_bounds__(PUSH_THREADS, 1) k_tc_push(const TcPushParams 
   }
   const uint32_t bar0 = smem_u32(&bars[0]);
   auto bar = [&](int idx) { return bar0 + (uint32_t)idx * 8u; };
-  const int iters = p.num_tiles > (int)blockIdx.x ? (p.num_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  TileMap tmap;
+  tmap.tpi = p.tiles_per_img; tmap.HW = HW; tmap.M = p.M; tmap.per_image = p.per_image;
+  int iters;
+  if (p.per_image) {
+    const long long lo = (long long)blockIdx.x * p.num_tiles / (int)gridDim.x;
+    const long long hi = (long long)(blockIdx.x + 1) * p.num_tiles / (int)gridDim.x;
+    tmap.first = (int)lo; tmap.stride = 1; iters = (int)(hi - lo);
+  } else {
+    tmap.first = (int)blockIdx.x; tmap.stride = (int)gridDim.x;
+    iters = p.num_tiles > (int)blockIdx.x ? (p.num_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  }
 
   // producer warps start fetching their first two tiles right away
   const bool is_producer = warp >= 8;
@@ -103,8 +134,10 @@ __global__ void __launch_bounds__(PUSH_THREADS, 1) k_tc_push(const TcPushParams 
   float zrA[KH], zrB[KH];
   uint32_t mkA = 0u, mkB = 0u;
   auto prefetch = [&](int it, float (&zr)[KH], uint32_t& mk) {
-    const int m = ((int)blockIdx.x + it * (int)gridDim.x) * TILE + cw;
-    if (it < iters && m < p.M) {
+    int m0 = 0, valid = 0;
+    if (it < iters) tmap.get(it, m0, valid);
+    const int m = m0 + cw;
+    if (cw < valid) {
       const int img = m / HW;
       const float* src = p.z + ((size_t)img * K + half * KH) * HW + (m - img * HW);
       if (K == KP) {
@@ -114,7 +147,7 @@ __global__ void __launch_bounds__(PUSH_THREADS, 1) k_tc_push(const TcPushParams 
 #pragma unroll
         for (int k = 0; k < KH; ++k) zr[k] = (half * KH + k < K) ? __ldg(src + (size_t)k * HW) : CENTRE;
       }
-      mk = __ldg(p.mask + m);
+      mk = p.mask ? __ldg(p.mask + m) : 0xffffffffu;       // no mask: every patch is a candidate
     } else {
 #pragma unroll
       for (int k = 0; k < KH; ++k) zr[k] = CENTRE;
@@ -159,7 +192,7 @@ __global__ void __launch_bounds__(PUSH_THREADS, 1) k_tc_push(const TcPushParams 
     }
     tmem_st_wait();
     if (n < N) {
-      const int pc = p.proto_class[n];
+      const int pc = p.proto_class ? p.proto_class[n] : 0;   // no class table: every prototype reads bit 0
       if (pc >= 0 && pc < 32) crow = pc;
     }
   }
@@ -255,9 +288,29 @@ __global__ void __launch_bounds__(PUSH_THREADS, 1) k_tc_push(const TcPushParams 
     float best = __int_as_float(0x7f800000);                            // +inf
     int best_m = -1;
     const float negp2 = -p2;
+    int cur_img = -1;
+    auto flush = [&]() {
+      if (n < N && best_m >= 0) {
+        const unsigned long long dbits = (unsigned long long)__float_as_uint(fmaxf(best + p2, 0.f)) << 32;
+        if (p.per_image)
+          atomicMin(p.packed_min + (size_t)cur_img * N + n, dbits | (unsigned long long)(best_m - cur_img * HW));
+        else
+          atomicMin(p.packed_min + n, dbits | (p.patch_base + (unsigned long long)best_m));
+      }
+    };
     for (int it = 0; it < iters; ++it) {
       const int a = it & 1, j = it >> 1;
-      const int m0 = ((int)blockIdx.x + it * (int)gridDim.x) * TILE;
+      int m0, valid;
+      tmap.get(it, m0, valid);
+      if (p.per_image) {
+        const int img = m0 / HW;
+        if (img != cur_img) {
+          if (cur_img >= 0) flush();
+          best = __int_as_float(0x7f800000);
+          best_m = -1;
+          cur_img = img;
+        }
+      }
       if (blk < NB) {
         mbar_wait(bar(B_META + a), (uint32_t)j & 1u);
         mbar_wait(bar(B_AFULL + blk), (uint32_t)it & 1u);
@@ -297,12 +350,8 @@ __global__ void __launch_bounds__(PUSH_THREADS, 1) k_tc_push(const TcPushParams 
       }
       mbar_arrive(bar(B_MEMPTY + a));
     }
-    // padding columns of the last tile (m >= M) carry mask 0 and never win
-    if (n < N && best_m >= 0) {
-      const unsigned long long key =
-          ((unsigned long long)__float_as_uint(fmaxf(best + p2, 0.f)) << 32) | (p.patch_base + (unsigned long long)best_m);
-      atomicMin(p.packed_min + n, key);
-    }
+    // padding columns of a partly empty tile carry mask 0 and never win
+    flush();
   }
   fence_before();
   __syncthreads();
@@ -337,17 +386,20 @@ int launch_push(const TcPushParams& prm, cudaStream_t st) {
 
 int tc_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mask, const float* P, int N,
                  const int32_t* proto_class, long long patch_base, int prec_mode,
-                 unsigned long long* packed_min, cudaStream_t st) {
+                 unsigned long long* packed_min, int per_image, cudaStream_t st) {
   const long long M = (long long)n_img * HW;
+  const int tiles_per_img = (HW + TILE - 1) / TILE;
   // shapes beyond the tensor-core kernel's operand budget take the fp32 CUDA-core scan: same search, same keys
-  if (K > 64 || N > 224 || M >= (1ll << 31) - 256)
-    return simt_push_scan(z, n_img, K, HW, mask, P, N, proto_class, patch_base, packed_min, st);
+  if (K > 64 || N > 224 || M >= (1ll << 31) - 256 || (long long)n_img * tiles_per_img >= (1ll << 31))
+    return simt_push_scan(z, n_img, K, HW, mask, P, N, proto_class, patch_base, packed_min, per_image, st);
   TcPushParams prm;
   prm.z = z; prm.mask = mask; prm.P = P; prm.proto_class = proto_class; prm.packed_min = packed_min;
   prm.patch_base = (unsigned long long)patch_base;
   prm.K = K; prm.HW = HW; prm.N = N;
   prm.M = (int)M;
-  prm.num_tiles = (int)((M + TILE - 1) / TILE);
+  prm.per_image = per_image;
+  prm.tiles_per_img = tiles_per_img;
+  prm.num_tiles = per_image ? n_img * tiles_per_img : (int)((M + TILE - 1) / TILE);
   const bool x3 = prec_mode == ADLM_PREC_TF32X3;
   const int nb = N > 128 ? 2 : 1;
 #define ADLM_PUSH_CASE(KPV)                                                                    \

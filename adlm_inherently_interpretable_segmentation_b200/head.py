@@ -329,3 +329,65 @@ class FusedStepFunction(torch.autograd.Function):
         g = dloss.to(torch.float32)
         return (dz * g if need[0] else None, dP * g if need[1] else None, dW * g if need[2] else None,
                 None, None, None)
+
+
+# ---- legacy min-pool classification branch (model.py:284-299) -------------------------------------------------
+
+#: arithmetic of the min-pool scan: the arg-min decides where the gradient goes, so fp32-class distances by default
+MIN_POOL_DEFAULT_PRECISION = "tf32x3"
+
+
+def min_pool_forward(z, prototypes, precision=None):
+    """z (B,K,h,w), prototypes (N,K[,1,1]) -> (min_distances (B,N) f32, argmin (B,N) int32 patch index, packed (B,N)
+    int64 workspace for the backward).  The (B,N,h,w) distance map is never written (adlm_min_pool_fwd)."""
+    lib = _lib.load()
+    _check_cuda_f32("conv_features", z)
+    _check_cuda_f32("prototype_vectors", prototypes)
+    if z.dim() != 4:
+        raise ValueError("conv_features must be (B,K,h,w)")
+    z = z.contiguous()
+    P = _proto_2d(prototypes).contiguous()
+    B, K, h, w = z.shape
+    N = P.shape[0]
+    if P.shape[1] != K:
+        raise ValueError(f"shape mismatch: z K={K}, prototypes {tuple(P.shape)}")
+    dev = z.device
+    with torch.cuda.device(dev):
+        packed = torch.full((B, N), _lib.PUSH_NONE, device=dev, dtype=torch.int64)
+        mind = torch.empty((B, N), device=dev, dtype=torch.float32)
+        amin = torch.empty((B, N), device=dev, dtype=torch.int32)
+        rc = lib.adlm_min_pool_fwd(_lib.ptr(z), B, K, h * w, _lib.ptr(P), N,
+                                   _prec(precision or MIN_POOL_DEFAULT_PRECISION),
+                                   _lib.ptr(packed), _lib.ptr(mind), _lib.ptr(amin), _lib.stream_ptr())
+    _lib.check(rc, "adlm_min_pool_fwd")
+    return mind, amin, packed
+
+
+class MinPoolFunction(torch.autograd.Function):
+    """min_distances = -max_pool2d(-_l2_convolution(z)) (model.py:284-288) with autograd edges to z and the
+    prototypes; the backward scatters onto the arg-min patches (adlm_min_pool_bwd)."""
+
+    @staticmethod
+    def forward(ctx, z, prototypes, precision):
+        mind, amin, packed = min_pool_forward(z.detach(), prototypes.detach(), precision)
+        ctx.save_for_backward(z, prototypes, packed)
+        ctx.mark_non_differentiable(amin)
+        return mind, amin
+
+    @staticmethod
+    def backward(ctx, gmin, _gamin):
+        z, prototypes, packed = ctx.saved_tensors
+        lib = _lib.load()
+        zc = z.detach().contiguous()
+        P = _proto_2d(prototypes.detach()).contiguous()
+        B, K, h, w = zc.shape
+        N = P.shape[0]
+        need_dz, need_dP = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        g = gmin.contiguous().to(torch.float32)
+        with torch.cuda.device(zc.device):
+            dz = torch.zeros_like(zc) if need_dz else None
+            dP = torch.zeros_like(P) if need_dP else None
+            rc = lib.adlm_min_pool_bwd(_lib.ptr(zc), B, K, h * w, _lib.ptr(P), N, _lib.ptr(packed), _lib.ptr(g),
+                                       _lib.ptr(dz), _lib.ptr(dP), _lib.stream_ptr())
+        _lib.check(rc, "adlm_min_pool_bwd")
+        return dz, (dP.reshape(prototypes.shape) if need_dP else None), None

@@ -107,10 +107,17 @@ class PrototypeHeadMixin:
 
     def _forward_min_pool(self, conv_features, return_distances):
         """legacy ProtoPNet classification branch (model.py:284-299): global min-pool of the distance map,
-        then similarity + last layer on (B,N).  Distances come from the fused kernel; the (B,N)-sized
-        tail is negligible and stays in torch."""
-        distances = self._l2_convolution(conv_features)
-        min_distances = distances.flatten(2).min(dim=2).values
+        then similarity + last layer on (B,N).  The minima come from the per-image scan kernel
+        (adlm_min_pool_fwd: the (B,N,h,w) map is never written) and the backward scatters onto the arg-min
+        patches; the (B,N)-sized tail is negligible and stays in torch.  Only `return_distances=True`
+        materialises the map, because the caller asks for it."""
+        if return_distances:
+            distances = self._l2_convolution(conv_features)
+            min_distances = distances.flatten(2).min(dim=2).values
+        else:
+            distances = None
+            prec = self.head_precision if self.head_precision in ("fp32", "tf32x3") else None
+            min_distances, _ = _head.MinPoolFunction.apply(conv_features, self.prototype_vectors, prec)
         prototype_activations = self.distance_2_similarity(min_distances)
         logits = self.run_last_layer(prototype_activations)
         if return_distances:

@@ -5,13 +5,14 @@ copies the (N,h,w) distance map to the host, masks void pixels (labels resized w
 per-prototype minimum in numpy and keeps a heap of the k best images per prototype; prune.prune_prototypes
 (prune.py:11-42) prunes a prototype when fewer than `prune_threshold` of those k patches carry its own class.
 
-Here the per-image search is the push scan kernel (adlm_push_scan: distances on chip, one packed
-(distance bits, patch id) minimum per prototype) run with a void mask instead of the class mask; the top-k over
+Here the per-image search is the push scan kernel in its per-image mode (adlm_push_scan_images: ONE launch for
+all images, distances on chip, one packed (distance bits, patch index) minimum per (image, prototype)) run with a
+void mask instead of the class mask; the top-k over
 images is one stable sort of the (n_img, N) minima on the device, and only the N*k winning patches have their label
 regions looked at.  Deviation from the reference: an image without any non-void patch yields no candidate (the
 reference keeps it with distance + 1e7, find_nearest.py:132).
 """
-from ctypes import c_int, c_longlong
+from ctypes import c_int
 
 import numpy as np
 import torch
@@ -80,11 +81,10 @@ def find_k_nearest_tensors(z, labels, prototypes, proto_class, k=5, precision=No
     mask = void_mask(labels, h, w)
     packed = torch.full((n, N), _lib.PUSH_NONE, device=dev, dtype=torch.int64)
     prec = _prec(precision or PUSH_DEFAULT_PRECISION)
-    with torch.cuda.device(dev):
-        for i in range(n):                                   # one launch per image: per-(image, prototype) minima
-            rc = lib.adlm_push_scan(_lib.ptr(z[i]), 1, K, h * w, _lib.ptr(mask[i]), _lib.ptr(P), N, _lib.ptr(pc),
-                                    c_longlong(0), c_int(prec), _lib.ptr(packed[i]), _lib.stream_ptr())
-            _lib.check(rc, "adlm_push_scan")
+    with torch.cuda.device(dev):                             # one launch: per-(image, prototype) minima
+        rc = lib.adlm_push_scan_images(_lib.ptr(z), n, K, h * w, _lib.ptr(mask), _lib.ptr(P), N, _lib.ptr(pc),
+                                       c_int(prec), _lib.ptr(packed), _lib.stream_ptr())
+    _lib.check(rc, "adlm_push_scan_images")
     # packed words order like (distance, patch id); a stable sort over the image axis keeps the earlier image on
     # ties, as the reference's heap does (find_nearest.py:217-223)
     order = torch.sort(packed, dim=0, stable=True)

@@ -28,6 +28,9 @@
  *   adlm_push_scan         segmentation/push.py:249-280 (class-filtered per-prototype argmin,
  *                          strict '<' against the global minimum)
  *   adlm_push_gather       segmentation/push.py:268-280, :142-145 (winner feature vectors)
+ *   adlm_push_scan_images  find_nearest.py:128-160 (per-image, per-prototype nearest patch; void-masked)
+ *   adlm_min_pool_fwd/bwd  model.py:284-299 (legacy classification branch: global min-pool of the distance
+ *                          map) and its autograd backward, invoked at train_and_test.py:101
  */
 #ifndef ADLM_HEAD_H
 #define ADLM_HEAD_H
@@ -39,7 +42,7 @@
 extern "C" {
 #endif
 
-#define ADLM_ABI_VERSION 8
+#define ADLM_ABI_VERSION 9
 
 #if defined(__GNUC__)
 #define ADLM_API __attribute__((visibility("default")))
@@ -277,6 +280,34 @@ ADLM_API int adlm_push_scan(const float* z, int n_img, int K, int HW,
                    const uint32_t* mask, const float* P, int N, const int32_t* proto_class,
                    long long patch_base, int prec_mode,
                    unsigned long long* packed_min, void* stream);
+
+/*
+ * Per-image variant of the scan (find_nearest.py:128-160 takes the per-prototype minimum of every image's
+ * distance map; model.py:284-288 min-pools it): one launch for the whole batch.
+ *   packed_min [n_img,N] uint64, updated in place with
+ *       min(packed_min[i][j], (float_bits(d) << 32) | patch)       patch = index inside image i
+ *   mask may be NULL (every patch is a candidate), proto_class may be NULL (no class filter: every
+ *   prototype reads mask bit 0).  Initialise with ADLM_PUSH_NONE.
+ */
+ADLM_API int adlm_push_scan_images(const float* z, int n_img, int K, int HW,
+                          const uint32_t* mask, const float* P, int N, const int32_t* proto_class,
+                          int prec_mode, unsigned long long* packed_min, void* stream);
+
+/*
+ * Legacy classification branch (patch_classification = False, model.py:284-299): global min-pool of the
+ * distance map without materialising it.
+ *   fwd: packed [B,N] uint64 workspace (initialised with ADLM_PUSH_NONE by the caller, kept for the
+ *        backward), min_dist [B,N] = min over h*w of relu(|z|^2 - 2 z.p + |p|^2), argmin [B,N] int32
+ *        (patch index, may be NULL).
+ *   bwd: grad_min [B,N] -> dz [B,K,HW] and dP [N,K], both ACCUMULATED with atomics (caller zero-fills;
+ *        either may be NULL): the gradient reaches only the arg-min patch (max_pool2d backward,
+ *        model.py:287) and only where d > 0 (relu, model.py:218).
+ */
+ADLM_API int adlm_min_pool_fwd(const float* z, int B, int K, int HW, const float* P, int N, int prec_mode,
+                      unsigned long long* packed, float* min_dist, int32_t* argmin, void* stream);
+ADLM_API int adlm_min_pool_bwd(const float* z, int B, int K, int HW, const float* P, int N,
+                      const unsigned long long* packed, const float* grad_min,
+                      float* dz, float* dP, void* stream);
 
 /*
  * Push, step 3: fetch the winners that live in this shard.

@@ -15,6 +15,8 @@ Reference lines restated:
   patch_class_mask       segmentation/push.py:201-230 (pixel -> patch via int(i / (H/h)))
   push_search_image      segmentation/push.py:249-307 (class-filtered per-prototype argmin + RF box)
   push_finalize          segmentation/push.py:142-152 (de-dup with np.unique(axis=0))
+  min_pool_forward       model.py:284-299   (legacy classification branch: global min-pool, similarity, last layer)
+  min_pool_step          train_and_test.py:35-101 (cross entropy + cluster / separation costs + masked L1, backward)
 """
 import numpy as np
 
@@ -373,3 +375,67 @@ def prototypes_to_prune(nearest_labels, proto_class, prune_threshold):
     """prune.py:31-42: prototypes whose k nearest patches hold fewer than prune_threshold of their own class"""
     return [j for j in range(len(proto_class))
             if int(np.sum(np.asarray(nearest_labels[j]) == int(proto_class[j]))) < prune_threshold]
+
+
+def min_pool_forward(z, P, W, mode='log', dtype=np.float32):
+    """legacy classification branch   [model.py:284-299]
+    -> logits (B,C), min_distances (B,N), argmin (B,N) flat patch index (first minimum, as max_pool2d)"""
+    d = l2_distances(z, P, dtype)
+    B, N, h, w = d.shape
+    df = d.reshape(B, N, h * w)
+    amin = df.argmin(axis=2)
+    mind = np.take_along_axis(df, amin[:, :, None], axis=2)[:, :, 0]
+    act = distance_2_similarity(mind, mode)
+    logits = (act @ W.astype(dtype).T).astype(dtype)
+    return logits, mind, amin
+
+
+def min_pool_step(z, P, W, label, coefs=(1.0, 0.8, -0.08, 1e-4), eps=EPS):
+    """one class-specific training batch of train_and_test.py:35-101 (use_l1_mask=True, default coefficients
+    `cross_entropy + 0.8 cluster - 0.08 separation + 1e-4 l1`, :92) in float64, with the autograd backward
+    (:101) written out.  label (B,) ints.  -> dict(loss terms, logits, min_distances, dz, dP, dW)"""
+    z64, P64, W64 = z.astype(np.float64), P.astype(np.float64), W.astype(np.float64)
+    B, K, h, w = z.shape
+    N, C = P.shape[0], W.shape[0]
+    zf = z64.reshape(B, K, h * w)
+    pre = (zf * zf).sum(1)[:, None, :] - 2 * np.einsum('nk,bkm->bnm', P64, zf) + (P64 * P64).sum(1)[None, :, None]
+    df = np.maximum(pre, 0)
+    amin = df.argmin(axis=2)                                                 # (B,N)
+    mind = np.take_along_axis(df, amin[:, :, None], axis=2)[:, :, 0]
+    act = np.log((mind + 1) / (mind + eps))
+    logits = act @ W64.T
+    lse = _logsumexp(logits, axis=1)
+    logp = logits - lse[:, None]
+    ce = -logp[np.arange(B), label].mean()                                   # :38
+    ident = class_identity(N, C)
+    correct = ident[:, label].T                                              # (B,N)  :46
+    wrong = 1 - correct
+    max_dist = float(K)                                                      # :41-43, 1x1 prototypes
+    inv_c = (max_dist - mind) * correct
+    inv_w = (max_dist - mind) * wrong
+    nc, nw = inv_c.argmax(axis=1), inv_w.argmax(axis=1)
+    cluster = (max_dist - inv_c[np.arange(B), nc]).mean()                    # :47-48
+    separation = (max_dist - inv_w[np.arange(B), nw]).mean()                 # :51-54
+    l1_mask = 1 - ident.T                                                    # :62
+    l1 = np.abs(W64 * l1_mask).sum()
+    w_ce, w_cl, w_sep, w_l1 = coefs
+    loss = w_ce * ce + w_cl * cluster + w_sep * separation + w_l1 * l1
+    # backward
+    dlogits = np.exp(logp)
+    dlogits[np.arange(B), label] -= 1
+    dlogits *= w_ce / B
+    dW = dlogits.T @ act + w_l1 * np.sign(W64) * l1_mask
+    dmind = (dlogits @ W64) * (1 / (mind + 1) - 1 / (mind + eps))
+    dmind[np.arange(B), nc] += w_cl / B * correct[np.arange(B), nc]          # d(max_dist - (max_dist - m)) = dm
+    dmind[np.arange(B), nw] += w_sep / B * wrong[np.arange(B), nw]
+    gate = np.take_along_axis(pre, amin[:, :, None], axis=2)[:, :, 0] > 0    # relu, model.py:218
+    g = np.where(gate, dmind, 0.0)
+    dz = np.zeros_like(zf)
+    dP = np.zeros_like(P64)
+    for b in range(B):
+        for n in range(N):
+            diff = zf[b, :, amin[b, n]] - P64[n]
+            dz[b, :, amin[b, n]] += 2 * g[b, n] * diff
+            dP[n] -= 2 * g[b, n] * diff
+    return dict(loss=loss, cross_entropy=ce, cluster=cluster, separation=separation, l1=l1, logits=logits,
+                min_distances=mind, argmin=amin, dmind=dmind, dz=dz.reshape(z.shape), dP=dP, dW=dW)

@@ -183,3 +183,35 @@ def test_pil_nearest_lut_is_what_pillow_does():
         cc = np.asarray(Image.fromarray(cols).resize((w, h), resample=Image.NEAREST))[0, :]
         for f in (orc.pil_nearest_lut, nearest.pil_nearest_lut):
             assert np.array_equal(rr, f(H, h)) and np.array_equal(cc, f(W, w)), (H, W, h, w)
+
+
+# ------------------------------------------------------------------ legacy min-pool branch
+def test_min_pool_forward_matches_reference(golden):
+    g = golden("minpool_small_A")
+    logits, mind, amin = orc.min_pool_forward(g["z"], g["P"], g["W"])
+    assert np.array_equal(amin, g["argmin"])
+    assert np.abs(mind - g["min_distances"]).max() <= dist_tol(g["z"], g["P"])
+    assert np.allclose(logits, g["logits"], rtol=1e-4, atol=1e-4)
+
+
+def test_min_pool_step_matches_reference(golden):
+    """train_and_test._train_or_test on one batch: loss terms and the three gradients (float64 restatement)"""
+    g = golden("minpool_small_A")
+    r = orc.min_pool_step(g["z"], g["P"], g["W"], g["label"])
+    for key in ("cross_entropy", "cluster", "separation"):
+        assert abs(r[key] - float(g[key])) <= 2e-6 * max(1.0, abs(float(g[key]))), key
+    for key in ("dz", "dP", "dW"):
+        assert np.abs(r[key] - g[key]).max() <= 1e-5 * np.abs(g[key]).max(), key
+    assert np.array_equal(r["argmin"], g["argmin"])
+
+
+def test_min_pool_step_post_push_regime(golden):
+    """regime B: many minima are exactly 0, where log((d+1)/(d+eps)) amplifies the reference's own fp32 cancellation
+    noise by 1/eps; positions and the well-conditioned terms must still agree"""
+    g = golden("minpool_small_B")
+    r = orc.min_pool_step(g["z"], g["P"], g["W"], g["label"])
+    assert np.array_equal(r["argmin"], g["argmin"])
+    assert np.abs(r["min_distances"] - g["min_distances"]).max() <= dist_tol(g["z"], g["P"])
+    assert abs(r["cluster"] - float(g["cluster"])) <= 1e-5 and abs(r["separation"] - float(g["separation"])) <= 1e-5
+    for key in ("dz", "dP", "dW"):
+        assert np.abs(r[key] - g[key]).max() <= 5e-2 * np.abs(g[key]).max(), key
