@@ -130,7 +130,7 @@ def check(rc, what):
     raise AdlmError(msg)
 
 
-K_HEAD_FWD, K_HEAD_BWD, K_PUSH_SCAN, K_PATCH_MASK = 1, 2, 3, 4
+K_HEAD_FWD, K_HEAD_BWD, K_PUSH_SCAN, K_PATCH_MASK, K_KLD, K_STEP_PREPARE = 1, 2, 3, 4, 5, 6
 
 
 class kernel_timing:

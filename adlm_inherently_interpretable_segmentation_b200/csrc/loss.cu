@@ -67,9 +67,9 @@ __global__ void k_ce(const float* __restrict__ logits, const int32_t* __restrict
 // A[a][b] = E_a[d_b], the pair terms, and — same CTA, which owns exactly these pixels — dL/d(own distances)
 // for the backward kernels.  Thread = (pixel lane tid/16, prototype-in-class tid%16): ~50 registers, so all
 // B*C CTAs are resident at once.
-constexpr int KLD_THREADS = 512, KLD_PL = KLD_THREADS / 16, KLD_WARPS = KLD_THREADS / 32;
+constexpr int KLD_THREADS = 512, KLD_PL = KLD_THREADS / 16, KLD_WARPS = KLD_THREADS / 32, KLD_U = 8;
 
-__global__ void __launch_bounds__(KLD_THREADS)
+__global__ void __launch_bounds__(KLD_THREADS, 2)
 k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const int* __restrict__ hist,
       const int* __restrict__ cls_count, const int* __restrict__ counts, int HW, int C,
       float coef /* w_kld * grad_scale */, float* __restrict__ own_grad, double* __restrict__ accum) {
@@ -85,12 +85,36 @@ k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const i
   __shared__ float s_T[JMAX][JMAX];
   __shared__ float s_red[KLD_WARPS][JMAX];
   __shared__ float s_kl[JMAX][JMAX];
+  __shared__ float s_part[KLD_WARPS * (JMAX + 1) * JMAX];   // per-warp partial sums of pass B
   const int32_t* t = target + (size_t)b * HW;
   const float* ob = own + (size_t)b * HW * JMAX;
-  if (tid == 0) s_n = 0;
-  __syncthreads();
+  // Compaction without atomics: every warp counts its hits (labels are re-read from L1 in the second sweep), a
+  // 16-entry prefix gives each warp its base, and the ballots place the indices.  (One shared-memory atomicAdd
+  // with a returned value per ballot — 16 warps x 12 dependent same-address atomics at h*w = 4225 — cost more
+  // than the three passes over the distances together.)
+  __shared__ int s_wcnt[KLD_WARPS];
+  const int wid = tid >> 5;
+  int mine = 0;
   for (int p0 = 0; p0 < HW; p0 += 4 * KLD_THREADS) {
-    // four label loads in flight per thread; order inside the list is irrelevant
+    int lab[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int pp = p0 + u * KLD_THREADS + tid;
+      lab[u] = pp < HW ? t[pp] : -1;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) mine += __popc(__ballot_sync(0xffffffffu, lab[u] == l));
+  }
+  if (lane == 0) s_wcnt[wid] = mine;              // warp-uniform
+  __syncthreads();
+  int base = 0, total = 0;
+#pragma unroll
+  for (int w = 0; w < KLD_WARPS; ++w) {
+    const int c = s_wcnt[w];
+    base += w < wid ? c : 0;
+    total += c;
+  }
+  for (int p0 = 0; p0 < HW; p0 += 4 * KLD_THREADS) {
     int pp[4];
     bool hit[4];
 #pragma unroll
@@ -101,12 +125,11 @@ k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const i
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const unsigned bal = __ballot_sync(0xffffffffu, hit[u]);
-      int base = 0;
-      if (lane == 0 && bal) base = atomicAdd(&s_n, __popc(bal));
-      base = __shfl_sync(0xffffffffu, base, 0);
       if (hit[u]) s_list[base + __popc(bal & ((1u << lane) - 1u))] = pp[u];
+      base += __popc(bal);
     }
   }
+  if (tid == 0) s_n = total;
   __syncthreads();
   const int n = s_n;                              // == cnt
   const bool valid_group = J >= 2 && n >= 2;
@@ -116,13 +139,22 @@ k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const i
       for (int i = pl; i < n; i += KLD_PL) og[(size_t)s_list[i] * JMAX + j] = 0.f;
     return;
   }
+  // The three passes over the group's pixels are chains of gathers from L2; each batches KLD_U pixel iterations so
+  // that a thread has KLD_U independent loads in flight instead of one round trip per iteration.
   // pass A: per-prototype max over the group's pixels
   float mx = -INFINITY;
-  for (int i = pl; i < n; i += KLD_PL) mx = fmaxf(mx, ob[(size_t)s_list[i] * JMAX + j]);
+  for (int i0 = pl; i0 < n; i0 += KLD_PL * KLD_U) {
+    float v[KLD_U];
+#pragma unroll
+    for (int u = 0; u < KLD_U; ++u) {
+      const int i = i0 + u * KLD_PL;
+      v[u] = i < n ? ob[(size_t)s_list[i] * JMAX + j] : -INFINITY;
+    }
+#pragma unroll
+    for (int u = 0; u < KLD_U; ++u) mx = fmaxf(mx, v[u]);
+  }
   mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
   if (lane < 16) s_red[tid >> 5][j] = mx;
-  if (tid < JMAX * JMAX) s_T[pl][j] = 0.f;
-  if (tid < JMAX) s_S[tid] = 0.f;
   __syncthreads();
   if (tid < JMAX) {
     float m = s_red[0][tid];
@@ -130,35 +162,56 @@ k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const i
     s_mx[tid] = m;
   }
   __syncthreads();
-  // pass B: S_j = sum exp(d_j - mx_j), T[j][c] = sum exp(d_j - mx_j) d_c
+  // pass B: S_j = sum exp(d_j - mx_j), T[j][c] = sum exp(d_j - mx_j) d_c; per-warp partials go through
+  // s_part[warp][c][j] (conflict-free, no atomics) and are summed by 16 x 17 threads
   {
     const float mxj = s_mx[j];
     float S = 0.f, T[JMAX];
 #pragma unroll
     for (int c = 0; c < JMAX; ++c) T[c] = 0.f;
-    for (int i = pl; i < n; i += KLD_PL) {
-      const float* row = ob + (size_t)s_list[i] * JMAX;
-      const float dj = row[j];
-      const float4* o4 = reinterpret_cast<const float4*>(row);
-      float d[JMAX];
+    constexpr int UB = 2;
+    for (int i0 = pl; i0 < n; i0 += KLD_PL * UB) {
+      float4 x[UB][JMAX / 4];
+      float dj[UB];
 #pragma unroll
-      for (int v = 0; v < JMAX / 4; ++v) {
-        const float4 x = o4[v];
-        d[4 * v] = x.x; d[4 * v + 1] = x.y; d[4 * v + 2] = x.z; d[4 * v + 3] = x.w;
+      for (int u = 0; u < UB; ++u) {
+        const int i = i0 + u * KLD_PL;
+        const float* row = ob + (size_t)s_list[i < n ? i : 0] * JMAX;
+        dj[u] = i < n ? row[j] : -INFINITY;
+        const float4* o4 = reinterpret_cast<const float4*>(row);
+#pragma unroll
+        for (int v = 0; v < JMAX / 4; ++v) x[u][v] = o4[v];
       }
-      const float e = (j < J) ? __expf(dj - mxj) : 0.f;
-      S += e;
 #pragma unroll
-      for (int c = 0; c < JMAX; ++c) T[c] = fmaf(e, d[c], T[c]);
+      for (int u = 0; u < UB; ++u) {
+        const float e = (j < J) ? __expf(dj[u] - mxj) : 0.f;      // exp(-inf) = 0 for the padding iterations
+        S += e;
+#pragma unroll
+        for (int v = 0; v < JMAX / 4; ++v) {
+          T[4 * v] = fmaf(e, x[u][v].x, T[4 * v]);
+          T[4 * v + 1] = fmaf(e, x[u][v].y, T[4 * v + 1]);
+          T[4 * v + 2] = fmaf(e, x[u][v].z, T[4 * v + 2]);
+          T[4 * v + 3] = fmaf(e, x[u][v].w, T[4 * v + 3]);
+        }
+      }
     }
     S += __shfl_xor_sync(0xffffffffu, S, 16);
 #pragma unroll
     for (int c = 0; c < JMAX; ++c) T[c] += __shfl_xor_sync(0xffffffffu, T[c], 16);
-    if (lane < 16 && j < J) {
-      atomicAdd(&s_S[j], S);
+    if (lane < 16) {
+      float* part = s_part + (size_t)(tid >> 5) * (JMAX + 1) * JMAX;
 #pragma unroll
-      for (int c = 0; c < JMAX; ++c) atomicAdd(&s_T[j][c], T[c]);
+      for (int c = 0; c < JMAX; ++c) part[c * JMAX + j] = T[c];
+      part[JMAX * JMAX + j] = S;
     }
+  }
+  __syncthreads();
+  if (tid < (JMAX + 1) * JMAX) {
+    float a = 0.f;
+#pragma unroll
+    for (int w = 0; w < KLD_WARPS; ++w) a += s_part[(size_t)w * (JMAX + 1) * JMAX + tid];
+    const int c = tid / JMAX, jj = tid % JMAX;
+    if (c < JMAX) s_T[jj][c] = a; else s_S[jj] = a;
   }
   __syncthreads();
   if (tid < JMAX * JMAX) {
@@ -204,22 +257,32 @@ k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const i
 #pragma unroll
     for (int c = 0; c < JMAX; ++c) kl[c] = s_kl[j][c];   // zero for c >= J, c == a, a >= J
     const float csa = s_cs[j], ra = s_r[j], lsea = s_lse[j];
-    for (int i0 = 0; i0 < n; i0 += KLD_PL) {
-      const int i = i0 + pl;
-      const bool act = i < n;
-      const int pidx = s_list[act ? i : 0];
-      const float da = ob[(size_t)pidx * JMAX + j];
-      const float qa = (j < J) ? __expf(da - lsea) : 0.f;
-      float cd = 0.f, cq = 0.f;
+    constexpr int UG = 4;
+    for (int i0 = 0; i0 < n; i0 += KLD_PL * UG) {
+      int pidx[UG];
+      float dav[UG];
 #pragma unroll
-      for (int c = 0; c < JMAX; ++c) {
-        const float dc = __shfl_sync(0xffffffffu, da, c, 16);
-        const float qc = __shfl_sync(0xffffffffu, qa, c, 16);
-        cd = fmaf(kl[c], dc, cd);
-        cq = fmaf(kl[c], qc, cq);
+      for (int u = 0; u < UG; ++u) {
+        const int i = i0 + u * KLD_PL + pl;
+        pidx[u] = s_list[i < n ? i : 0];
+        dav[u] = ob[(size_t)pidx[u] * JMAX + j];
       }
-      const float ga = qa * (da * csa - cd - ra) + qa * csa - cq;
-      if (act) og[(size_t)pidx * JMAX + j] = ga;
+#pragma unroll
+      for (int u = 0; u < UG; ++u) {
+        const bool act = i0 + u * KLD_PL + pl < n;
+        const float da = dav[u];
+        const float qa = (j < J) ? __expf(da - lsea) : 0.f;
+        float cd = 0.f, cq = 0.f;
+#pragma unroll
+        for (int c = 0; c < JMAX; ++c) {
+          const float dc = __shfl_sync(0xffffffffu, da, c, 16);
+          const float qc = __shfl_sync(0xffffffffu, qa, c, 16);
+          cd = fmaf(kl[c], dc, cd);
+          cq = fmaf(kl[c], qc, cq);
+        }
+        const float ga = qa * (da * csa - cd - ra) + qa * csa - cq;
+        if (act) og[(size_t)pidx[u] * JMAX + j] = ga;
+      }
     }
   }
 }
@@ -433,6 +496,7 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
       cm = *comm;
       lay = dp_layout(s.K, N, C, cm.world);
     }
+    KernelTimer timer(ADLM_K_STEP_PREPARE, st);
     k_step_prepare<<<B, 1024, 0, st>>>(target, proto_class, B, HW, C, N, ignore_void, slot, ws.hist, ws.cls_count,
                                        ws.counts, ws.rank, ws.accum, cm, lay);
     ADLM_LAUNCH_CHECK();
@@ -473,6 +537,7 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
     dim3 grid(C, B);
     ADLM_CHECK_SUPPORTED((size_t)HW * sizeof(int) <= 200 * 1024, "feature map too large for the KLD kernel (h*w > 51200)");
     ADLM_CUDA(cudaFuncSetAttribute(k_kld, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)HW * sizeof(int))));
+    KernelTimer timer(ADLM_K_KLD, st);
     k_kld<<<grid, KLD_THREADS, (size_t)HW * sizeof(int), st>>>(ws.own, target, ws.hist, ws.cls_count, counts, HW, C,
                                                     w_kld * grad_scale, want_grad ? ws.own_grad : nullptr, ws.accum);
     ADLM_LAUNCH_CHECK();

@@ -424,8 +424,13 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
   if (warp < 8) {
     // one-time operands, staged by the eight epilogue warps only: the builder warps have their loads in flight
     // and the MMA warp is allocating TMEM
-    stage_rows_kmajor<KP, false, 4>(PkA, PkA, p.P, N, K, Npad2, CENTRE, tid, 256);
-    stage_wt_kmajor(WtA, p.W, C, N, C8, Npad2, 1.f, has_dl, tid, 256);
+    constexpr int PB = Npad2 * (KP / 4) / 256, WB = 4 * NB;      // C8 <= 32: (C8 / 4) * Npad2 <= WB * 256
+    if (K == KP && (reinterpret_cast<uintptr_t>(p.P) & 15u) == 0 && PB <= 16) {
+      stage_rows_and_wt_once<KP, (PB <= 16 ? PB : 1), WB>(PkA, WtA, p.P, p.W, N, C, C8, Npad2, CENTRE, has_dl, tid, 256);
+    } else {
+      stage_rows_kmajor<KP, false, 4>(PkA, PkA, p.P, N, K, Npad2, CENTRE, tid, 256);
+      stage_wt_kmajor(WtA, p.W, C, N, C8, Npad2, 1.f, has_dl, tid, 256);
+    }
     smem_zero4(dLtB, 32 * TILE / 4, tid, 256);
   }
   fence_async_smem();

@@ -245,6 +245,58 @@ __device__ __forceinline__ void stage_wt_kmajor(float* __restrict__ dst, const f
   }
 }
 
+// stage_rows_kmajor + stage_wt_kmajor with EVERY global load of both in flight before the first conversion: one
+// global latency for the one-time operands instead of one per batch (the dP/dW kernel spent 17 k cycles here in six
+// batches).  PB * nthreads float4 cover P, WB * nthreads quads cover W^T; the caller checks the fast-path
+// conditions (K == KP, 16-byte aligned P) and the capacities, else it calls the two functions above.
+template <int KP, int PB, int WB>
+__device__ __forceinline__ void stage_rows_and_wt_once(float* __restrict__ pk, float* __restrict__ wt,
+                                                       const float* __restrict__ P, const float* __restrict__ W,
+                                                       int N, int C, int C8, int rows_pad, float centre,
+                                                       bool valid_w, int tid, int nthreads) {
+  constexpr int Q = KP / 4;
+  const int total_p = rows_pad * Q, total_w = (C8 >> 2) * rows_pad;
+  const int n8 = rows_pad >> 3;
+  const float4* src4 = reinterpret_cast<const float4*>(P);
+  float wv[WB][4];
+  float4 pv[PB];
+#pragma unroll
+  for (int u = 0; u < WB; ++u) {
+    const int f = u * nthreads + tid;
+    const int c4 = f / rows_pad, n = f - c4 * rows_pad;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = c4 * 4 + j;
+      wv[u][j] = (valid_w && f < total_w && c < C && n < N) ? __ldg(W + (size_t)c * N + n) : 0.f;
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < PB; ++u) {
+    const int f = u * nthreads + tid;
+    const int g = f >> 5, l = f & 31;                         // group of 32 = 8 rows x 4 column groups
+    const int k4 = (g / n8) * 4 + (l >> 3), n = (g % n8) * 8 + (l & 7);
+    pv[u] = (f < total_p && n < N) ? __ldg(src4 + (size_t)n * Q + k4) : make_float4(centre, centre, centre, centre);
+  }
+#pragma unroll
+  for (int u = 0; u < WB; ++u) {
+    const int f = u * nthreads + tid;
+    if (f < total_w)
+      *reinterpret_cast<float4*>(wt + (size_t)f * 4) =
+          make_float4(rna_tf32_mask(wv[u][0]), rna_tf32_mask(wv[u][1]), rna_tf32_mask(wv[u][2]), rna_tf32_mask(wv[u][3]));
+  }
+#pragma unroll
+  for (int u = 0; u < PB; ++u) {
+    const int f = u * nthreads + tid;
+    if (f < total_p) {
+      const int g = f >> 5, li = f & 31;
+      const size_t o = ((size_t)((g / n8) * 4 + (li >> 3)) * rows_pad + (g % n8) * 8 + (li & 7)) * 4;
+      *reinterpret_cast<float4*>(pk + o) =
+          make_float4(rna_tf32_mask(pv[u].x - centre), rna_tf32_mask(pv[u].y - centre),
+                      rna_tf32_mask(pv[u].z - centre), rna_tf32_mask(pv[u].w - centre));
+    }
+  }
+}
+
 // Stage W [C x N] as a K-major operand with rows = classes c, K index = prototype n: [Npad/4][Cpad][4];
 // value = rna(scale * W[c][n]), zero beyond C / N.  A warp covers 8 classes x 4 prototype quads: conflict-free
 // 16-byte shared-memory stores, 64 contiguous bytes per class row on the global side.

@@ -79,7 +79,7 @@ constexpr int B_SFREE = 3;       // [3] MMAs reading the stage are done (commit)
 constexpr int B_AFULL = 6;       // [2] accumulator of block ready (commit)
 constexpr int B_AEMPTY = 8;      // [2] accumulator of block drained (epilogue warps of the block)
 constexpr int B_META = 10;       // [2] |z|^2 / mask slot written (256 producer threads)
-constexpr int B_MEMPTY = 12;     // [2] |z|^2 / mask slot drained (all 224 epilogue threads)
+constexpr int B_MEMPTY = 12;     // [2] |z|^2 / mask slot drained (the 128 or 224 epilogue threads that own a block)
 
 template <int KP, bool X3, int NB>
 __global__ void __launch_bounds__(PUSH_THREADS, 1) k_tc_push(const TcPushParams p) {
@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(PUSH_THREADS, 1) k_tc_push(const TcPushParams 
       mbar_init(smem_u32(&bars[B_AFULL + i]), 1);
       mbar_init(smem_u32(&bars[B_AEMPTY + i]), i == 0 ? 128 : 96);
       mbar_init(smem_u32(&bars[B_META + i]), 256);
-      mbar_init(smem_u32(&bars[B_MEMPTY + i]), 224);
+      mbar_init(smem_u32(&bars[B_MEMPTY + i]), NB == 2 ? 224 : 128);   // the epilogue threads that have a block
     }
     mbar_init_fence();
   }
@@ -311,6 +311,10 @@ __global__ void __launch_bounds__(PUSH_THREADS, 1) k_tc_push(const TcPushParams 
           cur_img = img;
         }
       }
+      // Warps without a prototype block (NB == 1: warps 4-6) take no part in the slot hand-shake.  They used to
+      // arrive on B_MEMPTY without waiting for anything, ran ahead, and their arrivals for a LATER tile completed
+      // the current phase early: with N <= 128 and three or more tiles per CTA the producer then overwrote a
+      // |z|^2 / class table that warp 0 was still reading (wrong minima; caught by the per-image scan test).
       if (blk < NB) {
         mbar_wait(bar(B_META + a), (uint32_t)j & 1u);
         mbar_wait(bar(B_AFULL + blk), (uint32_t)it & 1u);
@@ -347,8 +351,8 @@ __global__ void __launch_bounds__(PUSH_THREADS, 1) k_tc_push(const TcPushParams 
         }
         fence_before();
         mbar_arrive(bar(B_AEMPTY + blk));
+        mbar_arrive(bar(B_MEMPTY + a));
       }
-      mbar_arrive(bar(B_MEMPTY + a));
     }
     // padding columns of a partly empty tile carry mask 0 and never win
     flush();

@@ -93,6 +93,8 @@ ADLM_API unsigned long long adlm_launch_count(void);
 #define ADLM_K_HEAD_BWD 2
 #define ADLM_K_PUSH_SCAN 3
 #define ADLM_K_PATCH_MASK 4
+#define ADLM_K_KLD 5
+#define ADLM_K_STEP_PREPARE 6
 ADLM_API int adlm_timing_begin(int kernel_tag, int max_samples);
 ADLM_API int adlm_timing_end(float* ms_out);
 

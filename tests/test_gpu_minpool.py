@@ -148,7 +148,15 @@ def test_per_image_scan_equals_image_by_image_launches(prec, n, h, w, N):
             rc = lib.adlm_push_scan(_lib.ptr(z[i]), 1, K, h * w, _lib.ptr(mk_ref[i]), _lib.ptr(P), N,
                                     _lib.ptr(cls_ref), c_longlong(0), c_int(p), _lib.ptr(ref[i]), _lib.stream_ptr())
             _lib.check(rc, "adlm_push_scan")
-        assert torch.equal(one, ref), (prec, n, h, w, N, mk is None)
+        # distances must agree bit for bit.  The patch may differ only in a rounding tie: the running minimum inside
+        # a CTA compares t = |z|^2 - 2 z.p (before |p|^2 is added), CTAs merge on the rounded d = t + |p|^2, so two
+        # patches whose d round to the same float resolve by visiting order in one case and by patch id in the other
+        assert torch.equal(one >> 32, ref >> 32), (prec, n, h, w, N, mk is None)
+        differ = (one != ref)
+        assert differ.float().mean().item() <= 1e-3, (prec, n, h, w, N, mk is None, int(differ.sum()))
+        if differ.any():
+            print(f"per-image scan: {int(differ.sum())} rounding ties of {one.numel()} resolved to another patch "
+                  f"({prec}, n={n}, {h}x{w}, N={N})")
     assert (one != _lib.PUSH_NONE).all()
 
 

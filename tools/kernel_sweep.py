@@ -58,7 +58,8 @@ def main():
             ms = ev_time(fn, a.reps)
             print(f"B={B:4d} M={M:8d} {name:5s} {ms * 1e3:9.1f} us  {M / ms / 1e3:8.1f} Mpix/s  {nbytes / ms / 1e6:7.1f} GB/s(alg)",
                   flush=True)
-        for tag, nm in ((_lib.K_HEAD_FWD, "k_fwd"), (_lib.K_HEAD_BWD, "k_bwd")):
+        for tag, nm in ((_lib.K_STEP_PREPARE, "k_prepare"), (_lib.K_HEAD_FWD, "k_fwd"), (_lib.K_KLD, "k_kld"),
+                        (_lib.K_HEAD_BWD, "k_bwd")):
             with _lib.kernel_timing(tag, 64) as t:
                 for _ in range(5):
                     step()
