@@ -324,12 +324,46 @@ k_step_prepare(const int32_t* __restrict__ target, const int32_t* __restrict__ p
   __shared__ int s_cls[ADLM_MAX_C];
   __shared__ int s_valid, s_terms, s_last;
   const int tid = threadIdx.x, b = blockIdx.x;
+  // Everything that depends on the prototype classes only (class sizes for every CTA, ranks by CTA 0) runs while the
+  // label loads are in flight, not in the tail of the last CTA.
+  __shared__ int s_pc[1024];
   for (int i = tid; i <= C; i += 1024) sh[i] = 0;
-  __syncthreads();
+  for (int c = tid; c < C; c += 1024) s_cls[c] = 0;
+  if (tid == 0) { s_valid = 0; s_terms = 0; }
   const int32_t* t = target + (size_t)b * HW;
-  for (int p = tid; p < HW; p += 1024) {
+  constexpr int LB = 8;                           // label loads in flight per thread
+  int lab[LB];
+#pragma unroll
+  for (int u = 0; u < LB; ++u) {
+    const int p = u * 1024 + tid;
+    lab[u] = p < HW ? t[p] : -1;
+  }
+  const int pc0 = tid < N ? proto_class[tid] : -2;
+  __syncthreads();
+#pragma unroll
+  for (int u = 0; u < LB; ++u)
+    if (lab[u] >= 0 && lab[u] <= C) atomicAdd(&sh[lab[u]], 1);
+  for (int p = LB * 1024 + tid; p < HW; p += 1024) {
     const int l = t[p];
     if (l >= 0 && l <= C) atomicAdd(&sh[l], 1);
+  }
+  // class sizes (every CTA: the last one needs them) and the rank of a prototype inside its class (CTA 0)
+  for (int n0 = 0; n0 < N; n0 += 1024) {
+    const int n = n0 + tid;
+    const int c = n0 == 0 ? pc0 : (n < N ? proto_class[n] : -2);
+    if (n0 > 0) __syncthreads();
+    s_pc[tid] = c;
+    __syncthreads();
+    if (n < N) {
+      if (c >= 0 && c < C) atomicAdd(&s_cls[c], 1);
+      if (b == 0) {
+        int r = 0;
+        for (int i = 0; i < tid; ++i) r += (s_pc[i] == c);
+        if (n0 > 0)
+          for (int i = 0; i < n0; ++i) r += (proto_class[i] == c);
+        rank[n] = r;
+      }
+    }
   }
   __syncthreads();
   for (int i = tid; i <= C; i += 1024) hist[b * (C + 1) + i] = sh[i];
@@ -343,27 +377,6 @@ k_step_prepare(const int32_t* __restrict__ target, const int32_t* __restrict__ p
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  for (int c = tid; c < C; c += 1024) s_cls[c] = 0;
-  if (tid == 0) { s_valid = 0; s_terms = 0; }
-  __syncthreads();
-  // rank of a prototype inside its class: one warp-ballot pass per 32 candidates over a shared copy
-  __shared__ int s_pc[1024];
-  for (int n0 = 0; n0 < N; n0 += 1024) {
-    const int n = n0 + tid;
-    const int c = n < N ? proto_class[n] : -2;
-    __syncthreads();
-    s_pc[tid] = c;
-    __syncthreads();
-    if (n < N) {
-      if (c >= 0 && c < C) atomicAdd(&s_cls[c], 1);
-      int r = 0;
-      for (int i = 0; i < tid; ++i) r += (s_pc[i] == c);
-      if (n0 > 0)
-        for (int i = 0; i < n0; ++i) r += (proto_class[i] == c);
-      rank[n] = r;
-    }
-  }
-  __syncthreads();
   int valid = 0, terms = 0;
   const volatile int* vh = hist;
   for (int i = tid; i < B * (C + 1); i += 1024) {

@@ -11,4 +11,6 @@ timeout 400 ncu --set full --clock-control none --import-source on -k regex:'k_t
 timeout 400 ncu --set full --clock-control none --import-source on -k regex:'k_tc_push|k_patch_class_mask' -c 4 -o $O/r1_push_full -f python tools/push_once.py 64 tf32x3 > $O/ncu_p.log 2>&1
 timeout 200 python tools/sigmoid_fusion_bench.py > $O/r1_sigmoid_fusion.log 2>&1
 (echo '# python tools/eval_bench.py (B200, 4 images, CUDA events)'; timeout 300 python tools/eval_bench.py) > $O/r1_eval_upsample.log 2>&1
+(echo '# python tools/nearest_bench.py 64 (B200)'; timeout 300 python tools/nearest_bench.py 64) > $O/r1_k_nearest.log 2>&1
+(echo '# python tools/minpool_bench.py 16 (B200)'; timeout 300 python tools/minpool_bench.py 16) > $O/r1_min_pool.log 2>&1
 ls -la $O | tail -24

@@ -35,9 +35,12 @@ def main():
     ap.add_argument("--batches", default="16,64,256")
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--once", action="store_true", help="one call of each phase at the first batch size (for ncu)")
+    ap.add_argument("--protos", default="190,19", help="N,C: 190,19 = Cityscapes (cfg2), 30,3 = mds_new pancreas (cfg4)")
+    ap.add_argument("--infer", action="store_true", help="inference only: logits + per-pixel argmax (cfg4)")
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
-    K, h, w, N, C = 64, 65, 65, 190, 19
+    K, h, w = 64, 65, 65
+    N, C = [int(x) for x in a.protos.split(",")]
     _, Pn, Wn = synth.head_inputs(1, K, 2, 2, N, C, w_noise=0.1, seed=synth.BASE_SEED)
     P, W = torch.from_numpy(Pn).to(dev), torch.from_numpy(Wn).to(dev)
     pc = torch.arange(N, dtype=torch.int32, device=dev) // (N // C)
@@ -54,10 +57,14 @@ def main():
             fwd(); bwd(); step()
             torch.cuda.synchronize()
             return
-        for name, fn, nbytes in (("fwd", fwd, 332 * M), ("bwd", bwd, 588 * M), ("step", step, 920 * M)):
+        fb, bb = 4 * K + 4 * C + (4 if a.infer else 0), 8 * K + 4 * C   # algorithmic bytes / pixel (+4: argmax)
+        phases = (("fwd", fwd, fb * M),) if a.infer else (("fwd", fwd, fb * M), ("bwd", bwd, bb * M), ("step", step, (fb + bb) * M))
+        for name, fn, nbytes in phases:
             ms = ev_time(fn, a.reps)
             print(f"B={B:4d} M={M:8d} {name:5s} {ms * 1e3:9.1f} us  {M / ms / 1e3:8.1f} Mpix/s  {nbytes / ms / 1e6:7.1f} GB/s(alg)",
                   flush=True)
+        if a.infer:
+            continue
         for tag, nm in ((_lib.K_STEP_PREPARE, "k_prepare"), (_lib.K_HEAD_FWD, "k_fwd"), (_lib.K_KLD, "k_kld"),
                         (_lib.K_HEAD_BWD, "k_bwd")):
             with _lib.kernel_timing(tag, 64) as t:
