@@ -3,6 +3,7 @@
 // caller's stream.
 #include <atomic>
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -18,6 +19,10 @@ void set_error(const char* fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+}
+bool sync_launches() {
+  static const bool on = [] { const char* v = getenv("ADLM_SYNC_LAUNCHES"); return v != nullptr && v[0] == '1'; }();
+  return on;
 }
 void count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 

@@ -10,6 +10,7 @@ namespace adlm {
 
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
+bool sync_launches();
 
 #define ADLM_CHECK_ARG(cond, msg)                                   \
   do {                                                              \
@@ -37,10 +38,13 @@ void count_launch(int n = 1);
     }                                                                                \
   } while (0)
 
+// ADLM_SYNC_LAUNCHES=1 in the environment makes every launch synchronous, so that a device fault is reported
+// with the file:line of the kernel that raised it (debugging aid; never set for measurements)
 #define ADLM_LAUNCH_CHECK()                                                          \
   do {                                                                               \
     adlm::count_launch();                                                            \
     cudaError_t e__ = cudaGetLastError();                                            \
+    if (e__ == cudaSuccess && adlm::sync_launches()) e__ = cudaDeviceSynchronize();  \
     if (e__ != cudaSuccess) {                                                        \
       adlm::set_error("%s:%d launch -> %s", __FILE__, __LINE__,                      \
                       cudaGetErrorString(e__));                                      \

@@ -373,7 +373,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
   uint32_t* clsm = reinterpret_cast<uint32_t*>(misc + 3072);         // [slot][32 classes][4 words]: pixels of the tile
   float* css = reinterpret_cast<float*>(misc + 4096);                // [half][blk][128]
   uint64_t* bars = reinterpret_cast<uint64_t*>(misc + 4096 + 2048);
-  uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 8);     // seven barriers, then the TMEM base
+  uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 8);     // eight barriers, then the TMEM base
   float* ogs = reinterpret_cast<float*>(smem + L::ogs(Npad2, C8));   // [slot][128 px][16]: dL/d(own distances)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -390,6 +390,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
     mbar_init(smem_u32(&bars[4]), 256);   // gs[b]: G and S of the unit written back to TMEM buffer b
     mbar_init(smem_u32(&bars[5]), 256);
     mbar_init(smem_u32(&bars[6]), 128);   // full_t: transposed pixel operands (accumulate MMAs) written
+    mbar_init(smem_u32(&bars[7]), 1);     // k_free: the tile's last distance MMA has read ZkB / dLkB (one completion per tile)
     mbar_init_fence();
   }
   // the builder warps fetch their first tile before the one-time operand staging
@@ -451,7 +452,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
   // and the metadata as soon as the previous tile's last distance MMA has retired (they are consumed two units
   // ahead of the epilogue), the transposed operands once the previous tile's accumulate MMAs are done.
   const uint32_t bar_full = smem_u32(&bars[0]), bar_free = smem_u32(&bars[1]), bar_acc0 = smem_u32(&bars[2]),
-                 bar_gs0 = smem_u32(&bars[4]), bar_full_t = smem_u32(&bars[6]);
+                 bar_gs0 = smem_u32(&bars[4]), bar_full_t = smem_u32(&bars[6]), bar_kfree = smem_u32(&bars[7]);
 
   if (is_builder) {
     prefetch(0);
@@ -463,14 +464,13 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
       uint32_t* clsm_s = clsm + slot * 128;
       float* ogs_s = ogs + slot * 128 * JMAX;
       if (warp == 8) DP_PHASE(0, 1 + it * 8);
-      // ---- step K: wait until the last distance MMA of the previous tile has read ZkB / dLkB, i.e. for
-      //      completion number it * NU/2 of acc[1].  A parity wait only tells consecutive phases apart, so every
-      //      completion of the previous tile is observed in order (the next one after them needs this step's
-      //      full_k, so the barrier cannot run ahead of this thread).
-      if (it > 0) {
-#pragma unroll
-        for (int c = 0; c < NU / 2; ++c) mbar_wait(bar_acc0 + 8, (uint32_t)((it - 1) * (NU / 2) + c) & 1u);
-      }
+      // ---- step K: wait until the last distance MMA of the previous tile has read ZkB / dLkB.  k_free completes
+      //      ONCE per tile and its next completion needs this step's full_k, so a parity wait cannot alias however
+      //      late this thread arrives.  (The first version waited for the two per-tile completions of acc[1] in
+      //      order; a builder held up in the prefetch of the next tile for longer than two epilogue units — HBM
+      //      misses at B = 256 on some boxes — found both already done, the wait for the first one then matched the
+      //      parity of the NEXT phase and the CTA dead-locked until mbar_wait's watchdog trapped.)
+      if (it > 0) mbar_wait(bar_kfree, (uint32_t)(it - 1) & 1u);
       if (warp == 8) DP_PHASE(0, 2 + it * 8);
       clsm_s[cw] = 0u;
       if (kld && valid) {
@@ -545,6 +545,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
           mma_ss(tDb(b) + UW, make_desc(w0 + ks * 2 * Npad2 * 16, Npad2 * 16, 128), make_desc(l0 + ks * 2 * TILE * 16, TILE * 16, 128),
                  idesc_t, ks > 0 ? 1u : 0u);
         mma_commit(bar_acc0 + b * 8);
+        if (j == NU - 1) mma_commit(bar_kfree);
       };
       uint32_t gcnt[2] = {0u, 0u};
       mbar_wait(bar_full, 0u);
@@ -801,14 +802,23 @@ k_reduce_partials(const float* __restrict__ partials, int n_parts, int Npad2, in
       }
     }
     if (dst != nullptr) {
-      float a0 = 0.f, a1 = 0.f;
+      // eight partials in flight per thread (the 37 loads of a thread were two per round trip)
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+      const float* src = partials + off;
       int q = q4;
-      for (; q + 4 < n_parts; q += 8) {
-        a0 += partials[(size_t)q * per + off];
-        a1 += partials[(size_t)(q + 4) * per + off];
+      for (; q + 28 < n_parts; q += 32) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = src[(size_t)(q + 4 * u) * per];
+        a0 += v[0] + v[4]; a1 += v[1] + v[5]; a2 += v[2] + v[6]; a3 += v[3] + v[7];
       }
-      if (q < n_parts) a0 += partials[(size_t)q * per + off];
-      a = a0 + a1;
+      {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = (q + 4 * u < n_parts) ? src[(size_t)(q + 4 * u) * per] : 0.f;
+        a0 += v[0] + v[4]; a1 += v[1] + v[5]; a2 += v[2] + v[6]; a3 += v[3] + v[7];
+      }
+      a = (a0 + a1) + (a2 + a3);
     }
   }
   a += __shfl_xor_sync(0xffffffffu, a, 1);
@@ -857,9 +867,21 @@ k_reduce_partials(const float* __restrict__ partials, int n_parts, int Npad2, in
   if (fin.scalars != nullptr && blockIdx.x == 0) {
     __shared__ float s_part[8];
     float l1 = 0.f;
-    for (int i = threadIdx.x; i < C * N; i += 256) {
-      const int c = i / N, n = i - c * N;
-      if (proto_class[n] != c) l1 += fabsf(W[i]);
+    for (int i0 = 0; i0 < C * N; i0 += 256 * 8) {          // both loads of eight elements in flight at once
+      float wv[8];
+      int pv[8], cv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * 256 + (int)threadIdx.x;
+        const bool in = i < C * N;
+        const int c = in ? i / N : 0, n = in ? i - c * N : 0;
+        cv[u] = c;
+        pv[u] = in ? proto_class[n] : c;
+        wv[u] = in ? W[i] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (pv[u] != cv[u]) l1 += fabsf(wv[u]);
     }
     l1 = warp_sum(l1);
     if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = l1;

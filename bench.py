@@ -29,6 +29,10 @@ import sys
 import threading
 import time
 
+# the contract is ONE JSON line on stdout: NCCL's own banner ("NCCL version ...", printed when the box exports
+# NCCL_DEBUG) goes to stderr instead
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))

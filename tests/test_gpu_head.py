@@ -206,3 +206,30 @@ def test_forward_many_tiles_per_cta_equals_image_by_image(prec):
             assert torch.equal(full["logits"][i:i + 1], one["logits"]), (rep, i)
             assert torch.equal(full["dist"][i:i + 1], one["dist"]), (rep, i)
             assert torch.equal(full["argmax"][i:i + 1], one["argmax"]), (rep, i)
+
+
+def test_backward_57_tiles_per_cta_repeated():
+    """B = 256 of 65 x 65 is 8450 tiles, 57 per persistent CTA, with features streaming from HBM.  The dP/dW builder
+    once waited for the two per-tile completions of a distance-MMA barrier by parity; held up in the next tile's
+    prefetch (HBM misses) it could find both done, the first wait then aliased with the next phase and the CTA
+    dead-locked until mbar_wait's watchdog trapped (intermittent 'unspecified launch failure' on some boxes).  The
+    barrier now completes once per tile.  The result must also equal the sum of eight 32-image launches."""
+    if not available("tf32"):
+        pytest.skip("tf32 kernels not built")
+    B, K, h, w, N, C = 256, 64, 65, 65, 190, 19
+    g = torch.Generator(device="cuda").manual_seed(5)
+    z = torch.sigmoid(torch.randn(B, K, h, w, device="cuda", generator=g))
+    P = torch.rand(N, K, device="cuda", generator=g)
+    W = torch.randn(C, N, device="cuda", generator=g) * 0.3
+    dl = torch.randn(B, h * w, C, device="cuda", generator=g) / (B * h * w)
+    for rep in range(12):
+        dz, dP, dW = head.head_backward(z, P, W, dlogits=dl, precision="tf32")
+        torch.cuda.synchronize()
+    sP, sW = torch.zeros_like(dP), torch.zeros_like(dW)
+    for i in range(0, B, 32):
+        dz_i, dP_i, dW_i = head.head_backward(z[i:i + 32], P, W, dlogits=dl[i:i + 32], precision="tf32")
+        assert torch.equal(dz_i, dz[i:i + 32])
+        sP += dP_i
+        sW += dW_i
+    assert (dP - sP).abs().max().item() <= 1e-5 * sP.abs().max().item()
+    assert (dW - sW).abs().max().item() <= 1e-5 * sW.abs().max().item()
