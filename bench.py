@@ -29,9 +29,17 @@ import sys
 import threading
 import time
 
-# the contract is ONE JSON line on stdout: NCCL's own banner ("NCCL version ...", printed when the box exports
-# NCCL_DEBUG) goes to stderr instead
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+# The contract is ONE JSON line on stdout.  NCCL prints its banner ("NCCL version ...", when the box exports
+# NCCL_DEBUG) with its own printf on file descriptor 1, so for the whole run descriptor 1 is pointed at stderr and the
+# result line is written to a saved copy of the real stdout.
+sys.stdout.flush()
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
 
 import numpy as np
 
@@ -225,7 +233,7 @@ def run_reference(args):
         "e2e": {"value": val, "unit": "Mpixels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def config_dict(prec, ring):
@@ -416,7 +424,7 @@ def main():
             "data": "synthetic", "config": config_dict(prec, ring), "clocks": sampler.summary(), "e2e": e2e,
             "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu, "push": push_res,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
