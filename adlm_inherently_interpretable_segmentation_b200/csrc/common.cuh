@@ -182,6 +182,7 @@ struct StepExtras {
   // features, applies the sigmoid while staging the tile and writes z to z_out; the dZ kernel multiplies by
   // z (1 - z).  Honoured by the tensor-core kernels only — callers must check head_fuses_sigmoid()
   float* z_out = nullptr;                // fwd: [B,K,HW] sigmoid(input); null = input already is z
+  int after_prepare = 0;                 // fwd: launched right after k_step_prepare; may overlap it (tc_head_ws.cu)
   int dz_sigmoid = 0;                    // bwd: dz <- dz * z (1 - z)
   // fused step epilogue (L1 term of dW, L1 value, the 8 scalars; module.py:213-222) inside the partials
   // reduction of the tensor-core backward — callers must check head_bwd_fuses_finalize()

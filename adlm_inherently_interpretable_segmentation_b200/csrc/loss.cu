@@ -324,6 +324,8 @@ k_step_prepare(const int32_t* __restrict__ target, const int32_t* __restrict__ p
   __shared__ int s_cls[ADLM_MAX_C];
   __shared__ int s_valid, s_terms, s_last;
   const int tid = threadIdx.x, b = blockIdx.x;
+  // the forward kernel may start now: it stages its operands and waits for this grid before reading its outputs
+  asm volatile("griddepcontrol.launch_dependents;");
   // Everything that depends on the prototype classes only (class sizes for every CTA, ranks by CTA 0) runs while the
   // label loads are in flight, not in the tail of the last CTA.
   __shared__ int s_pc[1024];
@@ -552,6 +554,7 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
   if (fuse_ce) {
     // CE, accuracy and dlogits come out of the forward kernel's logits registers; logits touch HBM only on request
     ex.ce_counts = counts;
+    ex.after_prepare = 1;                  // the forward is the launch right after k_step_prepare
     ex.ce_dlogits = want_grad ? ws.dlogits : nullptr;
     ex.ce_accum = ws.accum;
     ex.ce_scale = w_ce * grad_scale;

@@ -473,6 +473,7 @@ int tc_head_fwd(const HeadShape& s, int prec_mode, const float* z, const float* 
   prm.ce_counts = ex.ce_counts; prm.dlogits = ex.ce_dlogits; prm.ce_accum = ex.ce_accum;
   prm.ce_scale = ex.ce_scale; prm.ignore_void = ex.ignore_void;
   prm.z_out = ex.z_out;
+  prm.after_prepare = ex.after_prepare;
   if (ex.z_out != nullptr && (prec_mode == ADLM_PREC_TF32X3 || s.K > 64)) {
     set_error("tc_head_fwd: the fused sigmoid prologue needs ADLM_PREC_TF32 and K <= 64");
     return ADLM_E_UNSUPPORTED;

@@ -29,6 +29,9 @@ struct TcFwdParams {
   int Npad, Cpad;
   long long M;
   int num_tiles;
+  // launched right after k_step_prepare with programmatic stream serialisation: the CTAs start while the prologue
+  // kernel still runs, stage their operands and only then wait for it (griddepcontrol.wait)
+  int after_prepare;
 };
 // 1xTF32, K <= 64: producer / MMA / epilogue warps, double-buffered TMEM accumulators (tc_head_ws.cu)
 int tc_head_fwd_ws(const TcFwdParams& prm, cudaStream_t st);

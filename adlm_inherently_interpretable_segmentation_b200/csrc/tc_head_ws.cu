@@ -130,6 +130,10 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
   // Wk: B operand of MMA2, rows = classes, K index = prototype: [Npad/4][Cpad][4]; ln 2 folded in
   stage_w_kmajor(Wk, p.W, C, N, Cpad, Npad, p.act_mode == ADLM_ACT_LOG ? LN2 : 1.f, tid, WS_THREADS);
   __syncthreads();
+  // Everything above (TMEM, barriers, first feature tile in flight, P and W staged) is independent of the step's
+  // prologue kernel; its outputs (prototype ranks here, the CE normaliser and the cleared accumulators in the logits
+  // epilogue) are read from here on.  No-op unless launched with programmatic stream serialisation.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   for (int n = tid; n < Npad; n += WS_THREADS) {
     // |p|^2 of the ROUNDED vector, so that z == p gives d == 0
     float a = 0.f;
@@ -456,7 +460,21 @@ int launch_ws(const TcFwdParams& prm, cudaStream_t st) {
   ADLM_CUDA(cudaFuncSetAttribute(k_tc_fwd_ws<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
   const int grid = prm.num_tiles < sm_count_ws() ? prm.num_tiles : sm_count_ws();
   KernelTimer timer(ADLM_K_HEAD_FWD, st);
-  k_tc_fwd_ws<KP><<<grid, WS_THREADS, bytes, st>>>(prm);
+  if (prm.after_prepare) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(WS_THREADS);
+    cfg.dynamicSmemBytes = bytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    ADLM_CUDA(cudaLaunchKernelEx(&cfg, k_tc_fwd_ws<KP>, prm));
+  } else {
+    k_tc_fwd_ws<KP><<<grid, WS_THREADS, bytes, st>>>(prm);
+  }
   ADLM_LAUNCH_CHECK();
   return ADLM_OK;
 }

@@ -231,5 +231,6 @@ def test_backward_57_tiles_per_cta_repeated():
         assert torch.equal(dz_i, dz[i:i + 32])
         sP += dP_i
         sW += dW_i
-    assert (dP - sP).abs().max().item() <= 1e-5 * sP.abs().max().item()
-    assert (dW - sW).abs().max().item() <= 1e-5 * sW.abs().max().item()
+    # fp32 sums over 1.08 M pixels in a different order (per-CTA TMEM accumulators vs eight launches)
+    assert (dP - sP).abs().max().item() <= 1e-4 * sP.abs().max().item()
+    assert (dW - sW).abs().max().item() <= 1e-4 * sW.abs().max().item()
