@@ -60,6 +60,25 @@ struct KernelTimer {
   cudaStream_t st_;
 };
 
+// Launch with programmatic stream serialisation: the grid may start while the previous kernel of the stream still
+// runs (after that kernel's griddepcontrol.launch_dependents); it must execute griddepcontrol.wait before touching
+// anything the previous kernel writes.  pdl == false is an ordinary launch.
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_maybe_pdl(bool pdl, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                           cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<Args&&>(args)...);
+}
+
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 

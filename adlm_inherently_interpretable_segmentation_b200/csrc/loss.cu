@@ -125,6 +125,9 @@ k_kld(const float* __restrict__ own, const int32_t* __restrict__ target, const i
       float coef /* w_kld * grad_scale */, float* __restrict__ own_grad, double* __restrict__ accum) {
   static_assert(JMAX == 16, "thread layout assumes 16 prototypes per class at most");
   extern __shared__ int s_list[];                 // [cnt] pixel indices of this group
+  // the dZ kernel may start on SMs this grid leaves idle (1.03 waves: a long tail); it waits for this grid before
+  // reading the own-class gradients
+  asm volatile("griddepcontrol.launch_dependents;");
   const int l = blockIdx.x, b = blockIdx.y;
   const int J = min(cls_count[l], JMAX);
   const int cnt = hist[b * (C + 1) + l];

@@ -165,6 +165,11 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
   fence_before();
   __syncthreads();
   fence_after();
+  // Inside the step this grid is launched while k_kld still runs (its own-class gradients are first read in the
+  // tile loop below); the dP/dW kernel, which reads nothing this kernel writes, may in turn start as soon as CTAs of
+  // this grid leave their SMs — CTAs with one tile less (529 tiles over 148 CTAs) hand over early.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;");
 
   const uint32_t tmem_base = *tmem_base_s;
   const uint32_t tD = tmem_base + wg * 256;      // D1 half   [128 x NH]
@@ -936,17 +941,20 @@ int launch_bwd(TcBwdParams prm, float* dP, float* dW, const StepFinalize& fin, v
                cudaStream_t st) {
   const int grid = prm.num_tiles < sm_count() ? prm.num_tiles : sm_count();
   KernelTimer timer(ADLM_K_HEAD_BWD, st);
+  bool dz_launched = false;
   if (prm.dz != nullptr) {
     using L = DzSmem<KP>;
     const size_t bytes = L::total(prm.Npad, prm.C8);
+    const bool after_kld = prm.own_grad != nullptr;      // step path: the launch before this one is k_kld
     if (prm.dsim != nullptr || prm.ddist != nullptr) {
       ADLM_CUDA(cudaFuncSetAttribute(k_tc_bwd_dz<KP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-      k_tc_bwd_dz<KP, true><<<grid, 256, bytes, st>>>(prm);
+      ADLM_CUDA(launch_maybe_pdl(after_kld, k_tc_bwd_dz<KP, true>, dim3(grid), dim3(256), bytes, st, prm));
     } else {
       ADLM_CUDA(cudaFuncSetAttribute(k_tc_bwd_dz<KP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-      k_tc_bwd_dz<KP, false><<<grid, 256, bytes, st>>>(prm);
+      ADLM_CUDA(launch_maybe_pdl(after_kld, k_tc_bwd_dz<KP, false>, dim3(grid), dim3(256), bytes, st, prm));
     }
     ADLM_LAUNCH_CHECK();
+    dz_launched = true;
   }
   if (dP != nullptr || dW != nullptr) {
     using L = DpSmem<KP>;
@@ -962,7 +970,7 @@ int launch_bwd(TcBwdParams prm, float* dP, float* dW, const StepFinalize& fin, v
 #define ADLM_DP_LAUNCH(NBV, GEN)                                                                                       \
   do {                                                                                                                 \
     ADLM_CUDA(cudaFuncSetAttribute(k_tc_bwd_dp<KP, NBV, GEN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
-    k_tc_bwd_dp<KP, NBV, GEN><<<grid, DP_THREADS, bytes, st>>>(prm);                                                   \
+    ADLM_CUDA(launch_maybe_pdl(dz_launched, k_tc_bwd_dp<KP, NBV, GEN>, dim3(grid), dim3(DP_THREADS), bytes, st, prm));   \
   } while (0)
     if (NB == 1) { if (generic) ADLM_DP_LAUNCH(1, true); else ADLM_DP_LAUNCH(1, false); }
     else         { if (generic) ADLM_DP_LAUNCH(2, true); else ADLM_DP_LAUNCH(2, false); }
