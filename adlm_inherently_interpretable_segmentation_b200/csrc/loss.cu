@@ -371,6 +371,9 @@ k_step_prepare(const int32_t* __restrict__ target, const int32_t* __restrict__ p
     }
   }
   __syncthreads();
+  // Back-to-back steps: this grid may have started while the previous step's partials reduction still runs (it reads
+  // the accumulators this kernel clears and shares the workspace); labels, histogram and ranks above touch neither.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   for (int i = tid; i <= C; i += 1024) hist[b * (C + 1) + i] = sh[i];
   __threadfence();
   __syncthreads();
@@ -535,8 +538,8 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
       lay = dp_layout(s.K, N, C, cm.world);
     }
     KernelTimer timer(ADLM_K_STEP_PREPARE, st);
-    k_step_prepare<<<B, 1024, 0, st>>>(target, proto_class, B, HW, C, N, ignore_void, slot, ws.hist, ws.cls_count,
-                                       ws.counts, ws.rank, ws.accum, cm, lay);
+    ADLM_CUDA(launch_maybe_pdl(true, k_step_prepare, dim3(B), dim3(1024), 0, st, target, proto_class, B, HW, C, N,
+                               ignore_void, slot, ws.hist, ws.cls_count, ws.counts, ws.rank, ws.accum, cm, lay));
     ADLM_LAUNCH_CHECK();
   }
   const int* counts = (global_counts && !comm) ? global_counts : ws.counts;

@@ -785,6 +785,8 @@ __global__ void __launch_bounds__(256)
 k_reduce_partials(const float* __restrict__ partials, int n_parts, int Npad2, int KP, int N, int K,
                   int C, float* __restrict__ dP, float* __restrict__ dW, const float* __restrict__ W,
                   const int32_t* __restrict__ proto_class, const StepFinalize fin) {
+  // the next step's prologue kernel may start its label histogram now (it waits for this grid before it writes)
+  asm volatile("griddepcontrol.launch_dependents;");
   // 4 threads per output element, each sums a quarter of the per-CTA partials
   const size_t per = (size_t)Npad2 * KP + (size_t)Npad2 * 32;
   const int total = N * K + C * N;
