@@ -59,11 +59,9 @@ def patch_label(label_img, pi, pj, h, w, target_class):
     return int(vals[np.argmax(cnts)])
 
 
-def find_k_nearest_tensors(z, labels, prototypes, proto_class, k=5, precision=None, labels_host=None):
-    """z (n,K,h,w) CUDA features of the n images (PPNet.push_forward's first output), labels (n,H,W) CUDA uint8
-    (0 = void, class + 1 otherwise).  -> dict of numpy arrays, each (N,k), ordered by ascending distance:
-      labels     class id of the patch (find_nearest's labels_all_prototype; -1 void, -2 = fewer than k candidates)
-      distances, images, patch_i, patch_j"""
+def image_minima(z, labels, prototypes, proto_class, precision=None):
+    """per-(image, prototype) nearest non-void patch of a batch in ONE scan launch (adlm_push_scan_images):
+    -> (n,N) int64 packed words (float bits of the distance << 32 | patch index inside the image)"""
     lib = _lib.load()
     _check_cuda_f32("conv_features", z)
     z = z.contiguous()
@@ -74,8 +72,7 @@ def find_k_nearest_tensors(z, labels, prototypes, proto_class, k=5, precision=No
     dev = z.device
     if labels.dtype != torch.uint8 or not labels.is_cuda or labels.shape[0] != n:
         raise ValueError("labels must be a CUDA uint8 tensor (n,H,W)")
-    pc_np = proto_class.detach().cpu().numpy().astype(np.int64)
-    if int(pc_np.max()) >= _lib.MAX_PUSH_CLASSES:
+    if int(proto_class.max()) >= _lib.MAX_PUSH_CLASSES:
         raise NotImplementedError(f"the scan supports up to {_lib.MAX_PUSH_CLASSES} classes (uint32 patch mask)")
     pc = proto_class.to(device=dev, dtype=torch.int32).contiguous()
     mask = void_mask(labels, h, w)
@@ -85,34 +82,84 @@ def find_k_nearest_tensors(z, labels, prototypes, proto_class, k=5, precision=No
         rc = lib.adlm_push_scan_images(_lib.ptr(z), n, K, h * w, _lib.ptr(mask), _lib.ptr(P), N, _lib.ptr(pc),
                                        c_int(prec), _lib.ptr(packed), _lib.stream_ptr())
     _lib.check(rc, "adlm_push_scan_images")
-    # packed words order like (distance, patch id); a stable sort over the image axis keeps the earlier image on
+    return packed
+
+
+def top_k_and_labels(packed, k, label_of, pc_np, h, w, image_base=0, n_total=None, group=None):
+    """top-k images per prototype and the label rule on the winners (find_nearest.py:163-226).
+    packed (n_local,N) int64 minima of this rank's images [image_base, image_base + n_local) out of n_total;
+    label_of(i) -> (H,W) label image of LOCAL image i.  With a process group the minima are merged by one MIN
+    all-reduce of the (n_total,N) table (4.5 MB for Cityscapes train) and the labels of the N*k winners, each known to
+    the rank that owns the image, by one MAX all-reduce; every rank returns the same dict."""
+    import torch.distributed as dist
+    n_local, N = packed.shape
+    sharded = group is not None or (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+                                    and n_total is not None)
+    if n_total is None:
+        n_total = n_local
+    if sharded:
+        full = torch.full((n_total, N), _lib.PUSH_NONE, device=packed.device, dtype=torch.int64)
+        full[image_base:image_base + n_local] = packed
+        dist.all_reduce(full, op=dist.ReduceOp.MIN, group=group)
+    else:
+        full = packed
+    # packed words order like (distance, patch index); a stable sort over the image axis keeps the earlier image on
     # ties, as the reference's heap does (find_nearest.py:217-223)
-    order = torch.sort(packed, dim=0, stable=True)
-    top_words = order.values[:k].t().contiguous().cpu().numpy()          # (N,k)
+    order = torch.sort(full, dim=0, stable=True)
+    top_words = order.values[:k].t().contiguous().cpu().numpy()          # (N,kk)
     top_imgs = order.indices[:k].t().contiguous().cpu().numpy()
-    dist, patch = unpack(top_words.reshape(-1))
-    dist, patch = dist.reshape(top_words.shape), patch.reshape(top_words.shape)
+    dist_np, patch = unpack(top_words.reshape(-1))
+    dist_np, patch = dist_np.reshape(top_words.shape), patch.reshape(top_words.shape)
     kk = top_words.shape[1]
+    NOT_MINE, EMPTY = -10, -3
+    lab = np.full((N, kk), NOT_MINE, np.int64)
+    for j in range(N):
+        for t in range(kk):
+            i = int(top_imgs[j, t])
+            if patch[j, t] < 0 or not (image_base <= i < image_base + n_local):
+                continue
+            pi, pj = divmod(int(patch[j, t]), w)
+            got = patch_label(label_of(i - image_base), pi, pj, h, w, int(pc_np[j]))
+            lab[j, t] = EMPTY if got is None else got
+    if sharded:
+        lt = torch.from_numpy(lab)
+        if dist.get_backend(group) == "nccl":
+            lt = lt.to(packed.device)
+        dist.all_reduce(lt, op=dist.ReduceOp.MAX, group=group)
+        lab = lt.cpu().numpy()
     out = dict(labels=np.full((N, k), -2, np.int64), distances=np.full((N, k), np.inf),
                images=np.full((N, k), -1, np.int64), patch_i=np.full((N, k), -1, np.int64),
                patch_j=np.full((N, k), -1, np.int64))
-    host = {}
     for j in range(N):
         t_out = 0
         for t in range(kk):
-            if patch[j, t] < 0:
+            if patch[j, t] < 0 or lab[j, t] == EMPTY or lab[j, t] == NOT_MINE:
                 continue
-            i = int(top_imgs[j, t])
-            if i not in host:
-                host[i] = labels_host[i] if labels_host is not None else labels[i].cpu().numpy()
             pi, pj = divmod(int(patch[j, t]), w)
-            lab = patch_label(host[i], pi, pj, h, w, int(pc_np[j]))
-            if lab is None:
-                continue
-            out["labels"][j, t_out], out["distances"][j, t_out] = lab, dist[j, t]
-            out["images"][j, t_out], out["patch_i"][j, t_out], out["patch_j"][j, t_out] = i, pi, pj
+            out["labels"][j, t_out], out["distances"][j, t_out] = lab[j, t], dist_np[j, t]
+            out["images"][j, t_out], out["patch_i"][j, t_out], out["patch_j"][j, t_out] = int(top_imgs[j, t]), pi, pj
             t_out += 1
     return out
+
+
+def find_k_nearest_tensors(z, labels, prototypes, proto_class, k=5, precision=None, labels_host=None,
+                           image_base=0, n_total=None, group=None):
+    """z (n,K,h,w) CUDA features of the n images (PPNet.push_forward's first output), labels (n,H,W) CUDA uint8
+    (0 = void, class + 1 otherwise).  -> dict of numpy arrays, each (N,k), ordered by ascending distance:
+      labels     class id of the patch (find_nearest's labels_all_prototype; -1 void, -2 = fewer than k candidates)
+      distances, images, patch_i, patch_j
+    Multi-GPU: every rank passes its contiguous shard (parallel.image_range) with image_base / n_total; the result is
+    identical on all ranks (see top_k_and_labels)."""
+    packed = image_minima(z, labels, prototypes, proto_class, precision)
+    _, _, h, w = z.shape
+    pc_np = proto_class.detach().cpu().numpy().astype(np.int64)
+    host = {}
+
+    def label_of(i):
+        if i not in host:
+            host[i] = labels_host[i] if labels_host is not None else labels[i].cpu().numpy()
+        return host[i]
+    return top_k_and_labels(packed, k, label_of, pc_np, h, w, image_base, n_total, group)
 
 
 def prototypes_to_prune(nearest_labels, proto_class, prune_threshold):

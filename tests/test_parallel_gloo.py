@@ -130,3 +130,54 @@ def test_image_ranges_are_contiguous_and_cover():
         spans = [parallel.image_range(n, r, size) for r in range(size)]
         assert spans[0][0] == 0 and spans[-1][1] == n
         assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+
+
+# ------------------------------------------------------------------ k nearest patches, images sharded over ranks
+def _nearest_case():
+    n, K, h, w, N, C, H, W, k = 7, 16, 6, 7, 12, 4, 48, 56, 3
+    z, P, _ = synth.head_inputs(n, K, h, w, N, C, seed=31)
+    labels = synth.block_labels(n, H, W, C, block=8, seed=32)
+    labels[2, :, :30] = 0
+    pc = (np.arange(N) // (N // C)).astype(np.int64)
+    return z, P, labels, pc, (n, h, w, N, k)
+
+
+def _image_minima_cpu(z, P, labels, h, w):
+    """what adlm_push_scan_images returns for a void mask, from the oracle's distance maps"""
+    from adlm_inherently_interpretable_segmentation_b200 import nearest
+    n, N = z.shape[0], P.shape[0]
+    H, W = labels.shape[1:]
+    rl, cl = nearest.pil_nearest_lut(H, h), nearest.pil_nearest_lut(W, w)
+    packed = np.full((n, N), _lib.PUSH_NONE, dtype=np.int64)
+    for i in range(n):
+        d = orc.l2_distances(z[i:i + 1], P)[0].reshape(N, h * w)
+        ok = (labels[i][rl][:, cl] != 0).reshape(-1)
+        for j in range(N):
+            if ok.any():
+                dj = np.where(ok, d[j], np.inf)
+                a = int(dj.argmin())
+                packed[i, j] = (int(np.float32(dj[a]).view(np.uint32)) << 32) | a
+    return packed
+
+
+def _nearest_worker(rank, size):
+    from adlm_inherently_interpretable_segmentation_b200 import nearest
+    z, P, labels, pc, (n, h, w, N, k) = _nearest_case()
+    lo, hi = parallel.image_range(n, rank, size)
+    packed = torch.from_numpy(_image_minima_cpu(z[lo:hi], P, labels[lo:hi], h, w))
+    out = nearest.top_k_and_labels(packed, k, lambda i: labels[lo + i], pc, h, w, image_base=lo, n_total=n)
+    return {key: v.copy() for key, v in out.items()}
+
+
+def test_k_nearest_sharded_equals_single_process_and_oracle():
+    from adlm_inherently_interpretable_segmentation_b200 import nearest
+    z, P, labels, pc, (n, h, w, N, k) = _nearest_case()
+    packed = torch.from_numpy(_image_minima_cpu(z, P, labels, h, w))
+    single = nearest.top_k_and_labels(packed, k, lambda i: labels[i], pc, h, w)
+    for out in spawn(_nearest_worker):                # identical on both ranks and equal to the unsharded result
+        for key in single:
+            assert np.array_equal(out[key], single[key]), key
+    ol, od, oi, op = orc.find_k_nearest(z, P, labels, pc, k)
+    assert np.array_equal(single["labels"], ol) and np.array_equal(single["images"], oi)
+    assert np.array_equal(single["patch_i"] * w + single["patch_j"], op)
+    assert np.allclose(single["distances"], od, rtol=1e-6)
