@@ -352,7 +352,9 @@ k_step_prepare(const int32_t* __restrict__ target, const int32_t* __restrict__ p
     const int l = t[p];
     if (l >= 0 && l <= C) atomicAdd(&sh[l], 1);
   }
-  // class sizes (every CTA: the last one needs them) and the rank of a prototype inside its class (CTA 0)
+  // class sizes (every CTA: the last one needs them) and the rank of a prototype inside its class (CTA 0; kept in a
+  // register until the wait below: nothing is WRITTEN to global memory before it)
+  int my_rank = 0;
   for (int n0 = 0; n0 < N; n0 += 1024) {
     const int n = n0 + tid;
     const int c = n0 == 0 ? pc0 : (n < N ? proto_class[n] : -2);
@@ -361,19 +363,29 @@ k_step_prepare(const int32_t* __restrict__ target, const int32_t* __restrict__ p
     __syncthreads();
     if (n < N) {
       if (c >= 0 && c < C) atomicAdd(&s_cls[c], 1);
-      if (b == 0) {
+      if (b == 0 && n0 == 0) {
         int r = 0;
         for (int i = 0; i < tid; ++i) r += (s_pc[i] == c);
-        if (n0 > 0)
-          for (int i = 0; i < n0; ++i) r += (proto_class[i] == c);
-        rank[n] = r;
+        my_rank = r;
       }
     }
   }
   __syncthreads();
   // Back-to-back steps: this grid may have started while the previous step's partials reduction still runs (it reads
-  // the accumulators this kernel clears and shares the workspace); labels, histogram and ranks above touch neither.
+  // the accumulators this kernel clears and shares the workspace).  Everything above only READS inputs of this step
+  // (labels, prototype classes) into registers / shared memory; every global write comes after this wait.
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (b == 0) {
+    // a rank beyond the per-class capacity of the KLD side buffers is stored as -1: the head kernels then leave that
+    // prototype out of the KLD term and the last CTA flags the step as failed (scalars[7] > 0)
+    if (tid < N) rank[tid] = my_rank < JMAX ? my_rank : -1;
+    for (int n = 1024 + tid; n < N; n += 1024) {
+      const int c = proto_class[n];
+      int r = 0;
+      for (int i = 0; i < n; ++i) r += (proto_class[i] == c);
+      rank[n] = r < JMAX ? r : -1;
+    }
+  }
   for (int i = tid; i <= C; i += 1024) hist[b * (C + 1) + i] = sh[i];
   __threadfence();
   __syncthreads();
@@ -398,6 +410,10 @@ k_step_prepare(const int32_t* __restrict__ target, const int32_t* __restrict__ p
   __syncthreads();
   for (int c = tid; c < C; c += 1024) cls_count[c] = s_cls[c];
   if (tid < 4) accum[tid] = 0.0;
+  __syncthreads();
+  // more prototypes in one class than the own-class side buffers hold: the KLD term would be wrong -> fail the step
+  for (int c = tid; c < C; c += 1024)
+    if (s_cls[c] > JMAX) accum[3] = 1.0;
   if (comm.seq == 0u) {
     if (tid == 0) { counts[0] = s_valid; counts[1] = s_terms; }
     return;
@@ -465,7 +481,7 @@ __global__ void k_finalize(const float* __restrict__ W, const int32_t* __restric
     scalars[4] = accum[1];
     scalars[5] = n_valid;
     scalars[6] = n_terms;
-    scalars[7] = 0.0;
+    scalars[7] = accum[3];
   }
 }
 

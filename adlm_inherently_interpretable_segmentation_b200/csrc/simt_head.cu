@@ -139,8 +139,10 @@ k_simt_fwd(HeadShape s, const float* __restrict__ z, const float* __restrict__ P
         if (p < HW && n < N) {
           if (dist) dist[((size_t)b * N + n) * HW + p] = d;
           if (sim) sim[m * N + n] = sv;
-          if (lab[i] >= 0 && lab[i] == __ldg(ex.proto_class + n))
-            ex.own_dist[m * JMAX + __ldg(ex.proto_rank + n)] = d;
+          if (lab[i] >= 0 && lab[i] == __ldg(ex.proto_class + n)) {
+            const int rk = __ldg(ex.proto_rank + n);      // < 0: beyond ADLM_MAX_PROTOS_PER_CLASS (flagged by the prologue)
+            if (rk >= 0) ex.own_dist[m * JMAX + rk] = d;
+          }
         }
       }
     }
@@ -280,8 +282,10 @@ k_simt_bwd(HeadShape s, const float* __restrict__ z, const float* __restrict__ P
           if (dsim) up += __ldg(dsim + m * N + n);
           G = up * act_grad(d, s.eps, s.act_mode);
           if (ddist) G += __ldg(ddist + ((size_t)b * N + n) * HW + p);
-          if (lab[i] >= 0 && lab[i] == __ldg(ex.proto_class + n))
-            G += __ldg(ex.own_grad + m * JMAX + __ldg(ex.proto_rank + n));
+          if (lab[i] >= 0 && lab[i] == __ldg(ex.proto_class + n)) {
+            const int rk = __ldg(ex.proto_rank + n);
+            if (rk >= 0) G += __ldg(ex.own_grad + m * JMAX + rk);
+          }
           if (!(pre > 0.f)) G = 0.f;
         }
         gs[px * SS + nl] = G;

@@ -149,8 +149,9 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
       a = fmaf(v.x, v.x, a); a = fmaf(v.y, v.y, a); a = fmaf(v.z, v.z, a); a = fmaf(v.w, v.w, a);
     }
     p2s[n] = a;
-    pcs[n] = (kld && n < N) ? p.proto_class[n] : -1;
-    prs[n] = (kld && n < N) ? p.proto_rank[n] : 0;
+    const int rk = (kld && n < N) ? p.proto_rank[n] : -1;    // < 0: beyond ADLM_MAX_PROTOS_PER_CLASS
+    pcs[n] = rk >= 0 ? p.proto_class[n] : -1;
+    prs[n] = rk >= 0 ? rk : 0;
   }
   __syncthreads();
   for (int c = tid; c < Npad / 16; c += 256) {
@@ -608,7 +609,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
       pcl[blk] = -1;
       prk[blk] = 0;
       if (kld && n < N) { pcl[blk] = p.proto_class[n]; prk[blk] = p.proto_rank[n]; }
-      if (pcl[blk] < 0 || pcl[blk] >= 32) pcl[blk] = -1;
+      if (pcl[blk] < 0 || pcl[blk] >= 32 || prk[blk] < 0) { pcl[blk] = -1; prk[blk] = 0; }
     }
     const float eps = p.eps, epsm1 = p.eps - 1.f;
     const bool act_log = p.act_mode == ADLM_ACT_LOG;

@@ -142,8 +142,10 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
       a = fmaf(v.x, v.x, a); a = fmaf(v.y, v.y, a); a = fmaf(v.z, v.z, a); a = fmaf(v.w, v.w, a);
     }
     p2s[n] = a;
-    pcs[n] = (want_own && n < N) ? p.proto_class[n] : -1;
-    prs[n] = (want_own && n < N) ? p.proto_rank[n] : 0;
+    // rank < 0: the prototype lies beyond ADLM_MAX_PROTOS_PER_CLASS (the prologue kernel flags the step as failed)
+    const int rk = (want_own && n < N) ? p.proto_rank[n] : -1;
+    pcs[n] = rk >= 0 ? p.proto_class[n] : -1;
+    prs[n] = rk >= 0 ? rk : 0;
   }
   __syncthreads();
   for (int c = tid; c < Npad / 16; c += WS_THREADS) {

@@ -181,6 +181,29 @@ class _StepResult(dict):
     __getattr__ = dict.__getitem__
 
 
+_PER_CLASS_OK = {}
+
+
+def _check_protos_per_class(pc):
+    """The KLD side buffers hold at most ADLM_MAX_PROTOS_PER_CLASS (16) own-class distances per pixel; the reference
+    has no such limit (module.py:170-190), so a head with a larger class is rejected loudly rather than computed wrong.
+    One bincount + sync per distinct proto_class tensor (cached on storage pointer, version, length, device)."""
+    key = (pc.data_ptr(), pc._version, pc.numel(), str(pc.device))
+    if key in _PER_CLASS_OK:
+        return
+    if pc.numel():
+        if int(pc.min()) < 0:
+            raise ValueError("proto_class entries must be >= 0")
+        worst = int(torch.bincount(pc.to(torch.int64)).max())
+        if worst > _lib.MAX_PROTOS_PER_CLASS:
+            raise NotImplementedError(
+                f"fused_step supports at most {_lib.MAX_PROTOS_PER_CLASS} prototypes per class "
+                f"(ADLM_MAX_PROTOS_PER_CLASS); this head has a class with {worst}")
+    if len(_PER_CLASS_OK) > 64:
+        _PER_CLASS_OK.clear()
+    _PER_CLASS_OK[key] = True
+
+
 def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
                weights=(1.0, 0.25, 1e-4), grad_scale=1.0, eps=1e-4, precision=None,
                need_grads=True, want_logits=False, want_argmax=False, workspace=None, global_counts=None,
@@ -217,6 +240,7 @@ def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
     pc = proto_class.to(device=dev, dtype=torch.int32).contiguous()
     if pc.numel() != N:
         raise ValueError("proto_class must have N entries")
+    _check_protos_per_class(pc)
     w_ce, w_kld, w_l1 = (float(x) for x in weights)
     with torch.cuda.device(dev):
         need = int(lib.adlm_step_workspace_bytes(B, K, HW, N, C))

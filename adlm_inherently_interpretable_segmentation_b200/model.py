@@ -139,8 +139,23 @@ class PrototypeHeadMixin:
         return out["logits"], out["argmax"]
 
     def proto_class(self):
-        """(N,) int32 class of each prototype, on the prototypes' device"""
-        return _head.proto_class_from_identity(self.prototype_class_identity).to(self.prototype_vectors.device)
+        """(N,) int32 class of each prototype, on the prototypes' device.  Cached: the one-hot validation, the arg-max
+        and the host -> device copy cost more than a training step; the cache is keyed on the identity tensor (object,
+        version, shape) and the device, so prune_prototypes / a reassigned identity / .to(device) invalidate it."""
+        ident = self.prototype_class_identity
+        dev = self.prototype_vectors.device
+        key = (id(ident), ident._version, tuple(ident.shape), str(dev))
+        cached = self.__dict__.get('_proto_class_cache')
+        if cached is None or cached[0] != key:
+            pc = _head.proto_class_from_identity(ident).to(dev)
+            per_class = int(torch.bincount(pc.to(torch.int64).cpu(), minlength=1).max()) if pc.numel() else 0
+            cached = (key, pc, per_class)
+            self.__dict__['_proto_class_cache'] = cached
+        return cached[1]
+
+    def max_prototypes_per_class(self):
+        self.proto_class()
+        return self.__dict__['_proto_class_cache'][2]
 
     def fused_step(self, conv_features, target, ignore_void_class=True, loss_weights=(1.0, 0.25, 1e-4),
                    grad_scale=1.0):

@@ -148,9 +148,23 @@ class PushSearch:
         if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
             dist.all_reduce(self.packed, op=dist.ReduceOp.MIN, group=group)
 
+    def sync_map_size(self, group=None):
+        """multi-GPU: a rank whose image range is empty (more ranks than images) never scanned and does not know the
+        feature-map size the global patch ids are built on; take it from a rank that did (one MAX all-reduce)."""
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            t = torch.tensor(list(self.hw or (0, 0)), device=self.device, dtype=torch.int64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+            hw = (int(t[0]), int(t[1]))
+            if hw != (0, 0):
+                self.hw = hw
+
     def winners(self):
         """-> (min distance float64 (N,), image index (N,), patch_i (N,), patch_j (N,)); -1 where none"""
         d, ids = unpack(self.packed.cpu().numpy())
+        if self.hw is None:                      # nothing was scanned anywhere: no winners (push.py:57-61)
+            none = np.full(self.N, -1, dtype=np.int64)
+            return d, none, none.copy(), none.copy()
         h, w = self.hw
         img = np.where(ids >= 0, ids // (h * w), -1)
         patch = np.where(ids >= 0, ids % (h * w), -1)
@@ -279,7 +293,10 @@ def push_prototypes(dataset,
         proto_epoch_dir = root_dir_for_saving_prototypes
 
     proto_class = ppnet.proto_class()
-    search = PushSearch(ppnet.prototype_vectors, proto_class, precision=ppnet.head_precision)
+    # The winners must be the fp32 arg-min (push.py:259-265): a model trained with head_precision 'tf32' still
+    # searches with fp32-class distances, exactly as model._forward_min_pool does.
+    prec = ppnet.head_precision if ppnet.head_precision in ("fp32", "tf32x3") else PUSH_DEFAULT_PRECISION
+    search = PushSearch(ppnet.prototype_vectors, proto_class, precision=prec)
     dev = search.device
     img_ids = list(dataset.img_ids)
     per = (len(img_ids) + world - 1) // world
@@ -295,6 +312,7 @@ def push_prototypes(dataset,
             search.scan(z.float(), labels, idx)
             img_hw[idx] = ann.shape
         search.reduce()
+        search.sync_map_size()
         dmin, w_img, w_pi, w_pj = search.winners()
         new_protos = torch.zeros((N, search.K), device=dev, dtype=torch.float32)
         pc = proto_class.cpu().numpy()

@@ -5,8 +5,7 @@
  * adlm_inherently_interpretable_segmentation_b200/csrc/ by nvcc for sm_100a) exports exactly
  * the symbols declared here.  Plain C: pointers + sizes, no torch types.  Every pointer is a
  * DEVICE pointer unless it says "host"; every buffer is allocated and owned by the caller
- * (torch, in the Python host); nothing is allocated inside except lazily created TMA
- * descriptors.  Every call is asynchronous on `stream` (a cudaStream_t passed as void*).
+ * (torch, in the Python host); nothing is allocated inside.  Every call is asynchronous on `stream` (a cudaStream_t passed as void*).
  * Return value: 0 on success, negative ADLM_E_* on failure, message via adlm_last_error().
  * There is no CPU fallback and no fallback to a library GEMM: unsupported shapes return
  * ADLM_E_UNSUPPORTED.
@@ -76,7 +75,8 @@ extern "C" {
 /* number of doubles adlm_step_fwd_bwd writes to `scalars` */
 #define ADLM_STEP_NSCALARS 8
 /* scalars[0] loss  [1] cross_entropy  [2] kld_loss  [3] l1  [4] n_correct  [5] n_patches (non-void)
- * [6] n_kld_terms  [7] 0, or > 0 when a peer exchange of adlm_step_fwd_bwd_dp timed out (results are NaN) */
+ * [6] n_kld_terms  [7] 0, or > 0 when the step failed: a peer exchange of adlm_step_fwd_bwd_dp timed out (results are
+ * NaN), or a class has more than ADLM_MAX_PROTOS_PER_CLASS prototypes (the KLD term is then incomplete) */
 
 ADLM_API const char* adlm_last_error(void);
 ADLM_API int adlm_abi_version(void);
