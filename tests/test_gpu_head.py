@@ -39,8 +39,27 @@ def dist_delta(prec, K, z=None, P=None):
     ulps, _ = PRECISIONS[prec]
     if ulps is not None:
         return ulps * K * 2.0 ** -21
-    # 1xTF32 on centred operands: |z-0.5|,|p-0.5| <= 0.5 rounded to 11 bits -> K * 2 * 0.25 * 2^-11 worst case
-    return K * 0.5 * 2.0 ** -11
+    # 1xTF32 on centred operands, STATISTICAL bound: d = |zr - pr|^2 with zr, pr rounded to 11 significant bits, so the
+    # error is a sum of K independent terms ~ 2 (z-p) (dz-dp).  In units of u = sqrt(K) * 0.25 * 2^-11 a bit-level
+    # numpy emulation of the kernel's arithmetic gives max 2.0-2.6 u and mean 0.32-0.38 u over 1.6 M distances
+    # (regimes A and B, K = 32 and 64); the worst-case bound would be K * 0.5 * 2^-11 = 16 u at K = 64.
+    return TF32_MAX_UNITS * tf32_unit(K)
+
+
+TF32_MAX_UNITS, TF32_MEAN_UNITS = 4.0, 0.5
+
+
+def tf32_unit(K):
+    return np.sqrt(K) * 0.25 * 2.0 ** -11
+
+
+def check_dist_error(prec, K, dist, ref, what):
+    """max (all modes) and mean (tf32) distance error against the reference; prints what was measured"""
+    err = np.abs(dist.astype(np.float64) - ref.astype(np.float64))
+    print(f"[{what} {prec}] distance error max {err.max():.3e} mean {err.mean():.3e} (bound {dist_delta(prec, K):.3e})")
+    assert err.max() <= dist_delta(prec, K)
+    if prec == "tf32":
+        assert err.mean() <= TF32_MEAN_UNITS * tf32_unit(K)
 
 
 @pytest.mark.parametrize("prec", list(PRECISIONS))
@@ -59,7 +78,7 @@ def test_forward_matches_reference_golden(golden, name, prec):
     delta = dist_delta(prec, K)
     rel = PRECISIONS[prec][1]
     assert dist.min() >= 0
-    assert np.abs(dist - g["dist"]).max() <= delta
+    check_dist_error(prec, K, dist, g["dist"], name)
     dref = parity.dist_MN(g["dist"])
     assert np.all(np.abs(sim - g["act"]) <= parity.sim_tol(dref, delta, rel) + 1e-6)
     tol = parity.logit_tol(dref, g["W"], delta, rel)
@@ -71,7 +90,12 @@ def test_forward_matches_reference_golden(golden, name, prec):
     assert np.all(np.abs(logits.reshape(-1, C) - s64 @ w64.T) <= bound)
     assert np.array_equal(amax.reshape(-1), logits.reshape(-1, C).argmax(1))
     agree, unexplained = parity.argmax_agreement(logits, g["logits"], tol)
-    assert unexplained == 0 and agree > (0.97 if prec == "tf32" else 0.99)
+    n_px = logits.reshape(-1, C).shape[0]
+    n_ties = int(round((1.0 - agree) * n_px))
+    print(f"[{name} {prec}] argmax agreement {agree:.5f}: {n_ties} of {n_px} pixels differ, all of them near-ties "
+          f"inside the tolerance (logged as BASELINE.json asks); unexplained {unexplained}")
+    # every mismatch must be a logged near-tie, and there may be only a handful of them (emulation: 1 of 442)
+    assert unexplained == 0 and (agree > 0.995 or n_ties <= 2)
 
 
 @pytest.mark.parametrize("prec", list(PRECISIONS))
@@ -85,7 +109,7 @@ def test_forward_cfg1_full_size(golden, prec):
     z, P, W = cuda(zn, Pn, Wn)
     out = head.head_forward(z, P, W, precision=prec, want_dist=True, want_argmax=True)
     dist = out["dist"].cpu().numpy().reshape(B, N, h * w)
-    assert np.abs(dist[:, ::7, ::13] - g["dist_sample"]).max() <= dist_delta(prec, K)
+    check_dist_error(prec, K, dist[:, ::7, ::13], g["dist_sample"], "cfg1")
     logits = out["logits"].cpu().numpy()
     rel = 1e-3 if prec == "tf32" else 1e-4
     assert np.allclose(logits, g["logits"], rtol=rel, atol=rel * np.abs(g["logits"]).max())
@@ -94,6 +118,80 @@ def test_forward_cfg1_full_size(golden, prec):
     # outputs that were not requested are not needed for the same logits
     only = head.head_forward(z, P, W, precision=prec, want_dist=False)
     assert only["dist"] is None and torch.equal(only["logits"], out["logits"])
+
+
+def _full_inputs(g):
+    meta = [int(v) for v in g["meta"]]
+    B, K, h, w, N, C, seed, stride = meta[:8]
+    zn, Pn, Wn = synth.head_inputs(B, K, h, w, N, C, regime="B" if meta[8] else "A", w_noise=0.1, seed=seed)
+    return (B, K, h, w, N, C, stride), zn, Pn, Wn
+
+
+def _check_full_forward(g, prec, out, dims, dist_stats=None):
+    B, K, h, w, N, C, stride = dims
+    logits = out["logits"].cpu().numpy().reshape(B, h * w, C)
+    amax = out["argmax"].cpu().numpy().reshape(B, h * w)
+    regime_b = int(g["meta"][8]) == 1
+    rel = 1e-3 if prec == "tf32" else 1e-5
+    # regime B: prototypes ON pixels -> the reference's own fp32 noise at d ~ 0 dominates (tests/parity.py)
+    ltol = ((2e-2 if regime_b else 2e-4) + rel) * float(g["logits_absmax"])
+    if prec == "tf32" and regime_b:
+        ltol = 0.35 * float(g["logits_absmax"])            # a matched pixel's similarity moves by O(1) in one TF32 pass
+    e = float(np.abs(logits[:, ::stride] - g["logits_sample"]).max())
+    assert np.array_equal(amax, logits.argmax(axis=2))
+    bad = amax != g["argmax"]
+    ties = int(bad.sum())
+    print(f"[{prec}] full-size logits max err {e:.3e} (tolerance {ltol:.3e}); argmax differs on {ties} of {bad.size} "
+          f"pixels, largest reference top-two gap among them {float(g['top2_gap'][bad].max()) if ties else 0.0:.3e}")
+    assert e <= ltol
+    assert bad.mean() < (2e-2 if (prec == "tf32" and regime_b) else 2e-3) and np.all(g["top2_gap"][bad] <= 2 * ltol)
+    if dist_stats is not None:
+        dmin, dsum = dist_stats
+        delta = dist_delta(prec, K)
+        assert np.abs(dmin - g["dist_min"]).max() <= delta
+        assert np.abs(dsum - g["dist_plane_sums"]).max() <= (1e-3 if prec == "tf32" else 1e-5) * g["dist_plane_sums"].max()
+
+
+@pytest.mark.parametrize("prec", list(PRECISIONS))
+def test_forward_cfg4_full_size(golden, prec):
+    """BASELINE configs[3] (mds_new.gin:6-7): 64 slices of 64x65x65 features, 30 prototypes (3 classes x 10), inference
+    with the per-pixel argmax eval_valid.py:176 takes — against the reference model's own output at that size"""
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    g = golden("head_fwd_cfg4")
+    dims, zn, Pn, Wn = _full_inputs(g)
+    B, K, h, w, N, C, stride = dims
+    z, P, W = cuda(zn, Pn, Wn)
+    out = head.head_forward(z, P, W, precision=prec, want_dist=True, want_argmax=True)
+    d = out["dist"].reshape(B, N, h * w)
+    stats = (d.min(dim=2).values.cpu().numpy(), d.double().sum(dim=2).cpu().numpy())
+    _check_full_forward(g, prec, out, dims, stats)
+    only = head.head_forward(z, P, W, precision=prec, want_dist=False, want_argmax=True)    # the eval path (predict)
+    assert torch.equal(only["logits"], out["logits"]) and torch.equal(only["argmax"], out["argmax"])
+
+
+@pytest.mark.parametrize("prec", list(PRECISIONS))
+def test_forward_cfg5_crop(golden, prec):
+    """BASELINE configs[4] on a 129x257 crop: 1000 prototypes x 256-d, 100 classes — against the reference model"""
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    g = golden("head_fwd_cfg5")
+    dims, zn, Pn, Wn = _full_inputs(g)
+    B, K, h, w, N, C, stride = dims
+    z, P, W = cuda(zn, Pn, Wn)
+    try:
+        out = head.head_forward(z, P, W, precision=prec, want_dist=True, want_argmax=True)
+    except NotImplementedError:
+        # a tensor-core mode without a kernel for this shape must say so (ADLM_E_UNSUPPORTED), never reroute silently
+        assert prec != "fp32" and not CFG5_TENSOR_PATH
+        return
+    d = out["dist"].reshape(B, N, h * w)
+    stats = (d.min(dim=2).values.cpu().numpy(), d.double().sum(dim=2).cpu().numpy())
+    _check_full_forward(g, prec, out, dims, stats)
+
+
+#: set once the N-tiled tcgen05 forward for N > 224 / K > 64 exists: the cfg5 test then requires it to run
+CFG5_TENSOR_PATH = False
 
 
 @pytest.mark.parametrize("prec", list(PRECISIONS))

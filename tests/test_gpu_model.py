@@ -167,7 +167,10 @@ class _DiskDataset:
         return os.path.join(self.img_dir, img_id + ".png")
 
 
-def test_push_prototypes_end_to_end(tmp_path):
+@pytest.mark.parametrize("head_precision", [None, "tf32"])
+def test_push_prototypes_end_to_end(tmp_path, head_precision):
+    """head_precision 'tf32' (the pre-push training mode INTEGRATION.md recommends) must not leak into the search: the
+    winners are the fp32 arg-min either way (push.py:259-265)"""
     torch.manual_seed(1)
     rng = np.random.default_rng(5)
     n_img, H, W, K, N, C = 3, 64, 96, 16, 30, 3
@@ -177,6 +180,7 @@ def test_push_prototypes_end_to_end(tmp_path):
     ds = _DiskDataset(str(tmp_path), imgs, labels)
     net = model.PPNet(features=Backbone(K), img_size=64, prototype_shape=(N, K, 1, 1), proto_layer_rf_info=None,
                       num_classes=C, add_on_layers_type='deeplab_simple', patch_classification=True).cuda()
+    net.head_precision = head_precision
     P0 = net.prototype_vectors.detach().cpu().numpy().reshape(N, K).copy()
     # expected result from the oracle on the same features
     feats = []
@@ -204,6 +208,7 @@ def test_push_prototypes_end_to_end(tmp_path):
     assert np.all(bb[has, 1] <= orf[has, 1]) and np.all(bb[has, 2] >= orf[has, 2])
     assert any("push time" in str(l) for l in logs)
     # the pushed prototypes now sit on feature pixels: distance ~0 at the winner patch
+    net.head_precision = None
     with torch.no_grad():
         d = net._l2_convolution(torch.from_numpy(feats).cuda())
     dmin = d.flatten(2).min(dim=2).values.min(dim=0).values.cpu().numpy()

@@ -56,6 +56,27 @@ def test_push_matches_reference_fixture(golden, name, prec):
     ui, dup = push.dedup_prototypes(got.astype(np.float64))
     if same.all():
         assert np.array_equal(np.sort(ui), g["unique_index"]) and np.array_equal(dup, g["duplicate_idx"])
+    # activation-crop boxes (push.py:309-350) of the winners, EXACTLY as the reference stored them: similarity map
+    # of the winning prototype on the winner image -> cubic upsample -> 95th percentile -> crop growth on the
+    # ground-truth pixels of the prototype's class
+    try:
+        import cv2  # noqa: F401
+    except ImportError:
+        return
+    from adlm_inherently_interpretable_segmentation_b200 import head
+    W_last = torch.zeros(C, N, device="cuda")
+    pcn = proto_class(N, C).cpu().numpy()
+    n_checked = 0
+    for idx in sorted(set(int(i) for i in w_img[same & fin])):
+        dist_map = head.head_forward(z[idx:idx + 1], P, W_last, precision="fp32" if prec == "tf32" else prec,
+                                     want_dist=True)["dist"][0].cpu().numpy()
+        for j in np.nonzero((w_img == idx) & same & fin)[0]:
+            box = push.rf_box(int(w_pi[j]), int(w_pj[j]), H, Wimg, h, w)
+            bb = push.activation_bound_box(dist_map[j], g["labels"][idx], int(pcn[j]), box, 'log', 1e-4)
+            assert (idx,) + tuple(int(v) for v in bb) == tuple(int(v) for v in g["bound_boxes"][j][:5]), j
+            assert int(g["bound_boxes"][j][5]) == int(pcn[j])
+            n_checked += 1
+    assert n_checked == int((same & fin).sum()) > 0
 
 
 @pytest.mark.parametrize("prec", PRECS)

@@ -163,3 +163,26 @@ def test_nearest_patch_label_rule_and_pruning():
     pc = np.array([0, 1, 2, 3])
     assert nearest.prototypes_to_prune(labels, pc, 2) == orc.prototypes_to_prune(labels, pc, 2) == [2]
     assert nearest.prototypes_to_prune(labels, pc, 3) == [0, 2, 3]
+
+
+@pytest.mark.parametrize("name", ["push_small", "push_mds"])
+def test_activation_bound_boxes_equal_the_reference_fixture(golden, name):
+    """push.activation_bound_box / grow_high_activation_box (host code of push_prototypes) reproduce the boxes the
+    reference stored for every winner (push.py:309-350, helpers.py:48-82), exactly"""
+    pytest.importorskip("cv2")
+    from oracle import head_oracle as orc
+    g = golden(name)
+    n_img, K, h, w, N, C, H, Wimg, seed = [int(v) for v in g["meta"]]
+    pc = np.arange(N) // (N // C)
+    rf = g["rf_boxes"]
+    n = 0
+    for j in range(N):
+        if rf[j, 0] < 0:
+            assert np.all(g["bound_boxes"][j] == -1)
+            continue
+        idx = int(rf[j, 0])
+        d = orc.l2_distances(g["z"][idx:idx + 1], g["P"])[0]
+        bb = push.activation_bound_box(d[j], g["labels"][idx], int(pc[j]), tuple(int(v) for v in rf[j, 1:5]), 'log', 1e-4)
+        assert (idx,) + tuple(int(v) for v in bb) == tuple(int(v) for v in g["bound_boxes"][j][:5])
+        n += 1
+    assert n > 0

@@ -215,3 +215,50 @@ def test_min_pool_step_post_push_regime(golden):
     assert abs(r["cluster"] - float(g["cluster"])) <= 1e-5 and abs(r["separation"] - float(g["separation"])) <= 1e-5
     for key in ("dz", "dP", "dW"):
         assert np.abs(r[key] - g[key]).max() <= 5e-2 * np.abs(g[key]).max(), key
+
+
+# ---- full-size fixtures (oracle/make_golden_full.py): outputs of the reference at the sizes BASELINE.json quotes
+def full_inputs(g, regime=None):
+    meta = [int(v) for v in g["meta"]]
+    B, K, h, w, N, C, seed, stride = meta[:8]
+    if regime is None:
+        regime = "B" if len(meta) > 8 and meta[8] else "A"
+    z, P, W = synth.head_inputs(B, K, h, w, N, C, regime=regime, w_noise=0.1, seed=seed)
+    return (B, K, h, w, N, C, stride), z, P, W
+
+
+def test_step_cfg2_full_size_matches_reference_step(golden):
+    """BASELINE configs[1]: batch 16 of 64x65x65, 190x64, 19 classes, against the reference's own _step"""
+    g = golden("step_cfg2")
+    (B, K, h, w, N, C, stride), z, P, W = full_inputs(g, "A")
+    o = orc.step_loss(z, P, W, g["target"].astype(np.int64), ignore_void=True, weights=tuple(g["weights"]))
+    assert o["n_patches"] == int(g["n_patches"])
+    assert o["loss"] == pytest.approx(float(g["loss"]), rel=2e-5)
+    assert o["cross_entropy"] == pytest.approx(float(g["cross_entropy"]), rel=2e-5)
+    assert o["kld_loss"] == pytest.approx(float(g["kld_loss"]), rel=5e-5)
+    assert abs(o["n_correct"] - int(g["n_correct"])) <= 2
+    dz = o["dz"].reshape(B, K, h * w)
+    scale = float(g["dz_absmax"])
+    assert np.abs(dz[:, :, ::stride] - g["dz_sample"]).max() <= 2e-4 * scale
+    assert np.abs(dz.sum(axis=2) - g["dz_plane_sums"]).max() <= 2e-4 * np.abs(g["dz_plane_sums"]).max()
+    assert parity.rel_err(o["dP"], g["dP"]) <= 2e-4 and parity.rel_err(o["dW"], g["dW"]) <= 2e-4
+
+
+@pytest.mark.parametrize("name", ["head_fwd_cfg4", "head_fwd_cfg5"])
+def test_forward_full_size_matches_reference(golden, name):
+    """configs[3] (64 slices, 30 prototypes, per-pixel argmax) and configs[4] (1000 x 256-d, 100 classes, 129x257 crop)"""
+    g = golden(name)
+    (B, K, h, w, N, C, stride), z, P, W = full_inputs(g)
+    nb = 8 if name == "head_fwd_cfg4" else B            # the oracle is checked on a slice of the 64 images
+    logits, d, _ = orc.head_forward(z[:nb], P, W)
+    logits = logits.reshape(nb, h * w, C)
+    d = d.reshape(nb, N, h * w)
+    tol_d = dist_tol(z, P)
+    assert np.abs(d.min(axis=2) - g["dist_min"][:nb]).max() <= tol_d
+    assert np.abs(d.astype(np.float64).sum(axis=2) - g["dist_plane_sums"][:nb]).max() <= 1e-5 * g["dist_plane_sums"].max()
+    # regime B (cfg4) has prototypes ON pixels: those logits carry the reference's own d ~ 0 noise (parity.py)
+    ltol = (2e-2 if name == "head_fwd_cfg4" else 2e-4) * float(g["logits_absmax"])
+    assert np.abs(logits[:, ::stride] - g["logits_sample"][:nb]).max() <= ltol
+    am = logits.argmax(axis=2)
+    bad = am != g["argmax"][:nb]
+    assert bad.mean() < 2e-3 and np.all(g["top2_gap"][:nb][bad] <= 2 * ltol)      # near-ties only
