@@ -1004,8 +1004,15 @@ int tc_head_bwd(const HeadShape& s, int prec_mode, const float* z, const float* 
                 const float* dlogits, const float* ddist, const float* dsim, float* dz, float* dP,
                 float* dW, const StepExtras& ex, void* workspace, size_t workspace_bytes, cudaStream_t st) {
   if (!tc_bwd_supported(s, prec_mode)) {
-    // 3xTF32 (fp32-class) and shapes beyond the tensor-core backward's operand budget take the fp32
-    // CUDA-core backward: same mathematics, tighter arithmetic
+    if (prec_mode == ADLM_PREC_TF32) {
+      // beyond the tensor-core backward's operand budget: refused like the forward does, the caller picks
+      // ADLM_PREC_FP32 explicitly — no silent change of kernel class
+      set_error("adlm_head_bwd: the tcgen05 backward needs K <= 64, N <= 192, C <= 32 (got K=%d N=%d C=%d); use ADLM_PREC_FP32",
+                s.K, s.N, s.C);
+      return ADLM_E_UNSUPPORTED;
+    }
+    // ADLM_PREC_TF32X3 is the fp32-class mode: its backward IS the fp32 CUDA-core backward, for every shape
+    // (include/adlm_head.h) — same mathematics, tighter arithmetic
     if (ex.dz_sigmoid) {
       set_error("tc_head_bwd: the fused sigmoid backward needs ADLM_PREC_TF32, K <= 64, N <= 192, C <= 32");
       return ADLM_E_UNSUPPORTED;

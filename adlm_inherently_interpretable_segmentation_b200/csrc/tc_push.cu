@@ -393,9 +393,12 @@ int tc_push_scan(const float* z, int n_img, int K, int HW, const uint32_t* mask,
                  unsigned long long* packed_min, int per_image, cudaStream_t st) {
   const long long M = (long long)n_img * HW;
   const int tiles_per_img = (HW + TILE - 1) / TILE;
-  // shapes beyond the tensor-core kernel's operand budget take the fp32 CUDA-core scan: same search, same keys
-  if (K > 64 || N > 224 || M >= (1ll << 31) - 256 || (long long)n_img * tiles_per_img >= (1ll << 31))
-    return simt_push_scan(z, n_img, K, HW, mask, P, N, proto_class, patch_base, packed_min, per_image, st);
+  // Shapes beyond the tensor-core kernel's operand budget are refused, like the forward does: the caller picks
+  // ADLM_PREC_FP32 (the CUDA-core scan: same search, same keys) explicitly — no silent change of kernel class.
+  if (K > 64 || N > 224 || M >= (1ll << 31) - 256 || (long long)n_img * tiles_per_img >= (1ll << 31)) {
+    set_error("adlm_push_scan: the tcgen05 scan needs K <= 64 and N <= 224 (got K=%d N=%d); use ADLM_PREC_FP32", K, N);
+    return ADLM_E_UNSUPPORTED;
+  }
   TcPushParams prm;
   prm.z = z; prm.mask = mask; prm.P = P; prm.proto_class = proto_class; prm.packed_min = packed_min;
   prm.patch_base = (unsigned long long)patch_base;

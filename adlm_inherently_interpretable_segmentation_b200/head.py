@@ -381,7 +381,7 @@ def min_pool_forward(z, prototypes, precision=None):
         mind = torch.empty((B, N), device=dev, dtype=torch.float32)
         amin = torch.empty((B, N), device=dev, dtype=torch.int32)
         rc = lib.adlm_min_pool_fwd(_lib.ptr(z), B, K, h * w, _lib.ptr(P), N,
-                                   _prec(precision or MIN_POOL_DEFAULT_PRECISION),
+                                   _prec(precision or (MIN_POOL_DEFAULT_PRECISION if (K <= 64 and N <= 224) else "fp32")),
                                    _lib.ptr(packed), _lib.ptr(mind), _lib.ptr(amin), _lib.stream_ptr())
     _lib.check(rc, "adlm_min_pool_fwd")
     return mind, amin, packed

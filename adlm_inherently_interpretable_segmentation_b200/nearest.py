@@ -19,7 +19,7 @@ import torch
 
 from . import _lib
 from .head import _check_cuda_f32, _prec, _proto_2d
-from .push import PUSH_DEFAULT_PRECISION, unpack
+from .push import default_search_precision, unpack
 
 
 def pil_nearest_lut(in_size, out_size):
@@ -77,7 +77,7 @@ def image_minima(z, labels, prototypes, proto_class, precision=None):
     pc = proto_class.to(device=dev, dtype=torch.int32).contiguous()
     mask = void_mask(labels, h, w)
     packed = torch.full((n, N), _lib.PUSH_NONE, device=dev, dtype=torch.int64)
-    prec = _prec(precision or PUSH_DEFAULT_PRECISION)
+    prec = _prec(precision or default_search_precision(K, N))
     with torch.cuda.device(dev):                             # one launch: per-(image, prototype) minima
         rc = lib.adlm_push_scan_images(_lib.ptr(z), n, K, h * w, _lib.ptr(mask), _lib.ptr(P), N, _lib.ptr(pc),
                                        c_int(prec), _lib.ptr(packed), _lib.stream_ptr())
@@ -168,3 +168,134 @@ def prototypes_to_prune(nearest_labels, proto_class, prune_threshold):
     pc = np.asarray(proto_class.detach().cpu() if torch.is_tensor(proto_class) else proto_class).astype(np.int64)
     lab = np.asarray(nearest_labels)
     return [int(j) for j in range(len(pc)) if int(np.sum(lab[j] == pc[j])) < prune_threshold]
+
+
+# ------------------------------------------------------------------------------ the reference entry points
+def find_k_nearest_patches_to_prototypes(dataset,
+                                         prototype_network_parallel,
+                                         k=5,
+                                         preprocess_input_function=None,
+                                         full_save=False,
+                                         root_dir_for_saving_images='./nearest',
+                                         log=print,
+                                         prototype_activation_function_in_numpy=None,
+                                         chunk=16):
+    """Drop-in for find_nearest.find_k_nearest_patches_to_prototypes (find_nearest.py:66-342): same arguments (plus
+    `chunk`, images per scan launch), same return value — the (N,k) array of patch class ids, nearest first (-1 void;
+    -2 where the dataset offers fewer than k candidates, which the reference cannot produce because it keeps void-only
+    images at distance + 1e7).  Images are read exactly as the reference does (RGB, margin crop, ImageNet
+    normalisation — `preprocess_input_function` is unused there too), pushed through `conv_features`, and scanned on
+    the device; only the N*k winners have their label regions read back.  With `full_save` the numeric artefacts are
+    written (`<root>/<j>/class_id.npy`, `<root>/full_class_id.npy`); the PNG dumps of find_nearest.py:228-325 are
+    visualisation and are not produced.  Under torch.distributed every rank scans a contiguous slice of the images
+    and all ranks return the same array."""
+    import os
+    import time
+    import torch.distributed as dist
+    from .push import _load_sample, _to_normalized_tensor
+    ppnet = prototype_network_parallel.module if hasattr(prototype_network_parallel, 'module') \
+        else prototype_network_parallel
+    prototype_network_parallel.eval()
+    log('find nearest patches')
+    start = time.time()
+    world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+    rank = dist.get_rank() if world > 1 else 0
+    img_ids = list(dataset.img_ids)
+    n_total = len(img_ids)
+    per = (n_total + world - 1) // world
+    lo, hi = min(n_total, rank * per), min(n_total, (rank + 1) * per)
+    proto_class = ppnet.proto_class()
+    dev = ppnet.prototype_vectors.device
+    N = ppnet.num_prototypes
+    prec = ppnet.head_precision if ppnet.head_precision in ("fp32", "tf32x3") else None
+    rows, hw = [], None
+    with torch.no_grad():
+        for c0 in range(lo, hi, chunk):
+            zs, labs = [], []
+            for idx in range(c0, min(hi, c0 + chunk)):
+                img, ann = _load_sample(dataset, img_ids[idx])
+                zs.append(ppnet.conv_features(_to_normalized_tensor(img).unsqueeze(0).to(dev)).float())
+                labs.append(torch.from_numpy(np.ascontiguousarray(ann).astype(np.uint8)))
+            if len({tuple(t.shape) for t in zs}) != 1 or len({tuple(t.shape) for t in labs}) != 1:
+                raise NotImplementedError("all images of one search must share the image and feature-map size")
+            z = torch.cat(zs)
+            if hw is None:
+                hw = (z.shape[2], z.shape[3])
+            rows.append(image_minima(z, torch.stack(labs).to(dev), ppnet.prototype_vectors, proto_class, prec))
+    packed = torch.cat(rows) if rows else torch.full((0, N), _lib.PUSH_NONE, device=dev, dtype=torch.int64)
+    if world > 1:
+        t = torch.tensor(list(hw or (0, 0)), device=dev, dtype=torch.int64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        hw = (int(t[0]), int(t[1]))
+    cache = {}
+
+    def label_of(i):
+        if i not in cache:
+            cache[i] = np.asarray(_load_sample(dataset, img_ids[lo + i])[1]).astype(np.uint8)
+        return cache[i]
+    pc_np = proto_class.detach().cpu().numpy().astype(np.int64)
+    res = top_k_and_labels(packed, k, label_of, pc_np, hw[0], hw[1], image_base=lo,
+                           n_total=n_total if world > 1 else None)
+    labels_all_prototype = res["labels"]
+    if full_save and rank == 0:
+        for j in range(N):
+            d = os.path.join(root_dir_for_saving_images, str(j))
+            os.makedirs(d, exist_ok=True)
+            np.save(os.path.join(d, 'class_id.npy'), labels_all_prototype[j])
+        np.save(os.path.join(root_dir_for_saving_images, 'full_class_id.npy'), labels_all_prototype)
+    log('\tfind nearest patches time: \t{0}'.format(time.time() - start))
+    return labels_all_prototype
+
+
+def prune_prototypes(dataset,
+                     prototype_network_parallel,
+                     k,
+                     prune_threshold,
+                     preprocess_input_function,
+                     original_model_dir,
+                     epoch_number,
+                     log=print,
+                     copy_prototype_imgs=True):
+    """Drop-in for prune.prune_prototypes (prune.py:11-110), as segmentation/run_pruning.py:60-69 calls it: k nearest
+    patches of every prototype, prune those with fewer than `prune_threshold` own-class patches among them, write
+    `pruned_prototypes_epoch{e}_k{k}_pt{t}/prune_info.npy` and `prototypes_to_keep.json`, shrink the network in
+    place; returns prune_info (pruned index, its class).  The copies of the prototype images (prune.py:73-108) are made
+    for the files that exist."""
+    import json
+    import os
+    import shutil
+    ppnet = prototype_network_parallel.module if hasattr(prototype_network_parallel, 'module') \
+        else prototype_network_parallel
+    nearest = find_k_nearest_patches_to_prototypes(
+        dataset=dataset, prototype_network_parallel=prototype_network_parallel, k=k,
+        preprocess_input_function=preprocess_input_function, full_save=True,
+        root_dir_for_saving_images=os.path.join(original_model_dir, 'img'), log=log)
+    original_num_prototypes = ppnet.num_prototypes
+    pc = ppnet.proto_class().cpu().numpy().astype(np.int64)
+    to_prune = prototypes_to_prune(nearest, pc, prune_threshold)
+    log('k = {}, prune_threshold = {}'.format(k, prune_threshold))
+    log('{} prototypes will be pruned'.format(len(to_prune)))
+    prune_info = np.hstack((np.array(to_prune, dtype=np.int64).reshape(-1, 1), pc[to_prune].reshape(-1, 1)))
+    out_dir = os.path.join(original_model_dir, 'pruned_prototypes_epoch{}_k{}_pt{}'.format(epoch_number, k, prune_threshold))
+    os.makedirs(out_dir, exist_ok=True)
+    np.save(os.path.join(out_dir, 'prune_info.npy'), prune_info)
+    ppnet.prune_prototypes(to_prune)
+    keep = list(sorted(set(range(original_num_prototypes)) - set(to_prune)))
+    log(f'Prototypes to keep: {keep}')
+    with open(os.path.join(original_model_dir, 'prototypes_to_keep.json'), 'w') as fp:
+        json.dump(keep, fp)
+    if copy_prototype_imgs:
+        src_dir = os.path.join(original_model_dir, 'img', 'epoch-%d' % epoch_number)
+        dst_dir = os.path.join(out_dir, 'img', 'epoch-%d' % epoch_number)
+        os.makedirs(dst_dir, exist_ok=True)
+        for new, old in enumerate(keep):
+            for pat in ('prototype-img%d.png', 'prototype-img-original%d.png',
+                        'prototype-img-original_with_self_act%d.png', 'prototype-self-act%d.npy'):
+                src = os.path.join(src_dir, pat % old)
+                if os.path.exists(src):
+                    shutil.copyfile(src, os.path.join(dst_dir, pat % new))
+        for name in ('bb%d.npy' % epoch_number, 'bb-receptive_field%d.npy' % epoch_number):
+            src = os.path.join(src_dir, name)
+            if os.path.exists(src):
+                np.save(os.path.join(dst_dir, name), np.load(src)[keep])
+    return prune_info

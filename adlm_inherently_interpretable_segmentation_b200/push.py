@@ -30,6 +30,14 @@ from .head import _check_cuda_f32, _prec, _proto_2d
 
 #: the search must reproduce the fp32 argmin: tcgen05 3xTF32 (fp32-class distances) unless told otherwise
 PUSH_DEFAULT_PRECISION = "tf32x3"
+#: operand budget of the tcgen05 scan (csrc/tc_push.cu); beyond it the library refuses the tensor-core modes
+TC_SCAN_MAX_K, TC_SCAN_MAX_N = 64, 224
+
+
+def default_search_precision(K, N):
+    """precision used when the caller does not name one: 3xTF32 on the tensor cores where that kernel exists, else the
+    fp32 CUDA-core scan — both fp32-class, chosen HERE and visibly rather than rerouted inside the library"""
+    return PUSH_DEFAULT_PRECISION if (K <= TC_SCAN_MAX_K and N <= TC_SCAN_MAX_N) else "fp32"
 
 NORM_MEAN = (0.485, 0.456, 0.406)   # segmentation/constants.py:6-7 (find_nearest.to_normalized_tensor)
 NORM_STD = (0.229, 0.224, 0.225)
@@ -85,7 +93,7 @@ class PushSearch:
         self.proto_class = proto_class.to(device=self.device, dtype=torch.int32).contiguous()
         if int(self.proto_class.max()) >= _lib.MAX_PUSH_CLASSES:
             raise NotImplementedError(f"push supports up to {_lib.MAX_PUSH_CLASSES} classes (uint32 patch mask)")
-        self.prec = _prec(precision or PUSH_DEFAULT_PRECISION)
+        self.prec = _prec(precision or default_search_precision(self.K, self.N))
         self.packed = torch.full((self.N,), _lib.PUSH_NONE, device=self.device, dtype=torch.int64)
         self._lut_cache = {}
         self.hw = None
@@ -295,7 +303,7 @@ def push_prototypes(dataset,
     proto_class = ppnet.proto_class()
     # The winners must be the fp32 arg-min (push.py:259-265): a model trained with head_precision 'tf32' still
     # searches with fp32-class distances, exactly as model._forward_min_pool does.
-    prec = ppnet.head_precision if ppnet.head_precision in ("fp32", "tf32x3") else PUSH_DEFAULT_PRECISION
+    prec = ppnet.head_precision if ppnet.head_precision in ("fp32", "tf32x3") else None
     search = PushSearch(ppnet.prototype_vectors, proto_class, precision=prec)
     dev = search.device
     img_ids = list(dataset.img_ids)

@@ -214,3 +214,50 @@ def test_push_prototypes_end_to_end(tmp_path, head_precision):
     dmin = d.flatten(2).min(dim=2).values.min(dim=0).values.cpu().numpy()
     pushed = np.abs(got).sum(1) > 0
     assert pushed.sum() == len(ui) - 1 and dmin[pushed].max() <= 16 * 2.0 ** -19
+
+
+def test_find_nearest_and_prune_drop_ins(tmp_path):
+    """find_nearest.find_k_nearest_patches_to_prototypes (find_nearest.py:66-73) and prune.prune_prototypes
+    (prune.py:11-20) with the reference's own signatures, as segmentation/run_pruning.py:60-69 calls them: a dataset on
+    disk, a DataParallel-style wrapper exposing `.module`"""
+    from adlm_inherently_interpretable_segmentation_b200 import nearest
+    torch.manual_seed(3)
+    rng = np.random.default_rng(11)
+    n_img, H, W, K, N, C, k = 7, 64, 96, 16, 30, 3, 3
+    imgs = rng.integers(0, 255, size=(n_img, H, W, 3), dtype=np.uint8)
+    labels = synth.block_labels(n_img, H, W, C, block=8, seed=13)
+    ds = _DiskDataset(str(tmp_path), imgs, labels)
+    net = model.PPNet(features=Backbone(K), img_size=64, prototype_shape=(N, K, 1, 1), proto_layer_rf_info=None,
+                      num_classes=C, add_on_layers_type='deeplab_simple', patch_classification=True).cuda()
+
+    class Wrapper(nn.Module):
+        def __init__(self, m):
+            super().__init__()
+            self.module = m
+    wrapped = Wrapper(net)
+    with torch.no_grad():
+        feats = np.stack([net.conv_features(push._to_normalized_tensor(imgs[i]).unsqueeze(0).cuda())[0].cpu().numpy()
+                          for i in range(n_img)])
+    P0 = net.prototype_vectors.detach().cpu().numpy().reshape(N, K)
+    pc = np.arange(N) // (N // C)
+    ol, od, oi, op = orc.find_k_nearest(feats, P0, labels, pc, k)
+    logs = []
+    got = nearest.find_k_nearest_patches_to_prototypes(ds, wrapped, k=k, preprocess_input_function=None,
+                                                       full_save=False, log=logs.append, chunk=3)
+    assert got.shape == (N, k) and any("find nearest patches time" in str(l) for l in logs)
+    # a different image may win only on a distance tie inside the fp32 tolerance
+    same = np.all(got == ol, axis=1)
+    assert same.mean() >= 0.9
+    out_dir = os.path.join(str(tmp_path), "run")
+    os.makedirs(out_dir)
+    expect_prune = orc.prototypes_to_prune(got, pc, 2)
+    info = nearest.prune_prototypes(dataset=ds, prototype_network_parallel=wrapped, k=k, prune_threshold=2,
+                                    preprocess_input_function=None, original_model_dir=out_dir, epoch_number=0,
+                                    log=logs.append, copy_prototype_imgs=False)
+    assert [int(v) for v in info[:, 0]] == expect_prune and np.array_equal(info[:, 1], pc[expect_prune])
+    assert net.num_prototypes == N - len(expect_prune)
+    keep = json.load(open(os.path.join(out_dir, "prototypes_to_keep.json")))
+    assert keep == sorted(set(range(N)) - set(expect_prune))
+    assert np.array_equal(np.load(os.path.join(out_dir, "pruned_prototypes_epoch0_k3_pt2", "prune_info.npy")), info)
+    assert np.array_equal(np.load(os.path.join(out_dir, "img", "full_class_id.npy")), got)
+    assert np.array_equal(np.load(os.path.join(out_dir, "img", "5", "class_id.npy")), got[5])
