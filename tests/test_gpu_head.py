@@ -136,7 +136,9 @@ def _check_full_forward(g, prec, out, dims, dist_stats=None):
     # regime B: prototypes ON pixels -> the reference's own fp32 noise at d ~ 0 dominates (tests/parity.py)
     ltol = ((2e-2 if regime_b else 2e-4) + rel) * float(g["logits_absmax"])
     if prec == "tf32" and regime_b:
-        ltol = 0.35 * float(g["logits_absmax"])            # a matched pixel's similarity moves by O(1) in one TF32 pass
+        # z == p gives d == 0 exactly in this mode too (|p|^2 is taken of the rounded vector), so a matched pixel's
+        # similarity is as well defined as in fp32; measured 2.1e-2 at |logits| <= 11.5
+        ltol = 3e-2 * float(g["logits_absmax"])
     e = float(np.abs(logits[:, ::stride] - g["logits_sample"]).max())
     assert np.array_equal(amax, logits.argmax(axis=2))
     bad = amax != g["argmax"]

@@ -17,7 +17,9 @@ pytestmark = pytest.mark.gpu
 # (loss tolerance, gradient tolerance) per fixture: regime B sits prototypes ON pixels (d == 0), where the
 # reference's own fp32 distances carry ~2.5e-5 noise against ds/dd = -1e4 (tests/test_oracle_golden.py)
 STEP_TOL = {"step_small_A": (2e-5, 2e-4), "step_novoid": (2e-5, 2e-4), "step_small_B": (2e-3, 0.15)}
-PREC_SCALE = {"fp32": 1.0, "tf32x3": 1.0, "tf32": 50.0}
+# tf32: gradients measured on the B200 against the reference's _step are off by 0.4-1.6e-3 of the largest entry
+# (profiles/r2_pytest_gpu.log: step_small_A 1.6e-3, step_cfg2 1.3e-3); 15 x 2e-4 = 3e-3 is twice that
+PREC_SCALE = {"fp32": 1.0, "tf32x3": 1.0, "tf32": 15.0}
 
 
 def run_step(g, prec, **kw):
