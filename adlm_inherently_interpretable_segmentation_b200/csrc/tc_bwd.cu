@@ -11,6 +11,8 @@
 // (zc = z - 1/2, Pc = P - 1/2: both formulas are invariant under the common shift.)
 // A contraction over the TMEM lane index is impossible (lanes are the M index of an A operand), and MN-major
 // tf32 shared-memory operands do not work on this part, hence one kernel per orientation.
+#include <stdlib.h>
+
 #include "tc_head.cuh"
 #include "tc_common.cuh"
 
@@ -56,6 +58,7 @@ struct TcBwdParams {
   int Npad, C8;
   long long M;
   int num_tiles;
+  int exp_flags;          // debugging aid (ADLM_FUSED_EXP): 1 no dZ write-out, 2 no dZ^T MMAs, 4 no G shared-memory stores
 };
 
 // ------------------------------------------------------------------------------------------------ dZ
@@ -924,6 +927,8 @@ k_reduce_partials(const float* __restrict__ partials, int n_parts, int Npad2, in
   }
 }
 
+#include "tc_bwd_fused.cuh"
+
 int g_sms = 0;
 int sm_count() {
   if (g_sms == 0) {
@@ -939,11 +944,63 @@ bool tc_bwd_supported(const HeadShape& s, int prec_mode) {
   return prec_mode == ADLM_PREC_TF32 && s.K <= 64 && s.N <= 192 && s.C <= 32;
 }
 
+// The fused backward (tc_bwd_fused.cuh) is selected by ADLM_BWD_FUSED=1 / 0 in the environment; the default below is
+// whichever of the two measured faster on the B200 (profiles/r2_*).  ADLM_BWD_TWO_KERNELS=1 also forces the two-kernel form.
+constexpr bool FUSED_BWD_DEFAULT = false;
+bool use_fused_bwd() {
+  static const bool v = [] {
+    const char* two = getenv("ADLM_BWD_TWO_KERNELS");
+    if (two != nullptr && two[0] == '1') return false;
+    const char* e = getenv("ADLM_BWD_FUSED");
+    if (e != nullptr && (e[0] == '0' || e[0] == '1')) return e[0] == '1';
+    return FUSED_BWD_DEFAULT;
+  }();
+  return v;
+}
+
+template <int KP, int NB>
+int launch_fused(TcBwdParams prm, const StepFinalize& fin, float* dP, float* dW, cudaStream_t st) {
+  using L = FuSmem<KP, NB>;
+  const size_t bytes = L::total(prm.C8);
+  if (bytes > 227 * 1024) {
+    set_error("tc_head_bwd: %zu bytes of shared memory needed (> 227 KB) for K=%d N=%d C=%d", bytes, prm.K, prm.N, prm.C);
+    return ADLM_E_UNSUPPORTED;
+  }
+  prm.num_tiles = (int)((prm.M + FT - 1) / FT);
+  {
+    static const int flags = [] { const char* e = getenv("ADLM_FUSED_EXP"); return e ? atoi(e) : 0; }();
+    prm.exp_flags = flags;
+  }
+  const int grid = prm.num_tiles < sm_count() ? prm.num_tiles : sm_count();
+  const bool after_kld = prm.own_grad != nullptr;      // step path: the launch before this one is k_kld
+  ADLM_CUDA(cudaFuncSetAttribute(k_tc_bwd_fused<KP, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  ADLM_CUDA(launch_maybe_pdl(after_kld, k_tc_bwd_fused<KP, NB>, dim3(grid), dim3(FU_THREADS), bytes, st, prm));
+  ADLM_LAUNCH_CHECK();
+  const int total = prm.N * prm.K + prm.C * prm.N;
+  k_reduce_partials<<<(total * 4 + 255) / 256, 256, 0, st>>>(prm.partials, grid, NB * 128, KP, prm.N, prm.K, prm.C, dP, dW,
+                                                             prm.W, prm.proto_class, fin);
+  ADLM_LAUNCH_CHECK();
+  return ADLM_OK;
+}
+
 template <int KP>
 int launch_bwd(TcBwdParams prm, float* dP, float* dW, const StepFinalize& fin, void* workspace, size_t workspace_bytes,
                cudaStream_t st) {
   const int grid = prm.num_tiles < sm_count() ? prm.num_tiles : sm_count();
   KernelTimer timer(ADLM_K_HEAD_BWD, st);
+  // dZ together with dP / dW and no upstream gradient on the distance / similarity maps (the training step, and
+  // autograd through the logits): the fused kernel forms G once for all three
+  if (use_fused_bwd() && prm.dz != nullptr && (dP != nullptr || dW != nullptr) && prm.dsim == nullptr &&
+      prm.ddist == nullptr && prm.C8 <= 24) {
+    const int NB = (prm.N + 127) / 128, Npad2 = NB * 128;
+    const size_t per = ((size_t)Npad2 * KP + (size_t)Npad2 * 32) * sizeof(float);
+    if (workspace == nullptr || workspace_bytes < per * grid) {
+      set_error("tc_head_bwd: workspace too small (%zu < %zu)", workspace_bytes, per * grid);
+      return ADLM_E_WORKSPACE;
+    }
+    prm.partials = static_cast<float*>(workspace);
+    return NB == 1 ? launch_fused<KP, 1>(prm, fin, dP, dW, st) : launch_fused<KP, 2>(prm, fin, dP, dW, st);
+  }
   bool dz_launched = false;
   if (prm.dz != nullptr) {
     using L = DzSmem<KP>;
@@ -1032,6 +1089,7 @@ int tc_head_bwd(const HeadShape& s, int prec_mode, const float* z, const float* 
   prm.C8 = (s.C + 7) & ~7;
   prm.M = (long long)s.B * s.HW;
   prm.num_tiles = (int)((prm.M + TILE - 1) / TILE);
+  prm.exp_flags = 0;
   if (s.K <= 32) return launch_bwd<32>(prm, dP, dW, ex.fin, workspace, workspace_bytes, st);
   return launch_bwd<64>(prm, dP, dW, ex.fin, workspace, workspace_bytes, st);
 }
