@@ -43,6 +43,8 @@ SIGNATURES = {
                                   c_void_p, c_void_p, c_size_t, c_void_p]),
     "adlm_step_counts": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_int,
                                  c_void_p, c_void_p, c_size_t, c_void_p]),
+    "adlm_step_counts_noalloc": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_int,
+                                         c_void_p, c_void_p]),
     "adlm_patch_class_mask": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int,
                                       c_void_p, c_void_p]),
     "adlm_push_scan": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p,

@@ -292,6 +292,13 @@ int adlm_step_counts(const int32_t* target, int B, int HW, const int32_t* proto_
                           (cudaStream_t)stream);
 }
 
+int adlm_step_counts_noalloc(const int32_t* target, int B, int HW, const int32_t* proto_class, int N, int C,
+                             int ignore_void, int32_t* counts_out, void* stream) {
+  ADLM_CHECK_ARG(target && proto_class && counts_out, "null pointer argument");
+  ADLM_CHECK_ARG(B > 0 && HW > 0 && N > 0 && C > 0, "non-positive size");
+  return step_counts_noalloc_impl(target, B, HW, proto_class, N, C, ignore_void, counts_out, (cudaStream_t)stream);
+}
+
 int adlm_eval_upsample(const float* logits, const float* dist, int B, int h, int w, int C, int N, int H, int Wimg,
                        const int32_t* y0, const float* ly, const int32_t* x0, const float* lx, int patch_rows,
                        int patch_cols, uint8_t* pred, int16_t* nearest, const uint8_t* labels,

@@ -238,6 +238,8 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
                       double* scalars, void* workspace, const DpComm* comm, float* z_out, cudaStream_t st);
 int step_counts_impl(const int32_t* target, int B, int HW, const int32_t* proto_class, int N, int C,
                      int ignore_void, int32_t* counts_out, void* workspace, cudaStream_t st);
+int step_counts_noalloc_impl(const int32_t* target, int B, int HW, const int32_t* proto_class, int N, int C,
+                             int ignore_void, int32_t* counts_out, cudaStream_t st);
 
 // push (push.cu)
 int patch_class_mask_impl(const uint8_t* labels, int n_img, int H, int Wimg, const int32_t* row_lut,

@@ -641,4 +641,53 @@ int step_counts_impl(const int32_t* target, int B, int HW, const int32_t* proto_
   return ADLM_OK;
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// adlm_step_counts_noalloc: the loss normalisers of a batch shard WITHOUT a caller-provided workspace.  No counterpart
+// in the reference; added for callers that cannot allocate (code under CUDA
+// graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The scratch of k_step_prepare (per-image
+// label histograms, class sizes, prototype ranks, accumulators) lives in a file-scope device array of fixed size that
+// every GPU loading the library holds until exit.  ALL calls share it and it keeps the last call's contents: the kernel
+// overwrites every word it later reads (nothing has to start at zero; the ticket counter it uses is reset by the
+// kernel itself), but two calls that overlap on the GPU (different streams) race on it.
+constexpr int NOALLOC_MAX_B = ADLM_NOALLOC_MAX_B, NOALLOC_MAX_N = ADLM_NOALLOC_MAX_N;
+constexpr size_t NA_HIST = 0;                                                                   // int [B][C+1]
+constexpr size_t NA_CLS = NA_HIST + ((size_t)NOALLOC_MAX_B * (ADLM_MAX_C + 1) * 4 + 255) / 256 * 256;   // int [C]
+constexpr size_t NA_RANK = NA_CLS + ((size_t)ADLM_MAX_C * 4 + 255) / 256 * 256;                 // int32 [N]
+constexpr size_t NA_ACCUM = NA_RANK + ((size_t)NOALLOC_MAX_N * 4 + 255) / 256 * 256;            // double [4]
+constexpr size_t NA_BYTES = NA_ACCUM + 256;
+static_assert(NA_BYTES == ADLM_NOALLOC_SCRATCH_BYTES, "include/adlm_head.h states the size of the static scratch");
+static __device__ __align__(256) unsigned char g_counts_scratch[NA_BYTES];
+
+// device address of the scratch array, looked up once per device with that device current (in host code the
+// array's NAME is only a host-side stand-in for the symbol, never a device address)
+static void* g_counts_scratch_ptr[64] = {};
+
+int step_counts_noalloc_impl(const int32_t* target, int B, int HW, const int32_t* proto_class, int N, int C,
+                             int ignore_void, int32_t* counts_out, cudaStream_t st) {
+  if (B > NOALLOC_MAX_B || N > NOALLOC_MAX_N || C > ADLM_MAX_C) {
+    set_error("adlm_step_counts_noalloc: B=%d N=%d C=%d exceed the static scratch (B <= %d, N <= %d, C <= %d); "
+              "use adlm_step_counts with a workspace", B, N, C, NOALLOC_MAX_B, NOALLOC_MAX_N, ADLM_MAX_C);
+    return ADLM_E_UNSUPPORTED;
+  }
+  int dev = 0;
+  ADLM_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) {
+    set_error("adlm_step_counts_noalloc: device index %d out of range", dev);
+    return ADLM_E_UNSUPPORTED;
+  }
+  void* base = __atomic_load_n(&g_counts_scratch_ptr[dev], __ATOMIC_ACQUIRE);
+  if (base == nullptr) {
+    ADLM_CUDA(cudaGetSymbolAddress(&base, g_counts_scratch));
+    __atomic_store_n(&g_counts_scratch_ptr[dev], base, __ATOMIC_RELEASE);     // same value from every thread
+  }
+  char* b8 = static_cast<char*>(base);
+  const int slot = (int)(g_next_ticket_slot.fetch_add(1u, std::memory_order_relaxed) % TICKET_SLOTS);
+  k_step_prepare<<<B, 1024, 0, st>>>(target, proto_class, B, HW, C, N, ignore_void, slot,
+                                     reinterpret_cast<int*>(b8 + NA_HIST), reinterpret_cast<int*>(b8 + NA_CLS),
+                                     counts_out, reinterpret_cast<int32_t*>(b8 + NA_RANK),
+                                     reinterpret_cast<double*>(b8 + NA_ACCUM), DpComm{}, DpLayout{});
+  ADLM_LAUNCH_CHECK();
+  return ADLM_OK;
+}
+
 }  // namespace adlm

@@ -193,6 +193,25 @@ ADLM_API int adlm_step_counts(const int32_t* target, int B, int HW,
                      int32_t* counts_out, void* workspace, size_t workspace_bytes, void* stream);
 
 /*
+ * adlm_step_counts without a workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same inputs and the same counts_out as adlm_step_counts; the kernel's
+ * scratch (label histograms, class sizes, prototype ranks) lives in a static device array of
+ * ADLM_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit.  Limits: B <= ADLM_NOALLOC_MAX_B,
+ * N <= ADLM_NOALLOC_MAX_N, C <= ADLM_MAX_C, device index < 64; larger sizes return ADLM_E_UNSUPPORTED (use
+ * adlm_step_counts).  All calls on a device share the array, which keeps the last call's contents; nothing in it has
+ * to start at zero (the kernel overwrites what it reads), but calls that OVERLAP on the GPU (different streams,
+ * or the same stream from two threads without ordering) race on it — serialise them.  The first call on a device
+ * looks up the array's device address (cudaGetSymbolAddress); no call allocates or frees memory.
+ */
+#define ADLM_NOALLOC_MAX_B 256
+#define ADLM_NOALLOC_MAX_N 1024
+#define ADLM_NOALLOC_SCRATCH_BYTES 136960
+ADLM_API int adlm_step_counts_noalloc(const int32_t* target, int B, int HW,
+                             const int32_t* proto_class, int N, int C, int ignore_void,
+                             int32_t* counts_out, void* stream);
+
+/*
  * Data-parallel fused step over peer-mapped memory (one process per GPU, all GPUs of one NVLink domain).
  * Same arguments and results as adlm_step_fwd_bwd on this rank's image shard, except that
  *   - the two loss normalisers are summed over ranks inside the step's prologue kernel,
