@@ -58,7 +58,7 @@ struct TcBwdParams {
   int Npad, C8;
   long long M;
   int num_tiles;
-  int exp_flags;          // debugging aid (ADLM_FUSED_EXP): 1 no dZ write-out, 2 no dZ^T MMAs, 4 no G shared-memory stores
+  int exp_flags;          // timing aid of the fused backward (ADLM_FUSED_EXP; results wrong): 1 no dZ write-out, 2 no dZ MMAs, 4 no G shared-memory stores
 };
 
 // ------------------------------------------------------------------------------------------------ dZ

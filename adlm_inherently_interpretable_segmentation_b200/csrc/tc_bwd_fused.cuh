@@ -7,15 +7,16 @@
 //                        TMEM buffer (A operands) and G also into shared memory as a K-major operand [pixel][prototype]
 //     dP += G Z          .ts MMA, persistent TMEM accumulator [prototype][depth]     (contraction over pixels)
 //     dW += S dL         .ts MMA, persistent TMEM accumulator [prototype][class]
-//     dZ^T = [Pc^T; 1] G SS MMA, A = transposed prototypes + a row of ones, B = the shared-memory G: rows 0..K-1 are
-//                        (G P)^T, row K is rowsum(G) — the contraction over prototypes that the two-kernel version
-//                        needed a second orientation (and a second evaluation of D, Gl and G) for
-//   dZ = 2 (rowsum(G) zc - G Pc) leaves through three writer warps (lanes = depth, tcgen05.ld.16x256b so that one
-//   store instruction covers 8 rows x 32 bytes): z is re-read from L2.
+//     dZ' = G [Pc | 1]     SS MMA, A = the shared-memory G (rows = pixels), B = transposed prototypes + a row of ones:
+//                        columns 0..K-1 are G P, column K is rowsum(G) — the contraction over prototypes that the
+//                        two-kernel version needed a second orientation (and a second evaluation of D, Gl, G) for
+//   dZ = 2 (rowsum(G) zc - G Pc) leaves through two writer warps (thread = pixel: coalesced loads of z from L2 and
+//   stores of dz).  (A first version kept depth in the lanes: its stores touched 8-32 lines per instruction and the
+//   write-out alone took 20-50 k cycles per tile.)
 //
 // Warp roles (16 warps x 128 registers = the whole register file): 0-7 epilogue (lane quarter = warp % 4, column half =
-// warp / 4), 8-11 builder (pixel-side operands of the next tile), 12-14 writer (dZ^T of the finished tile: lane quarters
-// 0 and 1 hold the depth rows, quarter 2 the ones row), 15 MMA issuer.  Every mbarrier completes once per tile or once
+// warp / 4), 8-11 builder (pixel-side operands of the next tile), 12-13 writer (dZ of the finished tile: pixels in the
+// lanes of quarters 0 and 1), 14 spare, 15 MMA issuer.  Every mbarrier completes once per tile or once
 // per use of a TMEM buffer, and every waiter takes part in what completes it next (barrier lesson 2).
 //
 // Shared memory (KP = 64, two prototype blocks, C <= 24): 128-byte-swizzled Zt 16 K + dLt 8 K + G block 0 32 K +
@@ -73,7 +74,6 @@ __global__ void __launch_bounds__(FU_THREADS, 1) k_tc_bwd_fused(const TcBwdParam
   int* imgs = reinterpret_cast<int*>(misc + 768);                       // [slot][FT]
   int* pixs = reinterpret_cast<int*>(misc + 1280);                      // [slot][FT]
   uint32_t* clsm = reinterpret_cast<uint32_t*>(misc + 1792);            // [slot][32 classes][2 words]
-  float* rss = reinterpret_cast<float*>(misc + 2304);                   // [FT] rowsum(G) of the tile being written out
   uint64_t* bars = reinterpret_cast<uint64_t*>(misc + 2560);
   uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 12);
 
@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(FU_THREADS, 1) k_tc_bwd_fused(const TcBwdParam
     mbar_init(smem_u32(&bars[5]), 256);
     mbar_init(smem_u32(&bars[6]), 128);   // full_t: transposed pixel operands written
     mbar_init(smem_u32(&bars[7]), 1);     // k_free: the tile's last distance MMA has read ZkB / dLkB
-    mbar_init(smem_u32(&bars[8]), 96);    // dz_free: dZ^T of the tile read out of TMEM (three writer warps)
+    mbar_init(smem_u32(&bars[8]), 64);    // dz_free: dZ of the tile read out of TMEM (two writer warps)
     mbar_init(smem_u32(&bars[9]), 256);   // tile_seen: every epilogue thread has observed full_k of the tile (so the
                                           //   next full_k cannot complete behind a thread's back, and the metadata
                                           //   slot of the tile before is no longer read)
@@ -189,7 +189,13 @@ __global__ void __launch_bounds__(FU_THREADS, 1) k_tc_bwd_fused(const TcBwdParam
   asm volatile("griddepcontrol.launch_dependents;");
 
   const uint32_t tmem_base = *tmem_base_s;
-  const uint32_t tP0 = tmem_base + 256, tW0 = tmem_base + 256 + NB * KP, tZ = tmem_base + 448;
+  // TMEM columns: 0..255 two unit buffers (D^T | Gl^T, 64 + 64 each); dP accumulators [prototype][KP] from 256; dW
+  // accumulators [prototype][32] behind them, the two blocks WSTR = 24 columns apart (C8 <= 24: the upper 8 columns of
+  // a block are exact zeros, the accumulators start zeroed and every dW MMA accumulates, so a block adds 0.0 to the
+  // columns it shares); dZ [pixel][80] at 432..511: depth 0..63 | rowsum(G) | 7 zero columns | 8 unused.  Columns
+  // 432..439 are shared by dW block 1's zero columns (which only ever add 0.0) and dZ depth 0..7.
+  constexpr int WSTR = NB == 2 ? 24 : 32, ZN = 80;
+  const uint32_t tP0 = tmem_base + 256, tW0 = tmem_base + 256 + NB * KP, tZ = tmem_base + 432;
   auto tDb = [&](int b) { return tmem_base + (uint32_t)b * 128u; };
   const uint32_t bar_full = smem_u32(&bars[0]), bar_free = smem_u32(&bars[1]), bar_acc0 = smem_u32(&bars[2]),
                  bar_gs0 = smem_u32(&bars[4]), bar_full_t = smem_u32(&bars[6]), bar_kfree = smem_u32(&bars[7]),
@@ -262,116 +268,94 @@ __global__ void __launch_bounds__(FU_THREADS, 1) k_tc_bwd_fused(const TcBwdParam
             dLkB[((size_t)(c >> 2) * FT + px) * 4 + (c & 3)] = x[j];
           }
         }
-        dlv[v] = make_float4(x[0], x[1], x[2], x[3]);
       }
       asm volatile("cp.async.wait_all;" ::: "memory");
       fence_async_smem();
       mbar_arrive(bar_full);
       if (warp == 8) DP_PHASE(0, 3 + it * 8);
+      // The next tile's global loads go out now: the registers are free (step T below reads this tile's operands back
+      // from the K-major copies this thread has just written), and the loads travel while the thread waits.
+      prefetch(it + 1);
+      if (warp == 8) DP_PHASE(0, 4 + it * 8);
       // ---- step T: the previous tile's accumulate / dZ^T MMAs have retired
       if (it > 0) mbar_wait(bar_free, (uint32_t)(it - 1) & 1u);
-      if (warp == 8) DP_PHASE(0, 4 + it * 8);
+      if (warp == 8) DP_PHASE(0, 5 + it * 8);
 #pragma unroll
-      for (int k = 0; k < KH; ++k) ZtB[off_sw128(bkh * KH + k, bpx, KP)] = zr[k];
+      for (int k4 = 0; k4 < KH / 4; ++k4) {
+        const float4 v = *reinterpret_cast<const float4*>(ZkB + ((size_t)(bkh * (KH / 4) + k4) * FT + bpx) * 4);
+        const int k = bkh * KH + k4 * 4;
+        ZtB[off_sw128(k, bpx, KP)] = v.x;
+        ZtB[off_sw128(k + 1, bpx, KP)] = v.y;
+        ZtB[off_sw128(k + 2, bpx, KP)] = v.z;
+        ZtB[off_sw128(k + 3, bpx, KP)] = v.w;
+      }
 #pragma unroll
       for (int v = 0; v < DLV; ++v) {
-        const float x[4] = {dlv[v].x, dlv[v].y, dlv[v].z, dlv[v].w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const uint32_t pc = dle[v * 4 + j];
-          if (pc != 0xffffffffu) dLtB[off_sw128((int)(pc & 255u), (int)(pc >> 8), 32)] = x[j];
+          if (pc != 0xffffffffu) {
+            const int px = (int)(pc >> 8), c = (int)(pc & 255u);
+            dLtB[off_sw128(c, px, 32)] = dLkB[((size_t)(c >> 2) * FT + px) * 4 + (c & 3)];
+          }
         }
       }
       fence_async_smem();
       mbar_arrive(bar_full_t);
-      if (warp == 8) DP_PHASE(0, 5 + it * 8);
-      prefetch(it + 1);
       if (warp == 8) DP_PHASE(0, 6 + it * 8);
     }
-  } else if (warp >= 12 && warp < 15) {
-    // ================= writer: dZ = 2 (rowsum(G) zc - G Pc) of the finished tile, lanes = depth =================
-    const int q = warp - 12;
-    const int r0 = lane >> 2, cpair = (lane & 3) * 2;             // 16x256b fragment: rows r0, r0 + 8; columns cpair, cpair + 1 (+ 8 j)
-    const bool rows = q < KP / 32 && !(p.exp_flags & 1);
-    // fragment element (hf, cb, i): row q*32 + hf*16 + r0 + (i & 2 ? 8 : 0), column cb*16 + (i & 4 ? 8 : 0) + cpair + (i & 1)
-    auto elem_off = [&](int b0, int pix0, int hf, int cb, int i, int npx, bool& ok) -> size_t {
-      const int c = cb * 16 + ((i & 4) ? 8 : 0) + cpair + (i & 1);
-      const int k = q * 32 + hf * 16 + r0 + ((i & 2) ? 8 : 0);
-      int pix = pix0 + c, b = b0;
-      while (pix >= HW) { pix -= HW; ++b; }
-      ok = c < npx && k < K;
-      return ((size_t)b * K + k) * HW + pix;
-    };
+  } else if (warp >= 12 && warp < 14) {
+    // ================= writer: dZ = 2 (rowsum(G) zc - G Pc) of the finished tile, thread = pixel =================
+    // dZ sits in TMEM with pixels in lanes 0..63 (M = 128 MMA whose upper 64 rows are over-read garbage): lane quarters
+    // 0 and 1.  Loads of z and stores of dz are coalesced along the pixels, as in the forward kernel.
+    const int q = warp - 12, px = q * 32 + lane;
+    const uint32_t taddr = tZ + ((uint32_t)(q * 32) << 16);
     for (int it = 0; it < iters; ++it) {
       const long long m0 = ((long long)blockIdx.x + (long long)it * gridDim.x) * FT;
-      const int npx = (int)((p.M - m0) < FT ? (p.M - m0) : FT);
-      const int b0 = (int)(m0 / HW), pix0 = (int)(m0 - (long long)b0 * HW);
-      // z of the whole tile (an input: available long before the tile's MMAs retire) travels while this warp waits
-      float zv[2][FT / 16][8];
-      if (rows) {
-#pragma unroll
-        for (int hf = 0; hf < 2; ++hf)
-#pragma unroll
-          for (int cb = 0; cb < FT / 16; ++cb)
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              bool ok;
-              const size_t off = elem_off(b0, pix0, hf, cb, i, npx, ok);
-              zv[hf][cb][i] = ok ? __ldg(p.z + off) : CENTRE;
-            }
-      }
+      const int m = (int)m0 + px;
+      const bool valid = m < Mi && !(p.exp_flags & 1);
+      const int b = valid ? m / HW : 0;
+      const size_t base = ((size_t)b * K) * HW + (valid ? m - b * HW : 0);
       mbar_wait(bar_free, (uint32_t)it & 1u);
       fence_after();
       if (warp == 12) DP_PHASE(0, 7 + it * 8);
-      if (q == KP / 32 && !(p.exp_flags & 8)) {
-        // lane KP of dZ^T holds rowsum(G) of every pixel column (the whole warp takes part in the aligned load)
-        const uint32_t lane_field = (uint32_t)(q * 32) << 16;
+      // the accumulator is copied to registers and handed back at once (the next tile's dZ MMAs wait for it); the
+      // arithmetic, the loads of z and the stores follow off the critical path
+      uint32_t r[KP / 16][16], rsr[16];
 #pragma unroll
-        for (int ch = 0; ch < FT / 16; ++ch) {
-          uint32_t r[16];
-          tmem_ld16(tZ + lane_field + ch * 16, r);
-          tmem_ld_wait();
-          if (lane == 0) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) rss[ch * 16 + i] = __uint_as_float(r[i]);
-          }
-        }
-      }
-      named_bar_sync(3, 96);
-      if (rows) {
-#pragma unroll
-        for (int hf = 0; hf < 2; ++hf) {                           // lanes 0-15 / 16-31 of this quarter
-          const uint32_t taddr = tZ + ((uint32_t)(q * 32 + hf * 16) << 16);
-#pragma unroll
-          for (int cb = 0; cb < FT / 16; ++cb) {
-            uint32_t r[8];
-            asm volatile("tcgen05.ld.sync.aligned.16x256b.x2.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                         : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
-                         : "r"(taddr + cb * 16));
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              bool ok;
-              const size_t off = elem_off(b0, pix0, hf, cb, i, npx, ok);
-              if (ok) {
-                const int c = cb * 16 + ((i & 4) ? 8 : 0) + cpair + (i & 1);
-                const float z1 = zv[hf][cb][i];
-                float gz = 2.f * fmaf(rss[c], z1 - CENTRE, -__uint_as_float(r[i]));
-                if (p.dz_sigmoid) gz *= z1 * (1.f - z1);
-                p.dz[off] = gz;
-              }
-            }
-          }
-        }
-      }
+      for (int ch = 0; ch < KP / 16; ++ch) tmem_ld16(taddr + ch * 16, r[ch]);
+      tmem_ld16(taddr + KP, rsr);
+      tmem_ld_wait();
       fence_before();
       mbar_arrive(bar_dzfree);
+      const float rs = __uint_as_float(rsr[0]);
+#pragma unroll
+      for (int ch = 0; ch < KP / 16; ++ch) {
+        float zv[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int k = ch * 16 + i;
+          zv[i] = (valid && k < K) ? __ldg(p.z + base + (size_t)k * HW) : CENTRE;
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int k = ch * 16 + i;
+          if (valid && k < K) {
+            float gz = 2.f * fmaf(rs, zv[i] - CENTRE, -__uint_as_float(r[ch][i]));
+            if (p.dz_sigmoid) gz *= zv[i] * (1.f - zv[i]);
+            p.dz[base + (size_t)k * HW] = gz;
+          }
+        }
+      }
     }
+  } else if (warp == 14) {
+    // spare warp (no role since the dZ accumulator has pixels in its lanes: two writer warps cover them)
   } else if (warp == 15) {
     // ================= MMA issuer =================
-    if (lane == 0 && iters > 0) {
+    // all 32 lanes run the control flow (warp-uniform); one elected lane issues each MMA / commit (tc_common.cuh)
+    if (iters > 0) {
       const uint32_t idesc_t = make_idesc_tf32(128, FT), idesc_p = make_idesc_tf32(128, KP),
-                     idesc_w = make_idesc_tf32(128, 32);
+                     idesc_w = make_idesc_tf32(128, 32), idesc_z = make_idesc_tf32(128, ZN);
       const int ksteps = (K + 7) >> 3, csteps = C8 >> 3;
       const int total_units = iters * NB;
       // every descriptor is a base plus a compile-time multiple of 16 bytes in the start-address field: the issuing
@@ -387,15 +371,17 @@ __global__ void __launch_bounds__(FU_THREADS, 1) k_tc_bwd_fused(const TcBwdParam
         // descriptors, as the accumulate MMAs below do, gave wrong distance / Gl tiles from the second tile of a CTA
         // on — bisected on the GPU, cause not understood; this form is the one the two-kernel backward uses)
         const uint32_t a0b = smem_u32(PkA) + blk * 128 * 16, b0b = smem_u32(ZkB);
-        for (int ks = 0; ks < ksteps; ++ks)
-          mma_ss(td, make_desc(a0b + ks * 2 * ROWS * 16, ROWS * 16, 128), make_desc(b0b + ks * 2 * FT * 16, FT * 16, 128),
-                 idesc_t, ks > 0 ? 1u : 0u);
         const uint32_t w0b = smem_u32(WtA) + blk * 128 * 16, l0b = smem_u32(dLkB);
+        // One accumulation chain after the other: switching the accumulator between consecutive MMAs measured SLOWER
+        // (interleaved D / Gl chains: 96 -> 114 us at B = 16) — the tensor pipe streams a chain into one accumulator.
+        for (int ks = 0; ks < ksteps; ++ks)
+          mma_ss_w(td, make_desc(a0b + ks * 2 * ROWS * 16, ROWS * 16, 128), make_desc(b0b + ks * 2 * FT * 16, FT * 16, 128),
+                   idesc_t, ks > 0 ? 1u : 0u);
         for (int ks = 0; ks < csteps; ++ks)
-          mma_ss(td + FT, make_desc(w0b + ks * 2 * ROWS * 16, ROWS * 16, 128), make_desc(l0b + ks * 2 * FT * 16, FT * 16, 128),
-                 idesc_t, ks > 0 ? 1u : 0u);
-        mma_commit(bar_acc0 + b * 8);
-        if (blk == NB - 1) mma_commit(bar_kfree);
+          mma_ss_w(td + FT, make_desc(w0b + ks * 2 * ROWS * 16, ROWS * 16, 128), make_desc(l0b + ks * 2 * FT * 16, FT * 16, 128),
+                   idesc_t, ks > 0 ? 1u : 0u);
+        mma_commit_w(bar_acc0 + b * 8);
+        if (blk == NB - 1) mma_commit_w(bar_kfree);
       };
       uint32_t gcnt[2] = {0u, 0u};
       int fullk_seen = 0;                      // tiles whose full_k completion has been observed
@@ -422,28 +408,30 @@ __global__ void __launch_bounds__(FU_THREADS, 1) k_tc_bwd_fused(const TcBwdParam
         }
         fence_after();
         DP_PHASE(1, 1 + it * 8 + blk * 4);
-        const uint32_t td = tDb(b), tp = tP0 + blk * KP, tw = tW0 + blk * 32;
+        const uint32_t td = tDb(b), tp = tP0 + blk * KP, tw = tW0 + blk * WSTR;
         const uint32_t acc0 = it > 0 ? 1u : 0u;
-#pragma unroll
-        for (int ks = 0; ks < FT / 8; ++ks) {
-          const uint32_t acc = ks > 0 ? 1u : acc0;
-          mma_ts(tp, td + ks * 8, d_zt + (uint64_t)(((ks >> 2) * KP * 128 + (ks & 3) * 32) >> 4), idesc_p, acc);
-          mma_ts(tw, td + FT + ks * 8, d_dlt + (uint64_t)(((ks >> 2) * 32 * 128 + (ks & 3) * 32) >> 4), idesc_w, acc);
-        }
-        if (!(p.exp_flags & 2)) {
-          // dZ^T (+)= [Pc^T; 1] G^T over this block's prototypes
-          const uint64_t pa = d_pt + (uint64_t)(blk * 32 * PR);
-          const uint64_t gb = (NB == 1 ? (g & 1) : blk) == 0 ? d_g0 : d_g1;
-          const uint32_t accz = blk > 0 ? 1u : 0u;
-          constexpr int NK0 = (NPROT < 128 ? NPROT : 128) / 8;
-#pragma unroll
-          for (int ks = 0; ks < NK0; ++ks)
-            if (blk == 0 || ks < (NPROT - 128) / 8)
-              mma_ss(tZ, pa + (uint64_t)(ks * 2 * PR), gb + (uint64_t)(((ks >> 2) * FT * 128 + (ks & 3) * 32) >> 4), idesc_t,
+        // three accumulation chains (dP, dW, dZ), one after the other
+        const uint64_t pa = d_pt + (uint64_t)(blk * 32 * PR);
+        const uint64_t gb = (NB == 1 ? (g & 1) : blk) == 0 ? d_g0 : d_g1;
+        const uint32_t accz = blk > 0 ? 1u : 0u;
+        const bool with_z = !(p.exp_flags & 2);
+        constexpr int NK0 = (NPROT < 128 ? NPROT : 128) / 8;       // dZ k-steps of block 0 (block 1: the rest)
+        const int nkz = blk == 0 ? NK0 : (NPROT - 128) / 8;
+        auto z_step = [&](int ks) {
+          if (with_z && ks < nkz)
+            mma_ss_w(tZ, gb + (uint64_t)(((ks >> 2) * FT * 128 + (ks & 3) * 32) >> 4), pa + (uint64_t)(ks * 2 * PR), idesc_z,
                      ks > 0 ? 1u : accz);
-        }
-        if (blk == NB - 1) mma_commit(bar_free);
-        if (g == total_units - 1) mma_commit(bar_done);
+        };
+#pragma unroll
+        for (int ks = 0; ks < FT / 8; ++ks)
+          mma_ts_w(tp, td + ks * 8, d_zt + (uint64_t)(((ks >> 2) * KP * 128 + (ks & 3) * 32) >> 4), idesc_p, ks > 0 ? 1u : acc0);
+#pragma unroll
+        for (int ks = 0; ks < FT / 8; ++ks)
+          mma_ts_w(tw, td + FT + ks * 8, d_dlt + (uint64_t)(((ks >> 2) * 32 * 128 + (ks & 3) * 32) >> 4), idesc_w, 1u);
+#pragma unroll
+        for (int ks = 0; ks < NK0; ++ks) z_step(ks);
+        if (blk == NB - 1) mma_commit_w(bar_free);
+        if (g == total_units - 1) mma_commit_w(bar_done);
         DP_PHASE(1, 2 + it * 8 + blk * 4);
         if (g + 2 < total_units) {
           need_tile((g + 2) / NB);
@@ -482,6 +470,15 @@ __global__ void __launch_bounds__(FU_THREADS, 1) k_tc_bwd_fused(const TcBwdParam
       gofs[j] = (uint32_t)q * (FT * 128) + (uint32_t)j * 128 + ((((uint32_t)lane >> 2) ^ (uint32_t)j) << 4) + ((uint32_t)lane & 3u) * 4u;
     const float eps = p.eps, epsm1 = p.eps - 1.f;
     const bool act_log = p.act_mode == ADLM_ACT_LOG;
+    {
+      // the dW accumulators start at zero (their MMAs always accumulate, see the TMEM map above); ordered before the
+      // first dW MMA by this thread's first arrival on gs[]
+      uint32_t zz[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) zz[i] = 0u;
+      for (int c = half * NB * 16; c < (half + 1) * NB * 16; c += 16) tmem_st16(tW0 + lane_field + c, zz);
+      tmem_st_wait();
+    }
     uint32_t acnt[2] = {0u, 0u};
     for (int it = 0; it < iters; ++it) {
       mbar_wait(bar_full, (uint32_t)it & 1u);
@@ -621,7 +618,7 @@ __global__ void __launch_bounds__(FU_THREADS, 1) k_tc_bwd_fused(const TcBwdParam
         __syncwarp();
         uint32_t r[16];
         if (iters > 0) {
-          tmem_ld16(tW0 + blk * 32 + lane_field + half * 16, r);
+          tmem_ld16(tW0 + blk * WSTR + lane_field + half * 16, r);
           tmem_ld_wait();
         } else {
 #pragma unroll

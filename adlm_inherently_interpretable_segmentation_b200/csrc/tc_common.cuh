@@ -67,6 +67,26 @@ __device__ __forceinline__ void mma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 
+// Whole-warp forms: every lane of a CONVERGED warp calls them with warp-uniform arguments and one elected lane issues.
+// With the issue inside `if (lane == 0)` the compiler treats every operand as per-thread data and wraps each
+// tcgen05.mma in an elect / R2UR / branch loop to move the descriptors into uniform registers (~40 SASS instructions,
+// 80-130 cycles per MMA in the phase clocks); with uniform control flow around elect.sync the descriptors are computed
+// in the uniform datapath.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n .reg .pred p;\n elect.sync _|p, 0xffffffff;\n selp.u32 %0, 1, 0, p;\n}\n" : "=r"(pred));
+  return pred != 0u;
+}
+__device__ __forceinline__ void mma_ss_w(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  if (elect_one()) mma_ss(tmem_d, adesc, bdesc, idesc, accumulate);
+}
+__device__ __forceinline__ void mma_ts_w(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  if (elect_one()) mma_ts(tmem_d, tmem_a, bdesc, idesc, accumulate);
+}
+__device__ __forceinline__ void mma_commit_w(uint32_t bar) {
+  if (elect_one()) mma_commit(bar);
+}
+
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
   asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
