@@ -31,6 +31,9 @@ SIGNATURES = {
     "adlm_timing_end": (c_int, [c_void_p]),
     "adlm_head_fwd": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int,
                               c_float, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "adlm_head_fwd_big_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "adlm_head_fwd_big": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int,
+                                  c_float, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "adlm_head_bwd": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_int,
                               c_float, c_int, c_int, c_void_p, c_void_p, c_void_p,
                               c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),

