@@ -77,14 +77,23 @@ __device__ __forceinline__ bool elect_one() {
   asm volatile("{\n .reg .pred p;\n elect.sync _|p, 0xffffffff;\n selp.u32 %0, 1, 0, p;\n}\n" : "=r"(pred));
   return pred != 0u;
 }
+// elect.sync and the predicated instruction sit in ONE asm block: with `if (elect_one()) mma(...)` the compiler may
+// sink the descriptor arithmetic into the conditional and emit a divergent region (BSSY / BRA / BSYNC.RECONVERGENT
+// per MMA: ~160 cycles per instruction in the large-head forward's K loop, ncu source page, round 2); this form
+// leaves it nothing to branch around.
 __device__ __forceinline__ void mma_ss_w(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-  if (elect_one()) mma_ss(tmem_d, adesc, bdesc, idesc, accumulate);
+  asm volatile("{\n .reg .pred e, p;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 p, %4, 0;\n"
+               " @e tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}\n"
+               ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void mma_ts_w(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-  if (elect_one()) mma_ts(tmem_d, tmem_a, bdesc, idesc, accumulate);
+  asm volatile("{\n .reg .pred e, p;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 p, %4, 0;\n"
+               " @e tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n}\n"
+               ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void mma_commit_w(uint32_t bar) {
-  if (elect_one()) mma_commit(bar);
+  asm volatile("{\n .reg .pred e;\n elect.sync _|e, 0xffffffff;\n"
+               " @e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n}\n" ::"r"(bar) : "memory");
 }
 
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
@@ -156,6 +165,55 @@ __device__ __forceinline__ float rcp_approx(float x) {
 }
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+// ---- CTA-pair forms (cluster of two CTAs, tcgen05 ... cta_group::2; conventions verified with tools/tc_probe_pair.cu,
+// profiles/r2_probe_pair.log): one MMA has M = 256 — accumulator rows 0..127 land in the leader's tensor memory, rows
+// 128..255 in the peer's — each CTA supplies ITS 128 rows of A (own shared memory at the descriptor's address, or own
+// tensor memory for .ts) and N/2 rows of B: the leader (cluster rank 0) the accumulator columns [0, N/2), the peer
+// [N/2, N).  Only the leader issues; tcgen05.commit ... multicast::cluster arrives on the barrier at the same
+// shared-memory offset in both CTAs.
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t dst_smem, uint32_t ncols) {      // one warp in EACH CTA
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void mma_pair_ss_w(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n .reg .pred e, p;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 p, %4, 0;\n"
+               " @e tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n}\n"
+               ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void mma_pair_ts_w(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n .reg .pred e, p;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 p, %4, 0;\n"
+               " @e tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], %2, %3, p;\n}\n"
+               ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrives on `bar` (same offset) in both CTAs when every MMA issued so far by this thread has completed
+__device__ __forceinline__ void mma_pair_commit_w(uint32_t bar) {
+  asm volatile("{\n .reg .pred e;\n elect.sync _|e, 0xffffffff;\n"
+               " @e tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n}\n"
+               ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+// arrive on the barrier at this CTA's offset `bar` in CTA `cta` of the cluster.  Default semantics (release at CTA
+// scope), as CUTLASS's ClusterBarrier::arrive does: with .release.cluster ptxas puts MEMBAR.ALL.GPU in front of every
+// arrive (~1000 cycles; it serialised the large-head forward's chunk pipeline, gpurun_out/r2_cfg5_sweep4.log).  What a
+// remote arrival publishes here is either nothing (a relayed TMA completion) or data its own warp wrote and fenced
+// (fence.proxy.async / tcgen05.fence::before_thread_sync) before the arrive.  Waiters use the plain mbar_wait.
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t cta) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(bar), "r"(cta));
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
 }
 
 // round-to-nearest fp32 -> tf32 (the tensor core would otherwise truncate the low 13 mantissa bits)

@@ -2,18 +2,28 @@
 // C <= 112 classes — BASELINE configs[4] (1000 prototypes x 256-d, 100 classes on 1024 x 2048 maps), the shapes the
 // warp-specialised kernel of tc_head_ws.cu cannot hold in shared memory.  Same mathematics (model.py:203-283).
 //
-// A 128-pixel tile keeps its features resident in shared memory as the A operand (K-major, all of K: 128 KB at
-// K = 256) and sweeps the prototypes in blocks of 128:
-//   MMA1  D1[b] = A . Pblk^T        32 x (M128 N128 K8); the block's prototypes stream through a 4-slot ring of 16 KB
-//                                   chunks [32 depth x 128 prototypes] fetched by cp.async.bulk (TMA bulk copy) from a
-//                                   pre-staged copy of P that already has the operand layout (centred, rounded)
+// The kernel runs on CTA PAIRS (cluster of two CTAs on one TPC, tcgen05 cta_group::2).  Each CTA of a pair owns one
+// 128-pixel tile whose features stay resident in its shared memory as the A operand (K-major, all of K: 128 KB at
+// K = 256); the pair sweeps the prototypes in blocks of 128 with M = 256 MMAs issued by the leader CTA:
+//   MMA1  D1[b] = A . Pblk^T        32 x (M256 N128 K8); each CTA streams only HALF of the block's prototypes (64 rows)
+//                                   through an 8-slot ring of 8 KB chunks [32 depth x 64 prototypes] fetched by
+//                                   cp.async.bulk (TMA bulk copy) from a pre-staged copy of P in operand layout
 //   E1    d = max(|z|^2 - 2 acc + |p|^2, 0) -> s = log2(1 + (1-eps)/(d+eps)) -> back into D1[b] (TMEM A operand)
-//   MMA2  D2[t&1] += S . Wblk^T     16 x (M128 N=Cpad K8), W chunks [32 prototypes x Cpad] through a 2-slot ring,
-//                                   accumulated over the prototype blocks: the last layer never sees an M x N map
+//   MMA2  D2[t&1] += S . Wblk^T     16 x (M256 N=Cpad K8), each CTA streams Cpad/2 class rows per W chunk through a
+//                                   2-slot ring; accumulated over the prototype blocks: no M x N map in memory
 //   E2    logits / per-pixel argmax from D2 after the last block
+// Why pairs: with one CTA per tile every 128 pixels pulled all of P and W (1.46 MB at cfg5) from L2, 6 GB per
+// 512 x 1024 map; with the MMAs and the epilogue switched off the kernel still took 0.79 of its 1.15 ms, i.e. it sat
+// on the ~7.6 TB/s L2 -> SM ceiling at 42 % of the TF32 matmul peak (gpurun_out/r2_cfg5_sweep3.log).
+// A pair shares each B operand, which halves that traffic.
 // D1 is double-buffered (MMA1 of block j+1 runs under the epilogue of block j), D2 by tile parity.
-// Warps: 0-7 epilogue, 8-11 producers (thread = pixel: coalesced LDG of the NCHW tile, centre, round, |z|^2),
-// 12 MMA issue (whole warp around elect.sync), 13 prototype-chunk loader, 14 last-layer-chunk loader.
+// Warps (per CTA): 0-7 epilogue, 8-11 producers (thread = pixel: coalesced LDG of the NCHW tile, centre, round, |z|^2),
+// 12 MMA issue in the leader (whole warp around elect.sync) / in the peer a forwarder that tells the leader when the
+// peer's chunks have landed, 13 prototype-chunk loader, 14 last-layer-chunk loader.
+// Barriers: "full" events of the peer reach the LEADER's barriers (producer and epilogue warps arrive remotely, the
+// forwarder relays the TMA completions); "free" events are tcgen05.commit multicasts onto both CTAs' barriers.
+#include <cstdio>
+#include <cstdlib>
 #include "tc_head.cuh"
 #include "tc_common.cuh"
 
@@ -24,27 +34,37 @@ namespace {
 using namespace tc;
 
 constexpr int TILE = 128, NBLK = 128, KCH = 32, BIG_THREADS = 480;
-constexpr int P_SLOTS = 4, W_SLOTS = 2;
+constexpr int P_SLOTS_MAX = 16, W_SLOTS = 2;
+constexpr int NHALF = NBLK / 2;                                 // prototype rows of a block held by one CTA
 constexpr float LN2 = 0.6931471805599453f;
 constexpr float CENTRE = 0.5f;
-constexpr int P_CHUNK_FLOATS = (KCH / 4) * NBLK * 4;            // 4096 floats = 16 KB
+constexpr int P_CHUNK_FLOATS = (KCH / 4) * NHALF * 4;           // 2048 floats = 8 KB per CTA
+// Chunks travel and are released in GROUPS: one bulk copy, one barrier round and one commit per PG prototype chunks
+// (WG last-layer chunks).  The fixed cost of a ring step (two barrier waits, fence, commit: ~230 cycles that do not
+// overlap the MMAs) is then paid per 8 MMAs instead of per 4; the ring's depth itself does not matter (2 slots run as
+// fast as 16, gpurun_out/r2_cfg5_sweep5.log).
+constexpr int PG = 2, WG = 2;
+constexpr int P_GROUP_FLOATS = PG * P_CHUNK_FLOATS;
 
 struct BigParams {
   const float* z;
-  const float* Pst;       // staged prototypes [nblk][KC][8][128][4]
+  const float* Pst;       // staged prototypes [nblk][KC/PG][2 halves][PG][8][64][4]
   const float* p2;        // [Npad] |p|^2 of the rounded, centred prototypes
-  const float* Wst;       // staged last layer [nblk][4][8][Cpad][4], ln 2 folded in
+  const float* Wst;       // staged last layer [nblk][4/WG][2 halves][WG][8][Cpad/2][4], ln 2 folded in
   float* logits;          // [M, C]
   float* dist;            // [B, N, HW] | null
   int32_t* argmax;        // [M] | null
   int B, K, HW, N, C;
-  int KC;                 // depth chunks of 32
+  int KC;                 // depth chunks of 32, rounded up to a multiple of PG (the padding is zeros on both sides)
   int nblk;               // prototype blocks of 128
   int Cpad;               // classes rounded up to 16
   float eps;
   int act_mode;
   long long M;
   int num_tiles;
+  int p_slots;            // depth of the prototype-chunk ring (what shared memory leaves, at most P_SLOTS_MAX)
+  int exp_flags;          // timing experiments (ADLM_BIG_EXP; results are wrong when set): 1 no MMA1, 2 no MMA2,
+                          // 4 no epilogue arithmetic
 };
 
 // ---- one-time staging of P and W into the operand layouts (a few microseconds: ~1.5 MB) ----
@@ -58,11 +78,13 @@ __global__ void __launch_bounds__(256) k_big_stage(const float* __restrict__ P, 
   const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long f = tid; f < nP; f += stride) {
-    const int row = (int)(f % NBLK);
-    const int k4 = (int)((f / NBLK) % 8);
-    const int kc = (int)((f / (NBLK * 8)) % KC);
+    const int row = (int)(f % NHALF);
+    const int k4 = (int)((f / NHALF) % 8);
+    const int g = (int)((f / (NHALF * 8)) % PG);
+    const int half = (int)((f / (NHALF * 8 * PG)) % 2);
+    const int kc = (int)((f / (NBLK * 8 * PG)) % (KC / PG)) * PG + g;
     const int blk = (int)(f / ((long long)NBLK * 8 * KC));
-    const int n = blk * NBLK + row;
+    const int n = blk * NBLK + half * NHALF + row;
     float v[4];
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
@@ -71,10 +93,11 @@ __global__ void __launch_bounds__(256) k_big_stage(const float* __restrict__ P, 
     }
     reinterpret_cast<float4*>(Pst)[f] = make_float4(v[0], v[1], v[2], v[3]);
   }
+  const int Ch = Cpad / 2;
   for (long long f = tid; f < nW; f += stride) {
-    const int c = (int)(f % Cpad);
-    const int k4 = (int)((f / Cpad) % 8);
-    const int kc2 = (int)((f / (Cpad * 8)) % 4);
+    const int c = (int)((f / (Ch * 8 * WG)) % 2) * Ch + (int)(f % Ch);
+    const int k4 = (int)((f / Ch) % 8);
+    const int kc2 = (int)((f / (Cpad * 8 * WG)) % (4 / WG)) * WG + (int)((f / (Ch * 8)) % WG);
     const int blk = (int)(f / ((long long)Cpad * 8 * 4));
     float v[4];
 #pragma unroll
@@ -95,17 +118,39 @@ __global__ void __launch_bounds__(256) k_big_stage(const float* __restrict__ P, 
   }
 }
 
-// barrier indices
-constexpr int B_AFULL = 0;               // A tile + |z|^2 written (128 producer threads), once per tile
-constexpr int B_AFREE = 1;               // last MMA1 of the tile has read A (commit)
-constexpr int B_D1FULL = 2;              // [2] D1[b] ready (commit)
-constexpr int B_SREADY = 4;              // [2] similarities back in D1[b] (256 epilogue threads)
-constexpr int B_D2FULL = 6;              // [2] D2[tile parity] complete (commit)
-constexpr int B_PFULL = 8;               // [P_SLOTS] prototype chunk landed (expect_tx)
-constexpr int B_PEMPTY = 12;             // [P_SLOTS] MMAs of the chunk done (commit)
-constexpr int B_WFULL = 16;              // [W_SLOTS]
-constexpr int B_WEMPTY = 18;             // [W_SLOTS]
-constexpr int NBARS = 20;
+// Phase clocks (ADLM_BIG_EXP & 16): cycles each role of every CTA spent per phase, printed by the host after the launch.
+constexpr int DBG_SLOTS = 24;
+__device__ long long g_big_clocks[160][DBG_SLOTS];
+struct PhaseClock {
+  long long t, acc[12];
+  bool on;
+  __device__ __forceinline__ void start(bool enable) {
+    on = enable;
+    for (int i = 0; i < 12; ++i) acc[i] = 0;
+    t = on ? clock64() : 0;
+  }
+  __device__ __forceinline__ void tick(int i) {
+    if (on) { const long long n = clock64(); acc[i] += n - t; t = n; }
+  }
+  __device__ __forceinline__ void flush(int base, int count) {
+    if (on && (threadIdx.x & 31) == 0 && blockIdx.x < 160)
+      for (int i = 0; i < count; ++i) g_big_clocks[blockIdx.x][base + i] = acc[i];
+  }
+};
+
+// barrier indices (same layout in both CTAs)
+constexpr int B_AFULL = 0;               // LEADER: A tiles + |z|^2 of both CTAs written (4 + 4 producer warps)
+constexpr int B_AFREE = 1;               // last MMA1 of the tile has read A (commit, both CTAs)
+constexpr int B_D1FULL = 2;              // [2] D1[b] ready (commit, both CTAs)
+constexpr int B_SREADY = 4;              // [2] LEADER: similarities back in D1[b] of both CTAs (8 + 8 epilogue warps)
+constexpr int B_D2FULL = 6;              // [2] D2[tile parity] complete (commit, both CTAs)
+constexpr int B_PFULL = 8;               // [P_SLOTS_MAX] own prototype chunk landed (expect_tx)
+constexpr int B_PEMPTY = 24;             // [P_SLOTS_MAX] MMAs of the chunk done (commit, both CTAs)
+constexpr int B_WFULL = 40;              // [W_SLOTS]
+constexpr int B_WEMPTY = 44;             // [W_SLOTS]
+constexpr int B_XPFULL = 48;             // [P_SLOTS_MAX] LEADER: the peer's chunk landed (peer's forwarder)
+constexpr int B_XWFULL = 64;             // [W_SLOTS] LEADER: same for the last-layer chunks
+constexpr int NBARS = 68;
 
 __device__ __forceinline__ void bulk_load(uint32_t dst_smem, const void* src, uint32_t bytes, uint32_t bar) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
@@ -117,52 +162,62 @@ struct BigSmem {
   // A [KPAD/4][128][4] | P ring | W ring | p2 [Npad] | x2 [2][128] | barriers | tmem base
   static __host__ __device__ size_t a() { return 0; }
   static __host__ __device__ size_t pring(int KC) { return (size_t)KC * KCH * TILE * 4; }
-  static __host__ __device__ size_t wring(int KC) { return pring(KC) + (size_t)P_SLOTS * P_CHUNK_FLOATS * 4; }
-  static __host__ __device__ size_t p2(int KC, int Cpad) { return wring(KC) + (size_t)W_SLOTS * 32 * Cpad * 4; }
-  static __host__ __device__ size_t x2(int KC, int Cpad, int Npad) { return p2(KC, Cpad) + (size_t)Npad * 4; }
-  static __host__ __device__ size_t bars(int KC, int Cpad, int Npad) { return x2(KC, Cpad, Npad) + 2 * TILE * 4; }
-  static __host__ __device__ size_t total(int KC, int Cpad, int Npad) { return bars(KC, Cpad, Npad) + NBARS * 8 + 16; }
+  static __host__ __device__ size_t wring(int KC, int slots) { return pring(KC) + (size_t)slots * P_GROUP_FLOATS * 4; }
+  static __host__ __device__ size_t p2(int KC, int slots, int Cpad) { return wring(KC, slots) + (size_t)W_SLOTS * WG * 32 * (Cpad / 2) * 4; }
+  static __host__ __device__ size_t x2(int KC, int slots, int Cpad, int Npad) { return p2(KC, slots, Cpad) + (size_t)Npad * 4; }
+  static __host__ __device__ size_t bars(int KC, int slots, int Cpad, int Npad) { return x2(KC, slots, Cpad, Npad) + 2 * TILE * 4; }
+  static __host__ __device__ size_t total(int KC, int slots, int Cpad, int Npad) { return bars(KC, slots, Cpad, Npad) + NBARS * 8 + 16; }
 };
 
-__global__ void __launch_bounds__(BIG_THREADS, 1) k_tc_fwd_big(const BigParams p) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc_fwd_big(const BigParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const int KC = p.KC, nblk = p.nblk, Cpad = p.Cpad, Npad = nblk * NBLK, K = p.K, N = p.N, C = p.C, HW = p.HW;
+  const uint32_t P_SLOTS = (uint32_t)p.p_slots;
   float* A = reinterpret_cast<float*>(smem + BigSmem::a());
   float* Pr = reinterpret_cast<float*>(smem + BigSmem::pring(KC));
-  float* Wr = reinterpret_cast<float*>(smem + BigSmem::wring(KC));
-  float* p2s = reinterpret_cast<float*>(smem + BigSmem::p2(KC, Cpad));
-  float* x2s = reinterpret_cast<float*>(smem + BigSmem::x2(KC, Cpad, Npad));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BigSmem::bars(KC, Cpad, Npad));
+  float* Wr = reinterpret_cast<float*>(smem + BigSmem::wring(KC, p.p_slots));
+  float* p2s = reinterpret_cast<float*>(smem + BigSmem::p2(KC, p.p_slots, Cpad));
+  float* x2s = reinterpret_cast<float*>(smem + BigSmem::x2(KC, p.p_slots, Cpad, Npad));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BigSmem::bars(KC, p.p_slots, Cpad, Npad));
   uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + NBARS);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int Mi = (int)p.M;
-  const int iters = p.num_tiles > (int)blockIdx.x ? (p.num_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
-  auto tile_of = [&](int it) { return (int)blockIdx.x + it * (int)gridDim.x; };
-  const uint32_t w_chunk_bytes = (uint32_t)(32 * Cpad * 4);
+  // pair q of the grid's pairs handles the tile pairs q, q + pairs, ...; this CTA takes tile 2 * pair + rank (a tile
+  // beyond the map has no valid pixel: it computes on the centre value and stores nothing)
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int pairs = (int)gridDim.x / 2, pair0 = (int)blockIdx.x / 2, num_pairs = (p.num_tiles + 1) / 2;
+  const int iters = num_pairs > pair0 ? (num_pairs - 1 - pair0) / pairs + 1 : 0;
+  auto tile_of = [&](int it) { return 2 * (pair0 + it * pairs) + (int)rank; };
+  const int Ch = Cpad / 2;                                         // class rows of a W chunk held by one CTA
+  const uint32_t w_chunk_bytes = (uint32_t)(32 * Ch * 4), w_group_bytes = WG * w_chunk_bytes;
+  const int KG = KC / PG;                                          // prototype-chunk groups per block
 
-  if (warp == 12) tmem_alloc(smem_u32(tmem_base_s), 512);
+  if (warp == 12) tmem_alloc_pair(smem_u32(tmem_base_s), 512);
   if (tid == 0) {
-    mbar_init(smem_u32(&bars[B_AFULL]), 128);
+    mbar_init(smem_u32(&bars[B_AFULL]), 8);
     mbar_init(smem_u32(&bars[B_AFREE]), 1);
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&bars[B_D1FULL + i]), 1);
-      mbar_init(smem_u32(&bars[B_SREADY + i]), 256);
+      mbar_init(smem_u32(&bars[B_SREADY + i]), 16);
       mbar_init(smem_u32(&bars[B_D2FULL + i]), 1);
     }
-    for (int i = 0; i < P_SLOTS; ++i) {
+    for (int i = 0; i < P_SLOTS_MAX; ++i) {
       mbar_init(smem_u32(&bars[B_PFULL + i]), 1);
       mbar_init(smem_u32(&bars[B_PEMPTY + i]), 1);
+      mbar_init(smem_u32(&bars[B_XPFULL + i]), 1);
     }
     for (int i = 0; i < W_SLOTS; ++i) {
       mbar_init(smem_u32(&bars[B_WFULL + i]), 1);
       mbar_init(smem_u32(&bars[B_WEMPTY + i]), 1);
+      mbar_init(smem_u32(&bars[B_XWFULL + i]), 1);
     }
     mbar_init_fence();
   }
   for (int n = tid; n < Npad; n += BIG_THREADS) p2s[n] = __ldg(p.p2 + n);
   fence_before();
-  __syncthreads();
+  cluster_sync_all();                      // barriers of BOTH CTAs initialised before anyone arrives remotely
   fence_after();
   const uint32_t tmem_base = *tmem_base_s;
   const uint32_t bar0 = smem_u32(&bars[0]);
@@ -172,51 +227,84 @@ __global__ void __launch_bounds__(BIG_THREADS, 1) k_tc_fwd_big(const BigParams p
   if (warp >= 8 && warp < 12) {
     // ================= producers: thread = pixel =================
     const int cw = tid - 256;
+    PhaseClock pc;                         // 0 wait for A to be free 1 fill
+    pc.start((p.exp_flags & 16) != 0 && warp == 8);
     for (int it = 0; it < iters; ++it) {
       const int m = tile_of(it) * TILE + cw;
       const bool valid = m < Mi;
       const int b = valid ? m / HW : 0;
       const float* src = p.z + ((size_t)b * K) * HW + (valid ? m - b * HW : 0);
-      float zr[KCH];
-      auto load = [&](int kc) {
+      // Two depth chunks are kept in flight in registers: the fill of a tile is a chain of load round trips (the map
+      // streams from DRAM), and it is the bubble the MMA warp sees at every tile boundary.
+      float zr[2][KCH];
+      auto load = [&](int kc, float (&dst)[KCH]) {
 #pragma unroll
         for (int k = 0; k < KCH; ++k) {
           const int kk = kc * KCH + k;
-          zr[k] = (valid && kk < K) ? __ldg(src + (size_t)kk * HW) : CENTRE;
+          dst[k] = (valid && kk < K) ? __ldg(src + (size_t)kk * HW) : CENTRE;
         }
       };
-      load(0);                                                   // in flight while the previous tile still owns A
-      if (it > 0) mbar_wait(bar(B_AFREE), (uint32_t)(it - 1) & 1u);
       float x2 = 0.f;
-      for (int kc = 0; kc < KC; ++kc) {
+      auto put = [&](int kc, float (&cur)[KCH]) {
         float v[KCH];
 #pragma unroll
         for (int k = 0; k < KCH; ++k) {
-          v[k] = rna_tf32_mask(zr[k] - CENTRE);
+          v[k] = rna_tf32_mask(cur[k] - CENTRE);
           x2 = fmaf(v[k], v[k], x2);
         }
-        if (kc + 1 < KC) load(kc + 1);
+        if (kc + 2 < KC) load(kc + 2, cur);
 #pragma unroll
         for (int k4 = 0; k4 < KCH / 4; ++k4)
           *reinterpret_cast<float4*>(A + ((size_t)(kc * (KCH / 4) + k4) * TILE + cw) * 4) =
               make_float4(v[k4 * 4], v[k4 * 4 + 1], v[k4 * 4 + 2], v[k4 * 4 + 3]);
+      };
+      load(0, zr[0]);                                            // in flight while the previous tile still owns A
+      load(1, zr[1]);                                            // (KC is even: a multiple of PG)
+      if (it > 0) mbar_wait(bar(B_AFREE), (uint32_t)(it - 1) & 1u);
+      pc.tick(0);
+      for (int kc = 0; kc < KC; kc += 2) {
+        put(kc, zr[0]);
+        put(kc + 1, zr[1]);
       }
       x2s[(it & 1) * TILE + cw] = x2;
       fence_async_smem();
-      mbar_arrive(bar(B_AFULL));
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(bar(B_AFULL), 0);
+      pc.tick(1);
+      // pull the NEXT tile's lines towards L2 now (a whole tile period ahead): its fill then pays L2, not DRAM, latency.
+      // Lane l touches the warp's 128-byte line of depth l, l + 32, ...
+      if (it + 1 < iters) {
+        const int mn = tile_of(it + 1) * TILE + (warp - 8) * 32;
+        if (mn < Mi) {
+          const int bn = mn / HW;
+          const float* nsrc = p.z + ((size_t)bn * K) * HW + (mn - bn * HW);
+          for (int kk = lane; kk < K; kk += 32)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(nsrc + (size_t)kk * HW));
+        }
+      }
     }
+    pc.flush(11, 2);
   } else if (warp == 13) {
     // ================= prototype-chunk loader (one thread, TMA bulk copies) =================
     if (lane == 0) {
       uint32_t i = 0;
+      PhaseClock pc;                       // 0 wait for a free slot 1 issue
+      pc.start((p.exp_flags & 16) != 0);
       for (int it = 0; it < iters; ++it)
         for (int blk = 0; blk < nblk; ++blk)
-          for (int kc = 0; kc < KC; ++kc, ++i) {
+          for (int kg = 0; kg < KG; ++kg, ++i) {
             const uint32_t slot = i % P_SLOTS, use = i / P_SLOTS;
             if (use > 0) mbar_wait(bar(B_PEMPTY + slot), (use - 1) & 1u);
-            bulk_load(smem_u32(Pr + (size_t)slot * P_CHUNK_FLOATS), p.Pst + ((size_t)blk * KC + kc) * P_CHUNK_FLOATS,
-                      P_CHUNK_FLOATS * 4, bar(B_PFULL + slot));
+            pc.tick(0);
+            bulk_load(smem_u32(Pr + (size_t)slot * P_GROUP_FLOATS),
+                      p.Pst + (((size_t)blk * KG + kg) * 2 + rank) * P_GROUP_FLOATS, P_GROUP_FLOATS * 4, bar(B_PFULL + slot));
+            pc.tick(1);
+            if (p.exp_flags & 32) {          // serialise: measures the latency of one bulk copy (issue -> complete_tx)
+              mbar_wait(bar(B_PFULL + slot), use & 1u);
+              pc.tick(2);
+            }
           }
+      pc.flush(13, 3);
     }
   } else if (warp == 14) {
     // ================= last-layer-chunk loader =================
@@ -224,62 +312,110 @@ __global__ void __launch_bounds__(BIG_THREADS, 1) k_tc_fwd_big(const BigParams p
       uint32_t i = 0;
       for (int it = 0; it < iters; ++it)
         for (int blk = 0; blk < nblk; ++blk)
-          for (int kc2 = 0; kc2 < 4; ++kc2, ++i) {
+          for (int wg = 0; wg < 4 / WG; ++wg, ++i) {
             const uint32_t slot = i % W_SLOTS, use = i / W_SLOTS;
             if (use > 0) mbar_wait(bar(B_WEMPTY + slot), (use - 1) & 1u);
-            bulk_load(smem_u32(Wr + (size_t)slot * 32 * Cpad), p.Wst + ((size_t)blk * 4 + kc2) * 32 * Cpad, w_chunk_bytes,
-                      bar(B_WFULL + slot));
+            bulk_load(smem_u32(Wr + (size_t)slot * WG * 32 * Ch),
+                      p.Wst + (((size_t)blk * (4 / WG) + wg) * 2 + rank) * WG * 32 * Ch, w_group_bytes, bar(B_WFULL + slot));
           }
     }
-  } else if (warp == 12) {
-    // ================= MMA issue (whole warp, one elected lane per instruction) =================
-    const uint32_t idesc1 = make_idesc_tf32(TILE, NBLK), idesc2 = make_idesc_tf32(TILE, Cpad);
+  } else if (warp == 12 && leader) {
+    // ================= MMA issue (leader CTA; whole warp, one elected lane per instruction) =================
+    const uint32_t idesc1 = make_idesc_tf32(2 * TILE, NBLK), idesc2 = make_idesc_tf32(2 * TILE, Cpad);
     const uint32_t a_base = smem_u32(A), p_base = smem_u32(Pr), w_base = smem_u32(Wr);
     uint32_t pi = 0, wi = 0;                                    // chunks consumed so far
     uint32_t d1cnt[2] = {0u, 0u};
+    PhaseClock pc;                         // 0 AFULL 1 PFULL 2 XPFULL 3 MMA1 issue 4 SREADY 5 WFULL 6 XWFULL 7 MMA2 issue
+    pc.start((p.exp_flags & 16) != 0);
     auto mma1 = [&](int blk, bool last_of_tile) {
       const int b = blk & 1;
-      for (int kc = 0; kc < KC; ++kc, ++pi) {
+      for (int kg = 0; kg < KG; ++kg, ++pi) {
         const uint32_t slot = pi % P_SLOTS, use = pi / P_SLOTS;
         mbar_wait(bar(B_PFULL + slot), use & 1u);
+        pc.tick(1);
+        mbar_wait(bar(B_XPFULL + slot), use & 1u);
+        pc.tick(2);
         fence_after();
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int ks = kc * 4 + j;
-          mma_ss_w(tD1 + b * NBLK, make_desc(a_base + ks * 2 * TILE * 16, TILE * 16, 128),
-                   make_desc(p_base + slot * (P_CHUNK_FLOATS * 4) + j * 2 * NBLK * 16, NBLK * 16, 128), idesc1,
-                   ks > 0 ? 1u : 0u);
+        for (int j = 0; j < 4 * PG; ++j) {
+          const int ks = kg * (4 * PG) + j;
+          if (p.exp_flags & 1) continue;
+          mma_pair_ss_w(tD1 + b * NBLK, make_desc(a_base + ks * 2 * TILE * 16, TILE * 16, 128),
+                        make_desc(p_base + slot * (P_GROUP_FLOATS * 4) + (j >> 2) * (P_CHUNK_FLOATS * 4) + (j & 3) * 2 * NHALF * 16,
+                                  NHALF * 16, 128),
+                        idesc1, ks > 0 ? 1u : 0u);
         }
-        mma_commit_w(bar(B_PEMPTY + slot));
+        mma_pair_commit_w(bar(B_PEMPTY + slot));
+        pc.tick(3);
       }
-      mma_commit_w(bar(B_D1FULL + b));
-      if (last_of_tile) mma_commit_w(bar(B_AFREE));
+      mma_pair_commit_w(bar(B_D1FULL + b));
+      if (last_of_tile) mma_pair_commit_w(bar(B_AFREE));
+      pc.tick(3);
     };
     auto mma2 = [&](int it, int blk) {
       const int b = blk & 1, tp = it & 1;
       mbar_wait(bar(B_SREADY + b), d1cnt[b] & 1u);
       ++d1cnt[b];
+      pc.tick(4);
       fence_after();
-      for (int kc2 = 0; kc2 < 4; ++kc2, ++wi) {
+      for (int wg = 0; wg < 4 / WG; ++wg, ++wi) {
         const uint32_t slot = wi % W_SLOTS, use = wi / W_SLOTS;
         mbar_wait(bar(B_WFULL + slot), use & 1u);
+        pc.tick(5);
+        mbar_wait(bar(B_XWFULL + slot), use & 1u);
+        pc.tick(6);
         fence_after();
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          mma_ts_w(tD2 + tp * Cpad, tD1 + b * NBLK + (kc2 * 4 + j) * 8,
-                   make_desc(w_base + slot * w_chunk_bytes + j * 2 * Cpad * 16, Cpad * 16, 128), idesc2,
-                   (blk > 0 || kc2 > 0 || j > 0) ? 1u : 0u);
-        mma_commit_w(bar(B_WEMPTY + slot));
+        for (int j = 0; j < 4 * WG; ++j)
+          if (!(p.exp_flags & 2))
+            mma_pair_ts_w(tD2 + tp * Cpad, tD1 + b * NBLK + (wg * (4 * WG) + j) * 8,
+                          make_desc(w_base + slot * w_group_bytes + (j >> 2) * w_chunk_bytes + (j & 3) * 2 * Ch * 16, Ch * 16, 128),
+                          idesc2, (blk > 0 || wg > 0 || j > 0) ? 1u : 0u);
+        mma_pair_commit_w(bar(B_WEMPTY + slot));
+        pc.tick(7);
       }
-      if (blk == nblk - 1) mma_commit_w(bar(B_D2FULL + tp));
+      if (blk == nblk - 1) mma_pair_commit_w(bar(B_D2FULL + tp));
     };
     for (int it = 0; it < iters; ++it) {
       mbar_wait(bar(B_AFULL), (uint32_t)it & 1u);
+      pc.tick(0);
       fence_after();
       mma1(0, nblk == 1);
       for (int blk = 0; blk < nblk; ++blk) {
         if (blk + 1 < nblk) mma1(blk + 1, blk + 1 == nblk - 1);
         mma2(it, blk);
+      }
+    }
+    pc.flush(0, 8);
+
+  } else if (warp == 12) {
+    // ================= peer CTA: forwarder =================
+    // Walks the chunk sequence in the leader's issue order; when one of this CTA's chunks has landed it arrives on the
+    // leader's barrier for that slot.  (The leader cannot wait on a barrier in another CTA, and a bulk copy signals a
+    // barrier of the CTA it writes to.)  A slot is reloaded only after the leader's commit for its previous use, which
+    // follows the leader's wait on that use — the forwarder is never more than one phase ahead.
+    if (lane == 0) {
+      uint32_t pi = 0, wi = 0;
+      auto fwd_p = [&]() {
+        for (int kg = 0; kg < KG; ++kg, ++pi) {
+          const uint32_t slot = pi % P_SLOTS, use = pi / P_SLOTS;
+          mbar_wait(bar(B_PFULL + slot), use & 1u);
+          mbar_arrive_cluster(bar(B_XPFULL + slot), 0);
+        }
+      };
+      auto fwd_w = [&]() {
+        for (int wg = 0; wg < 4 / WG; ++wg, ++wi) {
+          const uint32_t slot = wi % W_SLOTS, use = wi / W_SLOTS;
+          mbar_wait(bar(B_WFULL + slot), use & 1u);
+          mbar_arrive_cluster(bar(B_XWFULL + slot), 0);
+        }
+      };
+      for (int it = 0; it < iters; ++it) {
+        fwd_p();
+        for (int blk = 0; blk < nblk; ++blk) {
+          if (blk + 1 < nblk) fwd_p();
+          fwd_w();
+        }
       }
     }
   } else {
@@ -290,6 +426,8 @@ __global__ void __launch_bounds__(BIG_THREADS, 1) k_tc_fwd_big(const BigParams p
     const bool act_log = p.act_mode == ADLM_ACT_LOG;
     const float eps = p.eps, one_m_eps = 1.f - p.eps;
     uint32_t d1cnt[2] = {0u, 0u};
+    PhaseClock pc;                         // 0 D1FULL wait 1 similarity work + arrive 2 logits read-out
+    pc.start((p.exp_flags & 16) != 0 && warp == 0);
 
     auto epilogue2 = [&](int t) {
       const int tp = t & 1;
@@ -341,11 +479,13 @@ __global__ void __launch_bounds__(BIG_THREADS, 1) k_tc_fwd_big(const BigParams p
         const int db = blk & 1;
         mbar_wait(bar(B_D1FULL + db), d1cnt[db] & 1u);
         ++d1cnt[db];
+        pc.tick(0);
         fence_after();
         if (blk == 0) x2 = x2s[(it & 1) * TILE + row];
         const uint32_t t1 = tD1 + db * NBLK + lane_field;
 #pragma unroll 1
         for (int ch = 0; ch < 4; ++ch) {
+          if (p.exp_flags & 4) break;
           const int c0 = half * 64 + ch * 16, n0 = blk * NBLK + c0;
           uint32_t r[16], sb[16];
           tmem_ld16(t1 + c0, r);
@@ -374,16 +514,21 @@ __global__ void __launch_bounds__(BIG_THREADS, 1) k_tc_fwd_big(const BigParams p
         }
         tmem_st_wait();
         fence_before();
-        mbar_arrive(bar(B_SREADY + db));
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(bar(B_SREADY + db), 0);
+        pc.tick(1);
         // logits of the previous tile (its D2 is complete since its last block): the two halves alternate
         if (blk == 0 && it > 0 && ((it - 1) & 1) == half) epilogue2(it - 1);
+        pc.tick(2);
       }
     }
     if (iters > 0 && ((iters - 1) & 1) == half) epilogue2(iters - 1);
+    pc.tick(2);
+    pc.flush(8, 3);
   }
   fence_before();
-  __syncthreads();
-  if (warp == 12) tmem_dealloc(tmem_base, 512);
+  cluster_sync_all();                      // no CTA leaves while its peer may still arrive on, or read from, it
+  if (warp == 12) tmem_dealloc_pair(tmem_base, 512);
 }
 
 int g_sms_big = 0;
@@ -402,8 +547,8 @@ int sm_count_big() {
 bool tc_head_big_supported(const HeadShape& s) { return s.K <= 256 && s.N <= 1024 && s.C <= 112; }
 
 size_t tc_head_big_workspace_bytes(int K, int N, int C) {
-  const int KC = (K + KCH - 1) / KCH, nblk = (N + NBLK - 1) / NBLK, Cpad = (C + 15) & ~15;
-  return align_up((size_t)nblk * KC * P_CHUNK_FLOATS * 4, 256) + align_up((size_t)nblk * NBLK * 4, 256) +
+  const int KC = (K + KCH * PG - 1) / (KCH * PG) * PG, nblk = (N + NBLK - 1) / NBLK, Cpad = (C + 15) & ~15;
+  return align_up((size_t)nblk * KC * 2 * P_CHUNK_FLOATS * 4, 256) + align_up((size_t)nblk * NBLK * 4, 256) +
          align_up((size_t)nblk * 4 * 32 * Cpad * 4, 256);
 }
 
@@ -419,12 +564,12 @@ int tc_head_fwd_big(const HeadShape& s, const float* z, const float* P, const fl
     return ADLM_E_WORKSPACE;
   }
   BigParams prm;
-  prm.KC = (s.K + KCH - 1) / KCH;
+  prm.KC = (s.K + KCH * PG - 1) / (KCH * PG) * PG;
   prm.nblk = (s.N + NBLK - 1) / NBLK;
   prm.Cpad = (s.C + 15) & ~15;
   char* w8 = static_cast<char*>(workspace);
   float* Pst = reinterpret_cast<float*>(w8);
-  float* p2 = reinterpret_cast<float*>(w8 + align_up((size_t)prm.nblk * prm.KC * P_CHUNK_FLOATS * 4, 256));
+  float* p2 = reinterpret_cast<float*>(w8 + align_up((size_t)prm.nblk * prm.KC * 2 * P_CHUNK_FLOATS * 4, 256));
   float* Wst = reinterpret_cast<float*>(reinterpret_cast<char*>(p2) + align_up((size_t)prm.nblk * NBLK * 4, 256));
   prm.z = z; prm.Pst = Pst; prm.p2 = p2; prm.Wst = Wst;
   prm.logits = logits; prm.dist = dist; prm.argmax = argmax;
@@ -432,19 +577,41 @@ int tc_head_fwd_big(const HeadShape& s, const float* z, const float* P, const fl
   prm.eps = s.eps; prm.act_mode = s.act_mode;
   prm.M = (long long)s.B * s.HW;
   prm.num_tiles = (int)((prm.M + TILE - 1) / TILE);
-  const size_t bytes = BigSmem::total(prm.KC, prm.Cpad, prm.nblk * NBLK);
-  if (bytes > 227 * 1024) {
-    set_error("adlm_head_fwd_big: %zu bytes of shared memory needed (> 227 KB)", bytes);
+  prm.exp_flags = 0;
+  if (const char* e = getenv("ADLM_BIG_EXP")) prm.exp_flags = atoi(e);
+  const size_t fixed = BigSmem::total(prm.KC, 0, prm.Cpad, prm.nblk * NBLK);
+  const size_t room = fixed < 227 * 1024 ? 227 * 1024 - fixed : 0;
+  prm.p_slots = (int)(room / (P_GROUP_FLOATS * 4));
+  if (prm.p_slots > P_SLOTS_MAX) prm.p_slots = P_SLOTS_MAX;
+  if (const char* e = getenv("ADLM_BIG_SLOTS")) { const int v = atoi(e); if (v >= 2 && v <= prm.p_slots) prm.p_slots = v; }
+  if (prm.p_slots < 2) {
+    set_error("adlm_head_fwd_big: %zu bytes of shared memory needed before the prototype ring (> 227 KB - 16 KB)", fixed);
     return ADLM_E_UNSUPPORTED;
   }
+  const size_t bytes = BigSmem::total(prm.KC, prm.p_slots, prm.Cpad, prm.nblk * NBLK);
   k_big_stage<<<256, 256, 0, st>>>(P, W, s.N, s.K, s.C, prm.KC, prm.nblk, prm.Cpad,
                                    s.act_mode == ADLM_ACT_LOG ? LN2 : 1.f, Pst, p2, Wst);
   ADLM_LAUNCH_CHECK();
   ADLM_CUDA(cudaFuncSetAttribute(k_tc_fwd_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-  const int grid = prm.num_tiles < sm_count_big() ? prm.num_tiles : sm_count_big();
+  // one CTA pair per TPC (the kernel carries __cluster_dims__(2, 1, 1)): an even grid of at most the SM count
+  const int num_pairs = (prm.num_tiles + 1) / 2, max_pairs = sm_count_big() / 2;
+  const int grid = 2 * (num_pairs < max_pairs ? num_pairs : max_pairs);
   KernelTimer timer(ADLM_K_HEAD_FWD, st);
   k_tc_fwd_big<<<grid, BIG_THREADS, bytes, st>>>(prm);
   ADLM_LAUNCH_CHECK();
+  if (prm.exp_flags & 16) {
+    static long long h[160][DBG_SLOTS];
+    cudaStreamSynchronize(st);
+    cudaMemcpyFromSymbol(h, g_big_clocks, sizeof(h));
+    static const char* names[16] = {"mma:AFULL", "mma:PFULL", "mma:XPFULL", "mma:MMA1issue", "mma:SREADY", "mma:WFULL",
+                                    "mma:XWFULL", "mma:MMA2issue", "epi:D1FULL", "epi:work", "epi:logits", "prod:AFREE",
+                                    "prod:fill", "pload:PEMPTY", "pload:issue", "pload:latency(exp32)"};
+    for (int c = 0; c < 4 && c < grid; ++c) {
+      fprintf(stderr, "[big clocks] cta %d:", c);
+      for (int i = 0; i < 16; ++i) fprintf(stderr, " %s=%lld", names[i], h[c][i]);
+      fprintf(stderr, "\n");
+    }
+  }
   return ADLM_OK;
 }
 
