@@ -140,6 +140,13 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     if (clock64() - t0 > 4000000000LL) __trap();
   }
 }
+// one non-blocking look at a barrier phase
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile("{\n .reg .pred p;\n mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
+               : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok != 0u;
+}
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
@@ -198,6 +205,23 @@ __device__ __forceinline__ void mma_pair_ts_w(uint32_t tmem_d, uint32_t tmem_a, 
   asm volatile("{\n .reg .pred e, p;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 p, %4, 0;\n"
                " @e tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], %2, %3, p;\n}\n"
                ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// The same with the descriptors given as (low word, high word): consecutive k-steps of an operand differ only in the
+// start-address field, so the caller steps the low word by (bytes >> 4) instead of rebuilding a descriptor per MMA
+// (make_desc costs four integer instructions per operand, and the issuing warp has < 87 cycles per MMA to spend).
+__device__ __forceinline__ void mma_pair_ss_lh(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t a_hi, uint32_t b_hi,
+                                               uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n .reg .pred e, p;\n .reg .b64 da, db;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 p, %6, 0;\n"
+               " mov.b64 da, {%1, %3};\n mov.b64 db, {%2, %4};\n"
+               " @e tcgen05.mma.cta_group::2.kind::tf32 [%0], da, db, %5, p;\n}\n"
+               ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(a_hi), "r"(b_hi), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void mma_pair_ts_lh(uint32_t tmem_d, uint32_t tmem_a, uint32_t b_lo, uint32_t b_hi, uint32_t idesc,
+                                               uint32_t accumulate) {
+  asm volatile("{\n .reg .pred e, p;\n .reg .b64 db;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 p, %5, 0;\n"
+               " mov.b64 db, {%2, %3};\n"
+               " @e tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], db, %4, p;\n}\n"
+               ::"r"(tmem_d), "r"(tmem_a), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate) : "memory");
 }
 // arrives on `bar` (same offset) in both CTAs when every MMA issued so far by this thread has completed
 __device__ __forceinline__ void mma_pair_commit_w(uint32_t bar) {

@@ -121,20 +121,42 @@ __global__ void __launch_bounds__(256) k_big_stage(const float* __restrict__ P, 
 // Phase clocks (ADLM_BIG_EXP & 16): cycles each role of every CTA spent per phase, printed by the host after the launch.
 constexpr int DBG_SLOTS = 24;
 __device__ long long g_big_clocks[160][DBG_SLOTS];
+template <bool DBG>
 struct PhaseClock {
   long long t, acc[12];
   bool on;
   __device__ __forceinline__ void start(bool enable) {
-    on = enable;
+    on = DBG && enable;
     for (int i = 0; i < 12; ++i) acc[i] = 0;
     t = on ? clock64() : 0;
   }
   __device__ __forceinline__ void tick(int i) {
-    if (on) { const long long n = clock64(); acc[i] += n - t; t = n; }
+    if (DBG && on) { const long long n = clock64(); acc[i] += n - t; t = n; }
   }
   __device__ __forceinline__ void flush(int base, int count) {
-    if (on && (threadIdx.x & 31) == 0 && blockIdx.x < 160)
+    if (DBG && on && (threadIdx.x & 31) == 0 && blockIdx.x < 160)
       for (int i = 0; i < count; ++i) g_big_clocks[blockIdx.x][base + i] = acc[i];
+  }
+};
+
+// Event trace (ADLM_BIG_EXP & 64): CTA 0 logs (event, clock) of its MMA warp and of epilogue warp 0 during tiles 2-3.
+constexpr int TRACE_N = 1024;
+__device__ long long g_big_trace[2][TRACE_N];
+__device__ int g_big_trace_ev[2][TRACE_N];
+template <bool DBG>
+struct Trace {
+  int n, role;
+  bool on;
+  __device__ __forceinline__ void start(bool enable, int r) { on = DBG && enable; n = 0; role = r; }
+  __device__ __forceinline__ void enable(bool e) { on = DBG && e; }
+  __device__ __forceinline__ void ev(int id) {
+    if (DBG) {
+      if (on && n < TRACE_N && (threadIdx.x & 31) == 0) {
+        g_big_trace[role][n] = clock64();
+        g_big_trace_ev[role][n] = id;
+      }
+      if (on) ++n;
+    }
   }
 };
 
@@ -169,7 +191,9 @@ struct BigSmem {
   static __host__ __device__ size_t total(int KC, int slots, int Cpad, int Npad) { return bars(KC, slots, Cpad, Npad) + NBARS * 8 + 16; }
 };
 
+template <bool DBG>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc_fwd_big(const BigParams p) {
+  const int xf = DBG ? p.exp_flags : 0;                            // experiment flags exist in the debug build only
   extern __shared__ __align__(1024) uint8_t smem[];
   const int KC = p.KC, nblk = p.nblk, Cpad = p.Cpad, Npad = nblk * NBLK, K = p.K, N = p.N, C = p.C, HW = p.HW;
   const uint32_t P_SLOTS = (uint32_t)p.p_slots;
@@ -227,8 +251,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc
   if (warp >= 8 && warp < 12) {
     // ================= producers: thread = pixel =================
     const int cw = tid - 256;
-    PhaseClock pc;                         // 0 wait for A to be free 1 fill
-    pc.start((p.exp_flags & 16) != 0 && warp == 8);
+    PhaseClock<DBG> pc;                         // 0 wait for A to be free 1 fill
+    pc.start((xf & 16) != 0 && warp == 8);
     for (int it = 0; it < iters; ++it) {
       const int m = tile_of(it) * TILE + cw;
       const bool valid = m < Mi;
@@ -288,8 +312,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc
     // ================= prototype-chunk loader (one thread, TMA bulk copies) =================
     if (lane == 0) {
       uint32_t i = 0;
-      PhaseClock pc;                       // 0 wait for a free slot 1 issue
-      pc.start((p.exp_flags & 16) != 0);
+      PhaseClock<DBG> pc;                       // 0 wait for a free slot 1 issue
+      pc.start((xf & 16) != 0);
       for (int it = 0; it < iters; ++it)
         for (int blk = 0; blk < nblk; ++blk)
           for (int kg = 0; kg < KG; ++kg, ++i) {
@@ -299,7 +323,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc
             bulk_load(smem_u32(Pr + (size_t)slot * P_GROUP_FLOATS),
                       p.Pst + (((size_t)blk * KG + kg) * 2 + rank) * P_GROUP_FLOATS, P_GROUP_FLOATS * 4, bar(B_PFULL + slot));
             pc.tick(1);
-            if (p.exp_flags & 32) {          // serialise: measures the latency of one bulk copy (issue -> complete_tx)
+            if (xf & 32) {          // serialise: measures the latency of one bulk copy (issue -> complete_tx)
               mbar_wait(bar(B_PFULL + slot), use & 1u);
               pc.tick(2);
             }
@@ -323,30 +347,66 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc
     // ================= MMA issue (leader CTA; whole warp, one elected lane per instruction) =================
     const uint32_t idesc1 = make_idesc_tf32(2 * TILE, NBLK), idesc2 = make_idesc_tf32(2 * TILE, Cpad);
     const uint32_t a_base = smem_u32(A), p_base = smem_u32(Pr), w_base = smem_u32(Wr);
-    uint32_t pi = 0, wi = 0;                                    // chunks consumed so far
-    uint32_t d1cnt[2] = {0u, 0u};
-    PhaseClock pc;                         // 0 AFULL 1 PFULL 2 XPFULL 3 MMA1 issue 4 SREADY 5 WFULL 6 XWFULL 7 MMA2 issue
-    pc.start((p.exp_flags & 16) != 0);
-    auto mma1 = [&](int blk, bool last_of_tile) {
+    // Ring positions as (slot, parity) counters; `*_ready` = the NEXT group's barriers were already seen complete.
+    // The look at the next group's barriers sits in the MIDDLE of the current group's MMAs: a barrier round trip costs
+    // ~150 cycles and the tensor pipe queues only a few MMAs, so with the look between two groups the pipe ran dry
+    // for ~250 cycles per group (122 instead of 87 cycles per MMA in the event trace, profiles/r2_big_trace.log).
+    uint32_t p_slot = 0, p_par = 0, w_slot = 0, w_par = 0;
+    uint32_t d1par[2] = {0u, 0u};
+    bool p_ready = false, w_ready = false, s_ready = false;
+    const bool no_peek = (xf & 256) != 0;
+    PhaseClock<DBG> pc;                         // 0 AFULL 1 PFULL 2 XPFULL 3 MMA1 issue 4 SREADY 5 WFULL 6 XWFULL 7 MMA2 issue
+    pc.start((xf & 16) != 0);
+    Trace<DBG> tr;
+    tr.start(false, 0);
+    // (the vote makes the flag warp-uniform for the compiler: the MMAs that follow stay in convergent code)
+    auto peek_p = [&](uint32_t slot, uint32_t par) {
+      if (!no_peek)
+        p_ready = __all_sync(0xffffffffu, mbar_test(bar(B_PFULL + slot), par) && mbar_test(bar(B_XPFULL + slot), par));
+    };
+    auto peek_w = [&](uint32_t slot, uint32_t par) {
+      if (!no_peek)
+        w_ready = __all_sync(0xffffffffu, mbar_test(bar(B_WFULL + slot), par) && mbar_test(bar(B_XWFULL + slot), par));
+    };
+    // descriptors: high words are constant per operand, low words step by (bytes >> 4) from MMA to MMA
+    const uint32_t a_hi = (uint32_t)(make_desc(0, TILE * 16, 128) >> 32), a_lo0 = (uint32_t)make_desc(a_base, TILE * 16, 128);
+    const uint32_t p_hi = (uint32_t)(make_desc(0, NHALF * 16, 128) >> 32), p_lo0 = (uint32_t)make_desc(p_base, NHALF * 16, 128);
+    const uint32_t w_hi = (uint32_t)(make_desc(0, Ch * 16, 128) >> 32), w_lo0 = (uint32_t)make_desc(w_base, Ch * 16, 128);
+    constexpr uint32_t A_STEP = (2 * TILE * 16) >> 4, P_STEP = (2 * NHALF * 16) >> 4;   // per k-step of 8
+    const uint32_t w_step = (uint32_t)(2 * Ch * 16) >> 4;
+    const bool skip1 = (xf & 1) != 0, skip2 = (xf & 2) != 0;
+    // MMA1 of one prototype block.  `next_s` = D1 buffer whose SREADY the following mma2 will need (-1: none).
+    auto mma1 = [&](int blk, bool last_of_tile, int next_s) {
       const int b = blk & 1;
-      for (int kg = 0; kg < KG; ++kg, ++pi) {
-        const uint32_t slot = pi % P_SLOTS, use = pi / P_SLOTS;
-        mbar_wait(bar(B_PFULL + slot), use & 1u);
-        pc.tick(1);
-        mbar_wait(bar(B_XPFULL + slot), use & 1u);
-        pc.tick(2);
+      for (int kg = 0; kg < KG; ++kg) {
+        const uint32_t slot = p_slot, par = p_par;
+        if (!p_ready) {
+          mbar_wait(bar(B_PFULL + slot), par);
+          pc.tick(1);
+          tr.ev(100 + blk * 10 + kg);           // own chunk group present
+          mbar_wait(bar(B_XPFULL + slot), par);
+          pc.tick(2);
+        }
+        tr.ev(200 + blk * 10 + kg);             // both present
+        p_ready = false;
+        if (++p_slot == P_SLOTS) { p_slot = 0; p_par ^= 1u; }
         fence_after();
 #pragma unroll
         for (int j = 0; j < 4 * PG; ++j) {
           const int ks = kg * (4 * PG) + j;
-          if (p.exp_flags & 1) continue;
-          mma_pair_ss_w(tD1 + b * NBLK, make_desc(a_base + ks * 2 * TILE * 16, TILE * 16, 128),
-                        make_desc(p_base + slot * (P_GROUP_FLOATS * 4) + (j >> 2) * (P_CHUNK_FLOATS * 4) + (j & 3) * 2 * NHALF * 16,
-                                  NHALF * 16, 128),
-                        idesc1, ks > 0 ? 1u : 0u);
+          if (j == 2 * PG) {                    // half of the group is queued: look ahead
+            peek_p(p_slot, p_par);
+            if (kg == KG - 1 && next_s >= 0 && !no_peek)
+              s_ready = __all_sync(0xffffffffu, mbar_test(bar(B_SREADY + next_s), d1par[next_s]));
+          }
+          if (skip1) continue;
+          // a chunk group is contiguous in the slot: [PG][8 slabs][64 rows][4] -> one step per MMA
+          mma_pair_ss_lh(tD1 + b * NBLK, a_lo0 + (uint32_t)ks * A_STEP,
+                         p_lo0 + slot * ((P_GROUP_FLOATS * 4) >> 4) + (uint32_t)j * P_STEP, a_hi, p_hi, idesc1, ks > 0 ? 1u : 0u);
         }
         mma_pair_commit_w(bar(B_PEMPTY + slot));
         pc.tick(3);
+        tr.ev(300 + blk * 10 + kg);             // MMA1 group issued
       }
       mma_pair_commit_w(bar(B_D1FULL + b));
       if (last_of_tile) mma_pair_commit_w(bar(B_AFREE));
@@ -354,40 +414,55 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc
     };
     auto mma2 = [&](int it, int blk) {
       const int b = blk & 1, tp = it & 1;
-      mbar_wait(bar(B_SREADY + b), d1cnt[b] & 1u);
-      ++d1cnt[b];
+      if (!s_ready) mbar_wait(bar(B_SREADY + b), d1par[b]);
+      s_ready = false;
+      d1par[b] ^= 1u;
       pc.tick(4);
+      tr.ev(400 + blk * 10);                    // similarities ready
       fence_after();
-      for (int wg = 0; wg < 4 / WG; ++wg, ++wi) {
-        const uint32_t slot = wi % W_SLOTS, use = wi / W_SLOTS;
-        mbar_wait(bar(B_WFULL + slot), use & 1u);
-        pc.tick(5);
-        mbar_wait(bar(B_XWFULL + slot), use & 1u);
-        pc.tick(6);
+      for (int wg = 0; wg < 4 / WG; ++wg) {
+        const uint32_t slot = w_slot, par = w_par;
+        if (!w_ready) {
+          mbar_wait(bar(B_WFULL + slot), par);
+          pc.tick(5);
+          mbar_wait(bar(B_XWFULL + slot), par);
+          pc.tick(6);
+        }
+        tr.ev(500 + blk * 10 + wg);             // W group present (both)
+        w_ready = false;
+        if (++w_slot == W_SLOTS) { w_slot = 0; w_par ^= 1u; }
         fence_after();
 #pragma unroll
-        for (int j = 0; j < 4 * WG; ++j)
-          if (!(p.exp_flags & 2))
-            mma_pair_ts_w(tD2 + tp * Cpad, tD1 + b * NBLK + (wg * (4 * WG) + j) * 8,
-                          make_desc(w_base + slot * w_group_bytes + (j >> 2) * w_chunk_bytes + (j & 3) * 2 * Ch * 16, Ch * 16, 128),
-                          idesc2, (blk > 0 || wg > 0 || j > 0) ? 1u : 0u);
+        for (int j = 0; j < 4 * WG; ++j) {
+          if (j == 2 * WG) {
+            peek_w(w_slot, w_par);
+            if (wg == 4 / WG - 1) peek_p(p_slot, p_par);       // the next prototype group, whichever block it belongs to
+          }
+          if (!skip2)
+            mma_pair_ts_lh(tD2 + tp * Cpad, tD1 + b * NBLK + (wg * (4 * WG) + j) * 8,
+                           w_lo0 + slot * (w_group_bytes >> 4) + (uint32_t)j * w_step, w_hi, idesc2,
+                           (blk > 0 || wg > 0 || j > 0) ? 1u : 0u);
+        }
         mma_pair_commit_w(bar(B_WEMPTY + slot));
         pc.tick(7);
+        tr.ev(600 + blk * 10 + wg);             // MMA2 group issued
       }
       if (blk == nblk - 1) mma_pair_commit_w(bar(B_D2FULL + tp));
     };
     for (int it = 0; it < iters; ++it) {
+      tr.enable((xf & 64) != 0 && blockIdx.x == 0 && (it == 2 || it == 3));
+      tr.ev(10);                                // waiting for A
       mbar_wait(bar(B_AFULL), (uint32_t)it & 1u);
       pc.tick(0);
+      tr.ev(11);                                // A present
       fence_after();
-      mma1(0, nblk == 1);
+      mma1(0, nblk == 1, nblk == 1 ? 0 : -1);
       for (int blk = 0; blk < nblk; ++blk) {
-        if (blk + 1 < nblk) mma1(blk + 1, blk + 1 == nblk - 1);
+        if (blk + 1 < nblk) mma1(blk + 1, blk + 1 == nblk - 1, blk & 1);
         mma2(it, blk);
       }
     }
     pc.flush(0, 8);
-
   } else if (warp == 12) {
     // ================= peer CTA: forwarder =================
     // Walks the chunk sequence in the leader's issue order; when one of this CTA's chunks has landed it arrives on the
@@ -426,8 +501,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc
     const bool act_log = p.act_mode == ADLM_ACT_LOG;
     const float eps = p.eps, one_m_eps = 1.f - p.eps;
     uint32_t d1cnt[2] = {0u, 0u};
-    PhaseClock pc;                         // 0 D1FULL wait 1 similarity work + arrive 2 logits read-out
-    pc.start((p.exp_flags & 16) != 0 && warp == 0);
+    PhaseClock<DBG> pc;                         // 0 D1FULL wait 1 similarity work + arrive 2 logits read-out
+    pc.start((xf & 16) != 0 && warp == 0);
+    Trace<DBG> tr;
+    tr.start(false, 1);
 
     auto epilogue2 = [&](int t) {
       const int tp = t & 1;
@@ -477,15 +554,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc
       float x2 = 0.f;
       for (int blk = 0; blk < nblk; ++blk) {
         const int db = blk & 1;
+        tr.enable((xf & 64) != 0 && blockIdx.x == 0 && warp == 0 && (it == 2 || it == 3));
         mbar_wait(bar(B_D1FULL + db), d1cnt[db] & 1u);
         ++d1cnt[db];
         pc.tick(0);
+        tr.ev(700 + blk * 10);                  // D1 complete
         fence_after();
         if (blk == 0) x2 = x2s[(it & 1) * TILE + row];
         const uint32_t t1 = tD1 + db * NBLK + lane_field;
 #pragma unroll 1
         for (int ch = 0; ch < 4; ++ch) {
-          if (p.exp_flags & 4) break;
+          if (xf & 4) break;
           const int c0 = half * 64 + ch * 16, n0 = blk * NBLK + c0;
           uint32_t r[16], sb[16];
           tmem_ld16(t1 + c0, r);
@@ -517,8 +596,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(bar(B_SREADY + db), 0);
         pc.tick(1);
+        tr.ev(800 + blk * 10);                  // similarities written
+
         // logits of the previous tile (its D2 is complete since its last block): the two halves alternate
-        if (blk == 0 && it > 0 && ((it - 1) & 1) == half) epilogue2(it - 1);
+        if (blk == 0 && it > 0 && ((it - 1) & 1) == half) { epilogue2(it - 1); tr.ev(900); }
         pc.tick(2);
       }
     }
@@ -592,13 +673,27 @@ int tc_head_fwd_big(const HeadShape& s, const float* z, const float* P, const fl
   k_big_stage<<<256, 256, 0, st>>>(P, W, s.N, s.K, s.C, prm.KC, prm.nblk, prm.Cpad,
                                    s.act_mode == ADLM_ACT_LOG ? LN2 : 1.f, Pst, p2, Wst);
   ADLM_LAUNCH_CHECK();
-  ADLM_CUDA(cudaFuncSetAttribute(k_tc_fwd_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  auto kernel = prm.exp_flags != 0 ? k_tc_fwd_big<true> : k_tc_fwd_big<false>;
+  ADLM_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
   // one CTA pair per TPC (the kernel carries __cluster_dims__(2, 1, 1)): an even grid of at most the SM count
   const int num_pairs = (prm.num_tiles + 1) / 2, max_pairs = sm_count_big() / 2;
   const int grid = 2 * (num_pairs < max_pairs ? num_pairs : max_pairs);
   KernelTimer timer(ADLM_K_HEAD_FWD, st);
-  k_tc_fwd_big<<<grid, BIG_THREADS, bytes, st>>>(prm);
+  kernel<<<grid, BIG_THREADS, bytes, st>>>(prm);
   ADLM_LAUNCH_CHECK();
+  if (prm.exp_flags & 64) {
+    static long long ht[2][TRACE_N];
+    static int he[2][TRACE_N];
+    cudaStreamSynchronize(st);
+    cudaMemcpyFromSymbol(ht, g_big_trace, sizeof(ht));
+    cudaMemcpyFromSymbol(he, g_big_trace_ev, sizeof(he));
+    long long t0 = 0;
+    for (int i = 0; i < TRACE_N; ++i) if (he[0][i] == 10) { t0 = ht[0][i]; break; }
+    for (int r = 0; r < 2; ++r)
+      for (int i = 0; i < TRACE_N; ++i)
+        if (he[r][i] != 0) fprintf(stderr, "[big trace] %s %d %lld\n", r ? "epi" : "mma", he[r][i], ht[r][i] - t0);
+    cudaMemset(nullptr, 0, 0);
+  }
   if (prm.exp_flags & 16) {
     static long long h[160][DBG_SLOTS];
     cudaStreamSynchronize(st);
