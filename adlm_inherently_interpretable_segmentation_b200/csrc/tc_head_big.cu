@@ -43,8 +43,10 @@ constexpr int P_CHUNK_FLOATS = (KCH / 4) * NHALF * 4;           // 2048 floats =
 // (WG last-layer chunks).  The fixed cost of a ring step (two barrier waits, fence, commit: ~230 cycles that do not
 // overlap the MMAs) is then paid per 8 MMAs instead of per 4; the ring's depth itself does not matter (2 slots run as
 // fast as 16, gpurun_out/r2_cfg5_sweep5.log).
-constexpr int PG = 2, WG = 2;
-constexpr int P_GROUP_FLOATS = PG * P_CHUNK_FLOATS;
+// PG = 4 (16 MMAs per ring step, two slots of 32 KB) when the depth is a multiple of 128, else 2: 2.93 -> 2.75 ms at
+// cfg5.  The depth is padded to a multiple of PG chunks, so PG = 4 would double the work of a 64-deep head.
+constexpr int WG = 2;
+__host__ __device__ constexpr int pick_pg(int K) { return ((K + KCH - 1) / KCH) % 4 == 0 ? 4 : 2; }
 
 struct BigParams {
   const float* z;
@@ -56,6 +58,7 @@ struct BigParams {
   int32_t* argmax;        // [M] | null
   int B, K, HW, N, C;
   int KC;                 // depth chunks of 32, rounded up to a multiple of PG (the padding is zeros on both sides)
+  int PG;                 // prototype chunks per ring step (2 | 4)
   int nblk;               // prototype blocks of 128
   int Cpad;               // classes rounded up to 16
   float eps;
@@ -69,7 +72,7 @@ struct BigParams {
 
 // ---- one-time staging of P and W into the operand layouts (a few microseconds: ~1.5 MB) ----
 __global__ void __launch_bounds__(256) k_big_stage(const float* __restrict__ P, const float* __restrict__ W, int N, int K,
-                                                   int C, int KC, int nblk, int Cpad, float wscale,
+                                                   int C, int KC, int PG, int nblk, int Cpad, float wscale,
                                                    float* __restrict__ Pst, float* __restrict__ p2,
                                                    float* __restrict__ Wst) {
   const int Npad = nblk * NBLK;
@@ -184,25 +187,27 @@ struct BigSmem {
   // A [KPAD/4][128][4] | P ring | W ring | p2 [Npad] | x2 [2][128] | barriers | tmem base
   static __host__ __device__ size_t a() { return 0; }
   static __host__ __device__ size_t pring(int KC) { return (size_t)KC * KCH * TILE * 4; }
-  static __host__ __device__ size_t wring(int KC, int slots) { return pring(KC) + (size_t)slots * P_GROUP_FLOATS * 4; }
+  // (`slots` = ring slots x chunks per slot: the ring's size in 8 KB chunks)
+  static __host__ __device__ size_t wring(int KC, int slots) { return pring(KC) + (size_t)slots * P_CHUNK_FLOATS * 4; }
   static __host__ __device__ size_t p2(int KC, int slots, int Cpad) { return wring(KC, slots) + (size_t)W_SLOTS * WG * 32 * (Cpad / 2) * 4; }
   static __host__ __device__ size_t x2(int KC, int slots, int Cpad, int Npad) { return p2(KC, slots, Cpad) + (size_t)Npad * 4; }
   static __host__ __device__ size_t bars(int KC, int slots, int Cpad, int Npad) { return x2(KC, slots, Cpad, Npad) + 2 * TILE * 4; }
   static __host__ __device__ size_t total(int KC, int slots, int Cpad, int Npad) { return bars(KC, slots, Cpad, Npad) + NBARS * 8 + 16; }
 };
 
-template <bool DBG>
+template <bool DBG, int PG>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc_fwd_big(const BigParams p) {
+  constexpr int P_GROUP_FLOATS = PG * P_CHUNK_FLOATS;
   const int xf = DBG ? p.exp_flags : 0;                            // experiment flags exist in the debug build only
   extern __shared__ __align__(1024) uint8_t smem[];
   const int KC = p.KC, nblk = p.nblk, Cpad = p.Cpad, Npad = nblk * NBLK, K = p.K, N = p.N, C = p.C, HW = p.HW;
   const uint32_t P_SLOTS = (uint32_t)p.p_slots;
   float* A = reinterpret_cast<float*>(smem + BigSmem::a());
   float* Pr = reinterpret_cast<float*>(smem + BigSmem::pring(KC));
-  float* Wr = reinterpret_cast<float*>(smem + BigSmem::wring(KC, p.p_slots));
-  float* p2s = reinterpret_cast<float*>(smem + BigSmem::p2(KC, p.p_slots, Cpad));
-  float* x2s = reinterpret_cast<float*>(smem + BigSmem::x2(KC, p.p_slots, Cpad, Npad));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BigSmem::bars(KC, p.p_slots, Cpad, Npad));
+  float* Wr = reinterpret_cast<float*>(smem + BigSmem::wring(KC, p.p_slots * PG));
+  float* p2s = reinterpret_cast<float*>(smem + BigSmem::p2(KC, p.p_slots * PG, Cpad));
+  float* x2s = reinterpret_cast<float*>(smem + BigSmem::x2(KC, p.p_slots * PG, Cpad, Npad));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BigSmem::bars(KC, p.p_slots * PG, Cpad, Npad));
   uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + NBARS);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -628,6 +633,7 @@ int sm_count_big() {
 bool tc_head_big_supported(const HeadShape& s) { return s.K <= 256 && s.N <= 1024 && s.C <= 112; }
 
 size_t tc_head_big_workspace_bytes(int K, int N, int C) {
+  const int PG = pick_pg(K);
   const int KC = (K + KCH * PG - 1) / (KCH * PG) * PG, nblk = (N + NBLK - 1) / NBLK, Cpad = (C + 15) & ~15;
   return align_up((size_t)nblk * KC * 2 * P_CHUNK_FLOATS * 4, 256) + align_up((size_t)nblk * NBLK * 4, 256) +
          align_up((size_t)nblk * 4 * 32 * Cpad * 4, 256);
@@ -645,6 +651,8 @@ int tc_head_fwd_big(const HeadShape& s, const float* z, const float* P, const fl
     return ADLM_E_WORKSPACE;
   }
   BigParams prm;
+  const int PG = pick_pg(s.K);
+  prm.PG = PG;
   prm.KC = (s.K + KCH * PG - 1) / (KCH * PG) * PG;
   prm.nblk = (s.N + NBLK - 1) / NBLK;
   prm.Cpad = (s.C + 15) & ~15;
@@ -662,18 +670,19 @@ int tc_head_fwd_big(const HeadShape& s, const float* z, const float* P, const fl
   if (const char* e = getenv("ADLM_BIG_EXP")) prm.exp_flags = atoi(e);
   const size_t fixed = BigSmem::total(prm.KC, 0, prm.Cpad, prm.nblk * NBLK);
   const size_t room = fixed < 227 * 1024 ? 227 * 1024 - fixed : 0;
-  prm.p_slots = (int)(room / (P_GROUP_FLOATS * 4));
+  prm.p_slots = (int)(room / ((size_t)PG * P_CHUNK_FLOATS * 4));
   if (prm.p_slots > P_SLOTS_MAX) prm.p_slots = P_SLOTS_MAX;
   if (const char* e = getenv("ADLM_BIG_SLOTS")) { const int v = atoi(e); if (v >= 2 && v <= prm.p_slots) prm.p_slots = v; }
   if (prm.p_slots < 2) {
     set_error("adlm_head_fwd_big: %zu bytes of shared memory needed before the prototype ring (> 227 KB - 16 KB)", fixed);
     return ADLM_E_UNSUPPORTED;
   }
-  const size_t bytes = BigSmem::total(prm.KC, prm.p_slots, prm.Cpad, prm.nblk * NBLK);
-  k_big_stage<<<256, 256, 0, st>>>(P, W, s.N, s.K, s.C, prm.KC, prm.nblk, prm.Cpad,
+  const size_t bytes = BigSmem::total(prm.KC, prm.p_slots * PG, prm.Cpad, prm.nblk * NBLK);
+  k_big_stage<<<256, 256, 0, st>>>(P, W, s.N, s.K, s.C, prm.KC, PG, prm.nblk, prm.Cpad,
                                    s.act_mode == ADLM_ACT_LOG ? LN2 : 1.f, Pst, p2, Wst);
   ADLM_LAUNCH_CHECK();
-  auto kernel = prm.exp_flags != 0 ? k_tc_fwd_big<true> : k_tc_fwd_big<false>;
+  auto kernel = prm.exp_flags != 0 ? (PG == 4 ? k_tc_fwd_big<true, 4> : k_tc_fwd_big<true, 2>)
+                                   : (PG == 4 ? k_tc_fwd_big<false, 4> : k_tc_fwd_big<false, 2>);
   ADLM_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
   // one CTA pair per TPC (the kernel carries __cluster_dims__(2, 1, 1)): an even grid of at most the SM count
   const int num_pairs = (prm.num_tiles + 1) / 2, max_pairs = sm_count_big() / 2;

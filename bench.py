@@ -23,6 +23,9 @@ Prints ONE JSON line (rank 0):
                  cross entropy, autograd; with and without the module.py:167-208 KLD loops) on the same B200 with stock
                  torch / cuDNN / cuBLAS, allow_tf32 on and off — the "beat this" number, there being no native kernel
   cfg4           BASELINE configs[3] (mds_new: 30 prototypes, 3 classes, batch 64 of 65x65, inference + per-pixel argmax)
+  cfg5           BASELINE configs[4] (1000 prototypes x 256-d, 100 classes, one 1024x2048 map): forward + argmax on the
+                 CTA-pair tensor-core kernel, algorithmic TFLOP/s against the TF32 matmul peak measured in this run;
+                 `--workload cfg5` makes it the line itself (batch-sharded over the ranks: one map per GPU, no collective)
   push           secondary metric of BASELINE.json: push imgs/s over the 2975-image Cityscapes-train-sized synthetic set,
                  sharded over the ranks (strong scaling: N=1 scans all 2975 images, N=8 372 each), with the pass breakdown
 
@@ -57,6 +60,7 @@ sys.path.insert(0, ROOT)
 
 CFG = dict(B=16, K=64, h=65, w=65, N=190, C=19)          # BASELINE configs[1], head only
 CFG4 = dict(B=64, K=64, h=65, w=65, N=30, C=3)           # BASELINE configs[3] (mds_new.gin:6-7)
+CFG5 = dict(B=1, K=256, h=1024, w=2048, N=1000, C=100)   # BASELINE configs[4]: large head, one full-resolution map per GPU
 WEIGHTS = (1.0, 0.25, 1e-4)                              # cityscapes_kld_imnet.gin:35,38-39
 BYTES_FWD = lambda K, C: 4 * K + 4 * C                   # z in, logits out
 BYTES_BWD = lambda K, C: 4 * K + 4 * C + 4 * K           # z + dlogits in, dz out
@@ -74,7 +78,10 @@ def parse():
     ap.add_argument("--precision", default=None)
     ap.add_argument("--no-push", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--no-extras", action="store_true", help="skip the stock-torch, cfg4 and TF32-peak legs")
+    ap.add_argument("--no-extras", action="store_true", help="skip the stock-torch, cfg4, cfg5 and TF32-peak legs")
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg5"],
+                    help="cfg2 (default): the fused training step, BASELINE's metric.  cfg5: the large-head forward "
+                         "(1000 prototypes x 256-d, 100 classes, one 1024x2048 map per GPU) as the line's own metric")
     ap.add_argument("--push-images", type=int, default=None, help="size of the push set (default 2975)")
     return ap.parse_args()
 
@@ -351,6 +358,8 @@ def main():
     import torch.distributed as dist
     from adlm_inherently_interpretable_segmentation_b200 import _lib, head, parallel, push, synth
 
+    if args.workload == "cfg5":
+        return run_cfg5(args, torch, dist, head, synth)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -545,12 +554,15 @@ def main():
     del hz, ht, dz_h, g_h, sc_h, z_d, t_d, dz_d, g_d, sc_d
 
     # ---- what the same GPU does with the reference formulation in stock torch, and configs[3]
-    stock = cfg4 = None
+    stock = cfg4 = cfg5 = None
     if rank == 0 and not args.no_extras:
         stock = bench_stock_torch(torch, zs[0], P, Wt, tgts[0], pc)
         cfg4 = bench_cfg4(torch, head, synth, dev, pk, prec)
     del zs
     torch.cuda.empty_cache()
+    if rank == 0 and not args.no_extras and prec == "tf32":
+        cfg5 = bench_cfg5(torch, head, synth, dev, tf32)
+        torch.cuda.empty_cache()
 
     # ---- secondary metric: push imgs/s over the Cityscapes-train-sized synthetic set (configs[2])
     push_res = None
@@ -569,7 +581,7 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": {"fp32": "f32", "tf32": "tf32", "tf32x3": "tf32x3"}[prec],
             "data": "synthetic", "config": config_dict(prec, ring, transport), "clocks": sampler.summary(), "e2e": e2e,
             "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu, "push": push_res,
-            "stock_torch_gpu": stock, "cfg4": cfg4, "tf32_peak": tf32,
+            "stock_torch_gpu": stock, "cfg4": cfg4, "cfg5": cfg5, "tf32_peak": tf32,
             "host_issue_us_per_step": host_us, "start_gate_us": gate_us,
         }
         emit(line)
@@ -721,6 +733,139 @@ def bench_cfg4(torch, head, synth, dev, pk, prec):
                          "frac": nbytes / (ms_k * 1e-3) / 1e9 / pk["hbm"], "algorithmic_bytes": nbytes,
                          "bytes_per_pixel": 4 * K + 4 * C + 4},
             "l2_policy": f"ring of {ring} batches ({ring * M * K * 4 / 2**20:.0f} MiB)"}
+
+
+def _cfg5_inputs(torch, synth, dev, seed):
+    c = CFG5
+    B, K, h, w, N, C = c["B"], c["K"], c["h"], c["w"], c["N"], c["C"]
+    g = torch.Generator(device=dev).manual_seed(seed)
+    z = torch.empty(B, K, h, w, device=dev)
+    for k0 in range(0, K, 32):                     # 2.1 GB of features, generated in slabs
+        z[:, k0:k0 + 32].normal_(generator=g).sigmoid_()
+    P = torch.rand(N, K, device=dev, generator=g)
+    W = torch.randn(C, N, device=dev, generator=g) * 0.1
+    return z, P, W
+
+
+def _cfg5_check(torch, out, z, P, W, h, w):
+    """spot check of a strip of pixels against float64 torch (model.py:203-283); raises when the kernel is off"""
+    K, N, C = z.shape[1], P.shape[0], W.shape[0]
+    zs = z[0].reshape(K, h * w)[:, :4096].t().double()
+    d = ((zs[:, None, :] - P.double()[None]) ** 2).sum(-1)
+    ref = torch.log((d + 1) / (d + 1e-4)) @ W.double().t()
+    got = out["logits"].reshape(h * w, C)[:4096].double()
+    rel = float((got - ref).abs().max() / ref.abs().max())
+    agree = float((got.argmax(1) == ref.argmax(1)).float().mean())
+    if not (rel < 2e-3 and agree > 0.99):
+        raise RuntimeError(f"cfg5 leg: logits off by {rel:.2e} (relative), argmax agreement {agree:.4f}")
+    return rel, agree
+
+
+def bench_cfg5(torch, head, synth, dev, tf32, reps=5):
+    """BASELINE configs[4]: 1000 prototypes x 256-d, 100 classes on a 1024x2048 feature map — forward + per-pixel argmax
+    through adlm_head_fwd_big (CTA pairs, tcgen05 cta_group::2).  Tensor-bound (AI ~ 680 flop/B): the roofline is the
+    TF32 matmul peak measured in this run; algorithmic flop = (2NK + 2NC) per pixel."""
+    from adlm_inherently_interpretable_segmentation_b200 import _lib
+    c = CFG5
+    B, K, h, w, N, C = c["B"], c["K"], c["h"], c["w"], c["N"], c["C"]
+    M = B * h * w
+    z, P, W = _cfg5_inputs(torch, synth, dev, synth.BASE_SEED + 5)
+    fn = lambda: head.head_forward(z, P, W, precision="tf32", want_dist=False, want_argmax=True)
+    out = fn()
+    rel, agree = _cfg5_check(torch, out, z, P, W, h, w)
+    del out
+    _cuda_time(torch, fn, 2, warm=1)
+    with _lib.kernel_timing(_lib.K_HEAD_FWD, 64) as t:
+        ms_call = _cuda_time(torch, fn, reps, warm=0)
+    ms_k = float(np.mean(t.ms)) if t.ms else ms_call
+    tfl = FLOPS_FWD(N, K, C) * M / (ms_k * 1e-3) / 1e12
+    peak = tf32["tf32_tflops"] if tf32 else None
+    return {"workload": "configs[4]: 1000 prototypes x 256-d, 100 classes, one 1024x2048 feature map, forward + per-pixel "
+                        "argmax (logits written, no distance map)", "precision": "tf32",
+            "value": M / (ms_call * 1e-3) / 1e6, "unit": "Mpixels/s", "ms_per_call": ms_call, "kernel_ms": ms_k,
+            "roofline": {"bound": "tensor", "achieved": tfl, "peak": peak, "unit": "TFLOP/s",
+                         "frac": tfl / peak if peak else None, "flop_per_pixel": FLOPS_FWD(N, K, C),
+                         "peak_source": "TF32 matmul measured in this run (tf32_peak)"},
+            "hbm_gbs_algorithmic": (4 * K + 4 * C + 4) * M / (ms_k * 1e-3) / 1e9,
+            "check": {"logits_rel_err_vs_fp64_strip": rel, "argmax_agreement_strip": agree},
+            "l2_policy": "one 2.1 GB map: every call streams its inputs from HBM"}
+
+
+def run_cfg5(args, torch, dist, head, synth):
+    """`--workload cfg5`: the large-head forward as the line's own metric.  One map per GPU per step, no collective
+    (batch-sharded inference); barrier + synchronize around the timed steps, max over ranks."""
+    from adlm_inherently_interpretable_segmentation_b200 import _lib
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    c = CFG5
+    B, K, h, w, N, C = c["B"], c["K"], c["h"], c["w"], c["N"], c["C"]
+    M = B * h * w
+    K_steps, W_steps = min(args.steps, 20), max(min(args.warmup, 5), 3)
+    z, P, W = _cfg5_inputs(torch, synth, dev, synth.BASE_SEED + 5 + rank)
+    fn = lambda: head.head_forward(z, P, W, precision="tf32", want_dist=False, want_argmax=True)
+    rel, agree = _cfg5_check(torch, fn(), z, P, W, h, w)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    for _ in range(W_steps):
+        fn()
+    sampler = ClockSampler(local)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with sampler, _lib.kernel_timing(_lib.K_HEAD_FWD, K_steps) as t:
+        e0.record()
+        for _ in range(K_steps):
+            fn()
+        e1.record()
+        barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms)
+    ms_k = float(np.mean(t.ms)) if t.ms else ms / K_steps
+    # e2e: argmax map back on the host every step; features are produced by the backbone on the device (out of scope),
+    # so the H2D leg carries nothing here
+    amax_h = torch.empty(B, h, w, dtype=torch.int32).pin_memory()
+    barrier()
+    e0.record()
+    for _ in range(K_steps):
+        amax_h.copy_(fn()["argmax"], non_blocking=True)
+    e1.record()
+    barrier()
+    ms_e = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms_e, op=dist.ReduceOp.MAX)
+    ms_e = float(ms_e)
+    tf32 = measure_tf32_peak(torch, dev) if rank == 0 else None
+    if rank == 0:
+        tfl = FLOPS_FWD(N, K, C) * M / (ms_k * 1e-3) / 1e12
+        emit({"metric": "proto_head_fwd_mpixels_per_s", "value": world * M * K_steps / (ms * 1e-3) / 1e6,
+              "unit": "Mpixels/s", "n_gpus": world, "steps": K_steps, "warmup": W_steps, "ms_per_step": ms / K_steps,
+              "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "tf32", "data": "synthetic",
+              "config": {"workload": "configs[4] head: 1000 prototypes x 256-d, 100 classes, one 1024x2048 feature map per GPU "
+                                     "per step, forward + per-pixel argmax; backbone out of scope",
+                         "parallelism": "batch-sharded inference, no collective",
+                         "l2_policy": "one 2.1 GB map per step: inputs stream from HBM"},
+              "clocks": sampler.summary(),
+              "e2e": {"value": world * M * K_steps / (ms_e * 1e-3) / 1e6, "unit": "Mpixels/s", "h2d_bytes_per_step": 0,
+                      "d2h_bytes_per_step": int(amax_h.numel() * 4), "ms_per_step": ms_e / K_steps,
+                      "note": "argmax map to pinned host memory every step; the features come from the backbone on the device"},
+              "gpu_launches": 2 * K_steps,
+              "roofline": {"bound": "tensor", "kernel": "head_fwd (k_tc_fwd_big)", "achieved": tfl,
+                           "peak": tf32["tf32_tflops"], "unit": "TFLOP/s", "frac": tfl / tf32["tf32_tflops"],
+                           "kernel_ms": ms_k, "flop_per_pixel": FLOPS_FWD(N, K, C), "traffic": None,
+                           "peak_source": "TF32 matmul measured in this run"},
+              "cpu_baseline": None, "tf32_peak": tf32,
+              "check": {"logits_rel_err_vs_fp64_strip": rel, "argmax_agreement_strip": agree}})
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def bench_push(torch, dist, push, synth, dev, rank, world, prec, pk, n_total):

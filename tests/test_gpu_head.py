@@ -199,6 +199,58 @@ def test_forward_cfg5_crop(golden, prec):
 CFG5_TENSOR_PATH = True
 
 
+#: (B, K, h, w, N, C): shapes of the CTA-pair large-head kernel (adlm_head_fwd_big) away from cfg5 — one tile only (the
+#: pair's second CTA has no valid pixel), an odd number of tiles, tiles straddling images, partial prototype blocks,
+#: depths that are / are not a multiple of 128 (4 or 2 chunks per ring step, zero-padded depth), few and many classes,
+#: more tiles than CTA pairs (several tiles per CTA: 3 x 160 x 161 = 604 tiles over 74 pairs)
+BIG_SHAPES = [(1, 96, 7, 9, 230, 5), (1, 256, 16, 24, 1000, 100), (3, 160, 13, 17, 300, 21), (2, 128, 23, 29, 129, 112),
+              (1, 72, 10, 13, 640, 33), (3, 64, 160, 161, 256, 19)]
+
+
+@pytest.mark.parametrize("shape", BIG_SHAPES, ids=lambda s: "x".join(str(v) for v in s))
+@pytest.mark.parametrize("activation", ["log", "linear"])
+def test_large_head_kernel_shapes(shape, activation):
+    """tf32 forward through adlm_head_fwd_big against the float64 restatement of model.py:203-283: logits, distances,
+    per-pixel argmax; and logits-only calls return the same bits as calls that also write the distance map"""
+    if not available("tf32"):
+        pytest.skip("tf32 kernels not built")
+    B, K, h, w, N, C = shape
+    assert head.uses_big_head_kernel(K, N, C)
+    if activation == "linear" and B * h * w > 20000:
+        pytest.skip("one activation is enough at the many-tiles size")
+    zn = synth.features(B, K, h, w, 11)
+    Pn = np.random.default_rng(12).random((N, K)).astype(np.float32)
+    Wn = (np.random.default_rng(13).standard_normal((C, N)) * 0.1).astype(np.float32)
+    z, P, W = cuda(zn, Pn, Wn)
+    out = head.head_forward(z, P, W, activation=activation, precision="tf32", want_dist=True, want_argmax=True)
+    only = head.head_forward(z, P, W, activation=activation, precision="tf32", want_dist=False, want_argmax=True)
+    assert torch.equal(only["logits"], out["logits"]) and torch.equal(only["argmax"], out["argmax"])
+    if B * h * w > 20000:                      # float64 reference on a strip of each image (the full map takes minutes)
+        rows = slice(h // 2 - 2, h // 2 + 2)
+        ref = parity.torch_head_reference(zn[:, :, rows], Pn, Wn, activation=activation)
+        dist = out["dist"][:, :, rows].cpu().numpy()
+        logits = out["logits"][:, rows].cpu().numpy()
+        amax = out["argmax"][:, rows].cpu().numpy()
+    else:
+        ref = parity.torch_head_reference(zn, Pn, Wn, activation=activation)
+        dist, logits, amax = out["dist"].cpu().numpy(), out["logits"].cpu().numpy(), out["argmax"].cpu().numpy()
+    tol = dist_delta("tf32", K)
+    ed = np.abs(dist - ref["dist"])
+    assert ed.max() <= tol, (ed.max(), tol)
+    # a similarity moves by at most |ds/dd| * tol; d >= ~1 for random features against random prototypes
+    dref = ref["dist"]
+    slope = 1.0 if activation == "linear" else float(((1 - 1e-4) / ((dref + 1) * (dref + 1e-4))).max())
+    lt = tol * slope * np.abs(Wn).sum(1).max() + 1e-3 * np.abs(ref["logits"]).max() + 1e-4
+    el = np.abs(logits - ref["logits"])
+    print(f"[big {shape} {activation}] dist err {ed.max():.3e} (tol {tol:.3e}), logits err {el.max():.3e} (tol {lt:.3e})")
+    assert el.max() <= lt
+    srt = np.sort(ref["logits"], axis=-1)
+    gap = srt[..., -1] - srt[..., -2]
+    bad = amax != ref["logits"].argmax(axis=-1)
+    assert np.all(gap[bad] <= 2 * lt)
+    assert np.array_equal(out["argmax"].cpu().numpy(), out["logits"].cpu().numpy().argmax(axis=-1))
+
+
 @pytest.mark.parametrize("prec", list(PRECISIONS))
 def test_linear_activation_and_odd_shapes(prec):
     if not available(prec):
