@@ -8,6 +8,7 @@
 // searches them in Python; here the distance never leaves the SM: each CTA keeps a running
 // (distance bits << 32 | global patch id) minimum per prototype in shared memory and folds it into
 // the global array with one 64-bit atomicMin per prototype.
+#include <cstdlib>
 #include "common.cuh"
 
 namespace adlm {
@@ -23,17 +24,23 @@ __global__ void __launch_bounds__(256)
 k_patch_class_mask(const uint8_t* __restrict__ labels, int H, int Wimg, const int32_t* __restrict__ row_lut,
                    const int32_t* __restrict__ col_lut, int h, int w, uint32_t* __restrict__ mask_out) {
   extern __shared__ uint32_t smask[];
+  __shared__ int s_rows[2];
   const int pi = blockIdx.x, img = blockIdx.y;
   for (int j = threadIdx.x; j < w; j += blockDim.x) smask[j] = 0u;
+  if (threadIdx.x < 2) s_rows[threadIdx.x] = 0;
   __syncthreads();
   const uint8_t* lab = labels + (size_t)img * H * Wimg;
-  // first/last row of this patch row (binary search on the monotone LUT)
-  int lo = 0, hi = H;
-  while (lo < hi) { const int mid = (lo + hi) >> 1; if (row_lut[mid] < pi) lo = mid + 1; else hi = mid; }
-  const int r0 = lo;
-  hi = H;
-  while (lo < hi) { const int mid = (lo + hi) >> 1; if (row_lut[mid] <= pi) lo = mid + 1; else hi = mid; }
-  const int r1 = lo;
+  // first / one-past-last label row of this patch row: the LUT is monotone, so the CTA looks at every row once, in
+  // parallel (one round of cached loads; the two binary searches this replaces were 22 dependent round trips in a
+  // CTA whose whole payload is one batch of label loads)
+  for (int r = threadIdx.x; r < H; r += blockDim.x) {
+    if (__ldg(row_lut + r) == pi) {
+      if (r == 0 || __ldg(row_lut + r - 1) != pi) s_rows[0] = r;
+      if (r == H - 1 || __ldg(row_lut + r + 1) != pi) s_rows[1] = r + 1;
+    }
+  }
+  __syncthreads();
+  const int r0 = s_rows[0], r1 = s_rows[1];
   if (VEC) {
     const int vpr = Wimg >> 4;                      // 16-pixel vectors per row
     const int nvec = (r1 - r0) * vpr;
@@ -101,6 +108,71 @@ k_patch_class_mask(const uint8_t* __restrict__ labels, int H, int Wimg, const in
   __syncthreads();
   uint32_t* out = mask_out + ((size_t)img * h + pi) * w;
   for (int j = threadIdx.x; j < w; j += blockDim.x) out[j] = smask[j];
+}
+
+// The same, one THREAD per patch: no shared memory, no atomics, no local arrays.  A patch of the reference's maps is
+// ~8 x 8 label pixels (1024 x 2048 labels -> 129 x 257 patches); a thread reads, for each of its label rows, the one
+// or two aligned 8-byte words that cover its columns and ORs the class bits of the bytes inside its range (one
+// compare when all of them are equal, which piecewise-constant label maps make the common case).  The 32 patches
+// of a warp cover ~256 contiguous bytes per row, so the loads coalesce; neighbours' overlapping words hit L1.
+// Row / column ranges come from the monotone LUTs by a local search around the proportional guess; a CTA covers
+// MASK_PR patch rows so a thread finds its column range once.  Needs Wimg % 8 == 0 and 8-byte aligned labels.
+// Measured (tools/mask_bench.py, 512 label maps of 1024 x 2048): 446 us = 2.4 TB/s whatever the label granularity;
+// the one-CTA-per-patch-row kernel above (ADLM_MASK_CTA_KERNEL=1) does 405 us on 32-pixel label blocks but 880 us on
+// 8-pixel blocks (its slow path and shared-memory atomics).  Both are instruction-bound, not HBM-bound: a variant with
+// all 16 loads of a patch in one batch and 32-bit arithmetic needed 83 registers and ran at 787 us.
+__device__ __forceinline__ int lut_lower_bound(const int32_t* __restrict__ lut, int n, int target, int guess) {
+  // first index i with lut[i] >= target (lut non-decreasing); `guess` only sets where the search starts
+  int g = guess < 0 ? 0 : (guess > n ? n : guess);
+  while (g > 0 && __ldg(lut + g - 1) >= target) --g;
+  while (g < n && __ldg(lut + g) < target) ++g;
+  return g;
+}
+
+constexpr int MASK_PR = 8;          // patch rows per CTA: a thread's column range is found once and used for all of them
+
+__global__ void __launch_bounds__(320)
+k_patch_class_mask_thread(const uint8_t* __restrict__ labels, int H, int Wimg, const int32_t* __restrict__ row_lut,
+                          const int32_t* __restrict__ col_lut, int h, int w, uint32_t* __restrict__ mask_out) {
+  const int pi0 = blockIdx.x * MASK_PR, img = blockIdx.y;
+  const int pi1 = pi0 + MASK_PR < h ? pi0 + MASK_PR : h;
+  const uint8_t* lab = labels + (size_t)img * H * Wimg;
+  const int rstep = H / h;
+  for (int pj = threadIdx.x; pj < w; pj += blockDim.x) {
+    const int c0 = lut_lower_bound(col_lut, Wimg, pj, (int)(((unsigned)pj * (unsigned)Wimg) / (unsigned)w));
+    const int c1 = lut_lower_bound(col_lut, Wimg, pj + 1, c0 + Wimg / w);
+    const int a0 = c0 & ~7;
+    int r0 = lut_lower_bound(row_lut, H, pi0, (int)(((unsigned)pi0 * (unsigned)H) / (unsigned)h));
+    for (int pi = pi0; pi < pi1; ++pi) {
+      const int r1 = lut_lower_bound(row_lut, H, pi + 1, r0 + rstep);
+      uint32_t bits = 0u;
+      for (int a = a0; a < c1; a += 8) {                        // aligned words that touch [c0, c1)
+        const int lo = c0 > a ? c0 - a : 0, hi = c1 - a < 8 ? c1 - a : 8;
+        const unsigned long long M = (hi - lo == 8) ? ~0ull : (((1ull << ((hi - lo) * 8)) - 1ull) << (lo * 8));
+        for (int rb = r0; rb < r1; rb += 8) {                   // eight rows in flight
+          unsigned long long wv[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+            wv[u] = rb + u < r1 ? __ldg(reinterpret_cast<const unsigned long long*>(lab + (size_t)(rb + u) * Wimg + a)) : 0ull;
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            if (rb + u >= r1) break;
+            const unsigned l0 = (unsigned)(wv[u] >> (lo * 8)) & 0xffu;
+            if (((wv[u] ^ (l0 * 0x0101010101010101ull)) & M) == 0ull) {
+              if (l0 - 1u < 32u) bits |= 1u << (l0 - 1u);
+            } else {
+              for (int bq = lo; bq < hi; ++bq) {
+                const unsigned l = (unsigned)(wv[u] >> (bq * 8)) & 0xffu;
+                if (l - 1u < 32u) bits |= 1u << (l - 1u);
+              }
+            }
+          }
+        }
+      }
+      mask_out[((size_t)img * h + pi) * w + pj] = bits;
+      r0 = r1;
+    }
+  }
 }
 
 constexpr int TM = 64, TN = 64, NT = 256, PS = TN + 4;
@@ -282,7 +354,13 @@ int patch_class_mask_impl(const uint8_t* labels, int n_img, int H, int Wimg, con
   // 16-byte label loads need Wimg % 16 == 0 and 16-byte aligned rows / LUT
   const bool vec = (Wimg % 16 == 0) && ((reinterpret_cast<uintptr_t>(labels) & 15u) == 0) &&
                    ((reinterpret_cast<uintptr_t>(col_lut) & 15u) == 0);
-  if (vec) k_patch_class_mask<true><<<grid, 256, sizeof(uint32_t) * w, st>>>(labels, H, Wimg, row_lut, col_lut, h, w, mask_out);
+  const bool per_thread = (Wimg % 8 == 0) && ((reinterpret_cast<uintptr_t>(labels) & 7u) == 0) && h <= H && w <= Wimg &&
+                          getenv("ADLM_MASK_CTA_KERNEL") == nullptr;
+  if (per_thread) {
+    const int threads = w >= 320 ? 320 : ((w + 31) / 32) * 32;
+    grid.x = (h + MASK_PR - 1) / MASK_PR;
+    k_patch_class_mask_thread<<<grid, threads, 0, st>>>(labels, H, Wimg, row_lut, col_lut, h, w, mask_out);
+  } else if (vec) k_patch_class_mask<true><<<grid, 256, sizeof(uint32_t) * w, st>>>(labels, H, Wimg, row_lut, col_lut, h, w, mask_out);
   else     k_patch_class_mask<false><<<grid, 256, sizeof(uint32_t) * w, st>>>(labels, H, Wimg, row_lut, col_lut, h, w, mask_out);
   ADLM_LAUNCH_CHECK();
   return ADLM_OK;

@@ -76,6 +76,9 @@ def unpack(packed):
 
 
 # ------------------------------------------------------------------------------ device search
+_LUT_CACHE = {}
+
+
 class PushSearch:
     """Running per-prototype nearest-patch state for one push pass on one device.
 
@@ -95,15 +98,16 @@ class PushSearch:
             raise NotImplementedError(f"push supports up to {_lib.MAX_PUSH_CLASSES} classes (uint32 patch mask)")
         self.prec = _prec(precision or default_search_precision(self.K, self.N))
         self.packed = torch.full((self.N,), _lib.PUSH_NONE, device=self.device, dtype=torch.int64)
-        self._lut_cache = {}
         self.hw = None
 
     def _luts(self, H, W, h, w):
-        key = (H, W, h, w)
-        if key not in self._lut_cache:
+        # the tables depend on the four sizes only: one copy per device for the life of the process (a push pass builds
+        # a new PushSearch; recomputing and re-uploading them was host time inside every pass)
+        key = (H, W, h, w, str(self.device))
+        if key not in _LUT_CACHE:
             r, c = patch_luts(H, W, h, w)
-            self._lut_cache[key] = (torch.from_numpy(r).to(self.device), torch.from_numpy(c).to(self.device))
-        return self._lut_cache[key]
+            _LUT_CACHE[key] = (torch.from_numpy(r).to(self.device), torch.from_numpy(c).to(self.device))
+        return _LUT_CACHE[key]
 
     def class_mask(self, labels, h, w):
         """labels (n,H,W) uint8 on the device (0 = void, class = label-1) -> (n,h*w) int32 bitmask"""

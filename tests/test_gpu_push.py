@@ -17,9 +17,19 @@ def proto_class(N, C):
     return torch.arange(N, dtype=torch.int32, device="cuda") // (N // C)
 
 
-@pytest.mark.parametrize("H,W,h,w", [(64, 96, 9, 13), (50, 70, 7, 9), (1024, 2048, 129, 257), (37, 53, 5, 7)])
-def test_patch_class_mask_bit_exact(H, W, h, w):
-    labels = synth.block_labels(2, H, W, 19, block=5 if H < 200 else 32, seed=3)
+@pytest.mark.parametrize("kernel", ["thread_per_patch", "cta_per_patch_row"])
+@pytest.mark.parametrize("H,W,h,w,block", [(64, 96, 9, 13, 5), (50, 70, 7, 9, 5), (1024, 2048, 129, 257, 32),
+                                           (1024, 2048, 129, 257, 3), (37, 53, 5, 7, 5), (513, 520, 65, 65, 7),
+                                           (96, 64, 96, 64, 2), (40, 80, 3, 2, 9)])
+def test_patch_class_mask_bit_exact(H, W, h, w, block, kernel, monkeypatch):
+    """both label -> patch-mask kernels (one thread per patch for widths that are a multiple of 8; one CTA per patch row
+    otherwise and with ADLM_MASK_CTA_KERNEL set) against push.py:201-230 as restated by the oracle: coarse and
+    fine-grained label maps, odd sizes (no vector path), one pixel per patch, patches wider than two 8-byte words"""
+    if kernel == "cta_per_patch_row":
+        monkeypatch.setenv("ADLM_MASK_CTA_KERNEL", "1")
+    else:
+        monkeypatch.delenv("ADLM_MASK_CTA_KERNEL", raising=False)
+    labels = synth.block_labels(2, H, W, 19, block=block, seed=3)
     labels[1, : H // 3] = 0
     s = push.PushSearch(torch.rand(19, 8, device="cuda"), proto_class(19, 19))
     mask = s.class_mask(torch.from_numpy(labels).cuda(), h, w).cpu().numpy().view(np.uint32)
