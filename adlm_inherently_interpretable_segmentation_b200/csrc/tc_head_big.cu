@@ -164,18 +164,23 @@ struct Trace {
 };
 
 // barrier indices (same layout in both CTAs)
-constexpr int B_AFULL = 0;               // LEADER: A tiles + |z|^2 of both CTAs written (4 + 4 producer warps)
-constexpr int B_AFREE = 1;               // last MMA1 of the tile has read A (commit, both CTAs)
-constexpr int B_D1FULL = 2;              // [2] D1[b] ready (commit, both CTAs)
-constexpr int B_SREADY = 4;              // [2] LEADER: similarities back in D1[b] of both CTAs (8 + 8 epilogue warps)
-constexpr int B_D2FULL = 6;              // [2] D2[tile parity] complete (commit, both CTAs)
-constexpr int B_PFULL = 8;               // [P_SLOTS_MAX] own prototype chunk landed (expect_tx)
-constexpr int B_PEMPTY = 24;             // [P_SLOTS_MAX] MMAs of the chunk done (commit, both CTAs)
-constexpr int B_WFULL = 40;              // [W_SLOTS]
-constexpr int B_WEMPTY = 44;             // [W_SLOTS]
-constexpr int B_XPFULL = 48;             // [P_SLOTS_MAX] LEADER: the peer's chunk landed (peer's forwarder)
-constexpr int B_XWFULL = 64;             // [W_SLOTS] LEADER: same for the last-layer chunks
-constexpr int NBARS = 68;
+// The A tile is handed over in depth GROUPS (the same PG chunks a ring step covers; at most 4 groups): the MMAs of
+// the tile's first prototype block start on group 0 while the producers still fill group 1, and a group is refilled
+// for the next tile as soon as the LAST block's MMAs on it are done — under that block's remaining MMAs and the last
+// two last-layer blocks — instead of after the whole tile (the MMA warp waited ~3.7 k cycles per tile for A).
+constexpr int A_GROUPS_MAX = 4;
+constexpr int B_AFULL = 0;               // [4] LEADER: depth group of both CTAs' A tiles written (4 + 4 producer warps)
+constexpr int B_AFREE = 4;               // [4] the tile's last MMA1 on the group has read it (commit, both CTAs)
+constexpr int B_D1FULL = 8;              // [2] D1[b] ready (commit, both CTAs)
+constexpr int B_SREADY = 10;             // [2] LEADER: similarities back in D1[b] of both CTAs (8 + 8 epilogue warps)
+constexpr int B_D2FULL = 12;             // [2] D2[tile parity] complete (commit, both CTAs)
+constexpr int B_PFULL = 16;              // [P_SLOTS_MAX] own prototype chunk landed (expect_tx)
+constexpr int B_PEMPTY = 32;             // [P_SLOTS_MAX] MMAs of the chunk done (commit, both CTAs)
+constexpr int B_WFULL = 48;              // [W_SLOTS]
+constexpr int B_WEMPTY = 52;             // [W_SLOTS]
+constexpr int B_XPFULL = 56;             // [P_SLOTS_MAX] LEADER: the peer's chunk landed (peer's forwarder)
+constexpr int B_XWFULL = 72;             // [W_SLOTS] LEADER: same for the last-layer chunks
+constexpr int NBARS = 76;
 
 __device__ __forceinline__ void bulk_load(uint32_t dst_smem, const void* src, uint32_t bytes, uint32_t bar) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
@@ -225,8 +230,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc
 
   if (warp == 12) tmem_alloc_pair(smem_u32(tmem_base_s), 512);
   if (tid == 0) {
-    mbar_init(smem_u32(&bars[B_AFULL]), 8);
-    mbar_init(smem_u32(&bars[B_AFREE]), 1);
+    for (int i = 0; i < A_GROUPS_MAX; ++i) {
+      mbar_init(smem_u32(&bars[B_AFULL + i]), 8);
+      mbar_init(smem_u32(&bars[B_AFREE + i]), 1);
+    }
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&bars[B_D1FULL + i]), 1);
       mbar_init(smem_u32(&bars[B_SREADY + i]), 16);
@@ -289,16 +296,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc
       };
       load(0, zr[0]);                                            // in flight while the previous tile still owns A
       load(1, zr[1]);                                            // (KC is even: a multiple of PG)
-      if (it > 0) mbar_wait(bar(B_AFREE), (uint32_t)(it - 1) & 1u);
-      pc.tick(0);
       for (int kc = 0; kc < KC; kc += 2) {
+        const int g = kc / PG;
+        if (kc % PG == 0 && it > 0) mbar_wait(bar(B_AFREE + g), (uint32_t)(it - 1) & 1u);
+        if (kc == 0) pc.tick(0);
         put(kc, zr[0]);
         put(kc + 1, zr[1]);
+        if ((kc + 2) % PG == 0) {                                // the group is complete: hand it to the MMA warp
+          if (kc + 2 == KC) x2s[(it & 1) * TILE + cw] = x2;      // |z|^2 goes with the last group
+          fence_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(bar(B_AFULL + g), 0);
+        }
       }
-      x2s[(it & 1) * TILE + cw] = x2;
-      fence_async_smem();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(bar(B_AFULL), 0);
       pc.tick(1);
       // pull the NEXT tile's lines towards L2 now (a whole tile period ahead): its fill then pays L2, not DRAM, latency.
       // Lane l touches the warp's 128-byte line of depth l, l + 32, ...
@@ -381,7 +391,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc
     const uint32_t w_step = (uint32_t)(2 * Ch * 16) >> 4;
     const bool skip1 = (xf & 1) != 0, skip2 = (xf & 2) != 0;
     // MMA1 of one prototype block.  `next_s` = D1 buffer whose SREADY the following mma2 will need (-1: none).
-    auto mma1 = [&](int blk, bool last_of_tile, int next_s) {
+    auto mma1 = [&](int it, int blk, bool last_of_tile, int next_s) {
       const int b = blk & 1;
       for (int kg = 0; kg < KG; ++kg) {
         const uint32_t slot = p_slot, par = p_par;
@@ -393,6 +403,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc
           pc.tick(2);
         }
         tr.ev(200 + blk * 10 + kg);             // both present
+        if (blk == 0) {                         // first block of the tile: this depth group of A must have been written
+          mbar_wait(bar(B_AFULL + kg), (uint32_t)it & 1u);
+          pc.tick(0);
+        }
         p_ready = false;
         if (++p_slot == P_SLOTS) { p_slot = 0; p_par ^= 1u; }
         fence_after();
@@ -410,11 +424,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc
                          p_lo0 + slot * ((P_GROUP_FLOATS * 4) >> 4) + (uint32_t)j * P_STEP, a_hi, p_hi, idesc1, ks > 0 ? 1u : 0u);
         }
         mma_pair_commit_w(bar(B_PEMPTY + slot));
+        if (last_of_tile) mma_pair_commit_w(bar(B_AFREE + kg));
         pc.tick(3);
         tr.ev(300 + blk * 10 + kg);             // MMA1 group issued
       }
       mma_pair_commit_w(bar(B_D1FULL + b));
-      if (last_of_tile) mma_pair_commit_w(bar(B_AFREE));
       pc.tick(3);
     };
     auto mma2 = [&](int it, int blk) {
@@ -456,14 +470,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc
     };
     for (int it = 0; it < iters; ++it) {
       tr.enable((xf & 64) != 0 && blockIdx.x == 0 && (it == 2 || it == 3));
-      tr.ev(10);                                // waiting for A
-      mbar_wait(bar(B_AFULL), (uint32_t)it & 1u);
-      pc.tick(0);
-      tr.ev(11);                                // A present
-      fence_after();
-      mma1(0, nblk == 1, nblk == 1 ? 0 : -1);
+      tr.ev(10);                                // tile start
+      mma1(it, 0, nblk == 1, nblk == 1 ? 0 : -1);
       for (int blk = 0; blk < nblk; ++blk) {
-        if (blk + 1 < nblk) mma1(blk + 1, blk + 1 == nblk - 1, blk & 1);
+        if (blk + 1 < nblk) mma1(it, blk + 1, blk + 1 == nblk - 1, blk & 1);
         mma2(it, blk);
       }
     }
