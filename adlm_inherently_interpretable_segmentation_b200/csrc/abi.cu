@@ -241,6 +241,10 @@ int adlm_step_fwd_bwd_dp(const float* z, int B, int K, int HW, const float* P, c
   cm.rank = comm->rank;
   cm.world = comm->world;
   cm.timeout_ns = (unsigned long long)(comm->timeout_ms ? comm->timeout_ms : 30000u) * 1000000ull;
+  // ADLM_DP_DEFER_COUNTS=1 moves the loss-normaliser rendezvous from k_step_prepare into the forward's first logits
+  // epilogue.  Off by default: on 8 GPUs it only moves the wait (prepare -5 us, forward +8 us; 200.8 vs 197.9 us per
+  // step on one box, 224 vs 228 us on another) — what the step waits for is the slowest rank, not a latency
+  cm.defer_counts = getenv("ADLM_DP_DEFER_COUNTS") != nullptr ? 1 : 0;
   // the flags hold the low 32 bits of the counter; 0 is the buffers' initial state, so it is skipped
   cm.seq = (unsigned int)(comm->seq & 0xffffffffull);
   if (cm.seq == 0u) cm.seq = 0x80000000u | (unsigned int)(comm->seq & 1ull);

@@ -125,6 +125,8 @@ constexpr int DP_MAX_WORLD = ADLM_DP_MAX_WORLD;
 struct DpComm {
   int rank = 0, world = 1;
   unsigned int seq = 0;                  // 0 = exchange disabled
+  int defer_counts = 0;                  // k_step_prepare publishes its counts and does NOT wait for the peers': the
+                                         // forward's logits epilogue collects them at first use (tc_head_ws.cu)
   unsigned long long timeout_ns = 30000000000ull;   // bound of every wait for a peer
   char* peer[DP_MAX_WORLD] = {};
 };
@@ -193,6 +195,12 @@ struct StepExtras {
   // fused cross entropy in the forward (module.py:156-165,210-211); honoured by the warp-specialised tcgen05
   // forward only — callers must check head_fwd_fuses_ce() and run the separate CE kernel otherwise
   const int32_t* ce_counts = nullptr;    // [0] = number of CE patches
+  // data-parallel step with the loss-normaliser rendezvous deferred into the forward: the peers' counts are read
+  // from this rank's exchange buffer at the first logits epilogue; CTA 0 stores the sums to ce_counts_out for the
+  // kernels that follow (KLD, finalize)
+  DpComm ce_dp;                          // seq != 0: deferred rendezvous
+  DpLayout ce_dp_lay = {};
+  int32_t* ce_counts_out = nullptr;      // [2]
   float* ce_dlogits = nullptr;           // [B*HW, C] | null
   double* ce_accum = nullptr;            // [0] += loss sum, [1] += correct
   float ce_scale = 0.f;                  // w_ce * grad_scale

@@ -431,6 +431,14 @@ k_step_prepare(const int32_t* __restrict__ target, const int32_t* __restrict__ p
     slot_out[1] = s_terms;
     __threadfence_system();
     st_release_sys(reinterpret_cast<unsigned int*>(pb + lay.cflag) + par * Wd + comm.rank, comm.seq);
+  }
+  if (comm.defer_counts) {
+    // the rendezvous is taken off this kernel's tail: the forward collects the peers' counts when its first logits
+    // epilogue needs them and stores the sums over `counts` (until then it holds this shard's own)
+    if (tid == 0) { counts[0] = s_valid; counts[1] = s_terms; }
+    return;
+  }
+  if (tid < Wd) {
     char* me = comm.peer[comm.rank];
     const bool ok = dp_wait_flag(reinterpret_cast<const unsigned int*>(me + lay.cflag) + par * Wd + tid, comm.seq,
                                  comm.timeout_ns);
@@ -576,6 +584,11 @@ int step_fwd_bwd_impl(const HeadShape& s, int prec_mode, const float* z, const f
   if (fuse_ce) {
     // CE, accuracy and dlogits come out of the forward kernel's logits registers; logits touch HBM only on request
     ex.ce_counts = counts;
+    if (comm != nullptr && comm->defer_counts) {
+      ex.ce_dp = *comm;
+      ex.ce_dp_lay = dp_layout(s.K, N, C, comm->world);
+      ex.ce_counts_out = ws.counts;
+    }
     ex.after_prepare = 1;                  // the forward is the launch right after k_step_prepare
     ex.ce_dlogits = want_grad ? ws.dlogits : nullptr;
     ex.ce_accum = ws.accum;

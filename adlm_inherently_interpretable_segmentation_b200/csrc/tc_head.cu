@@ -473,6 +473,7 @@ int tc_head_fwd(const HeadShape& s, int prec_mode, const float* z, const float* 
   prm.target = ex.target; prm.proto_class = ex.proto_class; prm.proto_rank = ex.proto_rank;
   prm.own_dist = ex.own_dist;
   prm.ce_counts = ex.ce_counts; prm.dlogits = ex.ce_dlogits; prm.ce_accum = ex.ce_accum;
+  prm.ce_dp = ex.ce_dp; prm.ce_dp_lay = ex.ce_dp_lay; prm.ce_counts_out = ex.ce_counts_out;
   prm.ce_scale = ex.ce_scale; prm.ignore_void = ex.ignore_void;
   prm.z_out = ex.z_out;
   prm.after_prepare = ex.after_prepare;

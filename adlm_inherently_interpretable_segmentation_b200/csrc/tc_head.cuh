@@ -18,6 +18,9 @@ struct TcFwdParams {
   float* own_dist;
   // fused cross entropy (warp-specialised kernel only): all null / 0 = plain forward
   const int32_t* ce_counts;   // [0] = number of CE patches (device)
+  DpComm ce_dp;               // seq != 0: collect the peers' counts here (StepExtras::ce_dp)
+  DpLayout ce_dp_lay;
+  int32_t* ce_counts_out;     // [2] global sums for the kernels after the forward (written by CTA 0)
   float* dlogits;             // [M, C] | null
   double* ce_accum;           // [0] += sum of losses, [1] += correct patches
   float ce_scale;             // w_ce * grad_scale

@@ -261,6 +261,41 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
     const float eps = p.eps, one_m_eps = 1.f - p.eps;
     float* stg = reinterpret_cast<float*>(smem + L::stg(half, Npad, Cpad));
 
+    // Data-parallel step: the loss normaliser is the sum over all ranks.  k_step_prepare has published this rank's
+    // counts to every peer without waiting (DpComm::defer_counts); the peers' arrive in this rank's exchange buffer
+    // while the first tiles' MMAs and similarity epilogues run, and are collected here, at first use: one lane per
+    // warp acquires the `world` flags (normally already set), sums the slots in rank order — every warp of every rank
+    // gets the same bits — and CTA 0 stores the sums for the kernels that follow the forward.
+    bool have_counts = false;
+    int n_ce_global = 1;
+    auto collect_counts = [&]() {
+      // lane r looks at rank r's flag and slot (a system-scope acquire load costs ~1 us: never chain them)
+      const int par = (int)(p.ce_dp.seq & 1u), Wd = p.ce_dp.world;
+      int v = 0, t2 = 0, ok = 1;
+      if (lane < Wd) {
+        char* me = p.ce_dp.peer[p.ce_dp.rank];
+        if (!dp_wait_flag(reinterpret_cast<const unsigned int*>(me + p.ce_dp_lay.cflag) + par * Wd + lane, p.ce_dp.seq,
+                          p.ce_dp.timeout_ns))
+          ok = 0;
+        const volatile int* slot_in = reinterpret_cast<const volatile int*>(me + p.ce_dp_lay.cnt) + (par * Wd + lane) * 2;
+        v = slot_in[0];
+        t2 = slot_in[1];
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {          // integer sums: the order does not matter, every warp gets the same bits
+        v += __shfl_xor_sync(0xffffffffu, v, o);
+        t2 += __shfl_xor_sync(0xffffffffu, t2, o);
+      }
+      ok = __all_sync(0xffffffffu, ok);
+      if (blockIdx.x == 0 && warp == 0 && lane == 0) {
+        p.ce_counts_out[0] = v;
+        p.ce_counts_out[1] = t2;
+        if (!ok) p.ce_accum[3] = 1.0;       // a peer never showed up: the step is flagged as failed (scalars[7])
+      }
+      n_ce_global = v;
+      have_counts = true;
+    };
+
     auto epilogue2 = [&](int t) {
       const int b = t & 1, jb = t >> 1;
       const int tile = tile_of(t);
@@ -270,7 +305,12 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
       float ce_sc = 0.f;
       if (p.ce_accum != nullptr) {
         if (m < Mi) tg = p.target[m];
-        ce_sc = p.ce_scale / (float)p.ce_counts[0];
+        if (p.ce_dp.seq != 0u) {
+          if (!have_counts) collect_counts();
+          ce_sc = p.ce_scale / (float)n_ce_global;
+        } else {
+          ce_sc = p.ce_scale / (float)p.ce_counts[0];
+        }
       }
       mbar_wait(bar(B_D2FULL + b), (uint32_t)jb & 1u);
       fence_after();

@@ -295,12 +295,19 @@ def _replay_publish(bufs, lay, world_size, seq, src, counts, grads, acc4):
         i32[o:o + lay["n_blocks"]] = seq
 
 
-def test_dp_exchange_two_ranks_replayed_on_one_device():
+@pytest.mark.parametrize("defer", [False, True], ids=["counts_in_prepare", "counts_in_forward"])
+def test_dp_exchange_two_ranks_replayed_on_one_device(defer, monkeypatch):
     """adlm_step_fwd_bwd_dp on rank 1 of 2, with rank 0's publications replayed into the exchange buffers from the
     global_counts API: reduced dP / dW / scalars equal the whole-batch step, and what rank 1 published into rank
-    0's buffer is exactly its own shard's partial result.  Two consecutive steps cover both slot parities."""
+    0's buffer is exactly its own shard's partial result.  Two consecutive steps cover both slot parities.  Both
+    places of the loss-normaliser rendezvous: k_step_prepare's tail (default) and the forward's first logits epilogue
+    (ADLM_DP_DEFER_COUNTS)."""
     if not available("tf32"):
         pytest.skip("tf32 kernels not built")
+    if defer:
+        monkeypatch.setenv("ADLM_DP_DEFER_COUNTS", "1")
+    else:
+        monkeypatch.delenv("ADLM_DP_DEFER_COUNTS", raising=False)
     z, P, W, target, pc, (K, N, C) = _dp_case()
     wts = (1.0, 0.25, 1e-4)
     full = head.fused_step(z, P, W, target, pc, weights=wts, precision="tf32")
@@ -362,10 +369,15 @@ def test_dp_exchange_world_of_one_and_limits():
         ex.next_comm(K, N + 1, C)
 
 
-def test_dp_exchange_dead_peer_times_out_with_nan():
+@pytest.mark.parametrize("defer", [False, True], ids=["counts_in_prepare", "counts_in_forward"])
+def test_dp_exchange_dead_peer_times_out_with_nan(defer, monkeypatch):
     """a peer that never publishes: the bounded waits expire (timeout_ms each), gradients are NaN, scalars[7] > 0"""
     if not available("tf32"):
         pytest.skip("tf32 kernels not built")
+    if defer:
+        monkeypatch.setenv("ADLM_DP_DEFER_COUNTS", "1")
+    else:
+        monkeypatch.delenv("ADLM_DP_DEFER_COUNTS", raising=False)
     z, P, W, target, pc, (K, N, C) = _dp_case(seed=91)
     exs = parallel.DpExchange.local(K, N, C, z.device, 2)
     exs[0].timeout_ms = 300
