@@ -415,8 +415,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(BIG_THREADS, 1) k_tc
           const int ks = kg * (4 * PG) + j;
           if (j == 2 * PG) {                    // half of the group is queued: look ahead
             peek_p(p_slot, p_par);
-            if (kg == KG - 1 && next_s >= 0 && !no_peek)
+            if (kg == KG - 1 && next_s >= 0 && !no_peek) {
               s_ready = __all_sync(0xffffffffu, mbar_test(bar(B_SREADY + next_s), d1par[next_s]));
+              // the look from the previous block's last-layer MMAs came too early for a two-slot ring (the slot had
+              // just been freed): look again now that the reload had a whole MMA1 block to land
+              if (!w_ready) peek_w(w_slot, w_par);
+            }
           }
           if (skip1) continue;
           // a chunk group is contiguous in the slot: [PG][8 slabs][64 rows][4] -> one step per MMA
