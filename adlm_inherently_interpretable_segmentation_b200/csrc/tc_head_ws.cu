@@ -130,10 +130,11 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
   // Wk: B operand of MMA2, rows = classes, K index = prototype: [Npad/4][Cpad][4]; ln 2 folded in
   stage_w_kmajor(Wk, p.W, C, N, Cpad, Npad, p.act_mode == ADLM_ACT_LOG ? LN2 : 1.f, tid, WS_THREADS);
   __syncthreads();
-  // Everything above (TMEM, barriers, first feature tile in flight, P and W staged) is independent of the step's
-  // prologue kernel; its outputs (prototype ranks here, the CE normaliser and the cleared accumulators in the logits
-  // epilogue) are read from here on.  No-op unless launched with programmatic stream serialisation.
-  asm volatile("griddepcontrol.wait;" ::: "memory");
+  // Everything up to the first logits epilogue is independent of the step's prologue kernel (k_step_prepare), under
+  // which this grid may have started: TMEM, barriers, feature tiles, P and W, the first tiles' MMAs and similarity
+  // epilogues.  The prototype ranks are recomputed here from proto_class (an input) instead of being read from the
+  // prologue's output, so the wait for that grid sits where its outputs are first touched: the CE normaliser and the
+  // cleared accumulators, in the logits epilogue (`waited` in epilogue2).
   for (int n = tid; n < Npad; n += WS_THREADS) {
     // |p|^2 of the ROUNDED vector, so that z == p gives d == 0
     float a = 0.f;
@@ -142,8 +143,15 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
       a = fmaf(v.x, v.x, a); a = fmaf(v.y, v.y, a); a = fmaf(v.z, v.z, a); a = fmaf(v.w, v.w, a);
     }
     p2s[n] = a;
-    // rank < 0: the prototype lies beyond ADLM_MAX_PROTOS_PER_CLASS (the prologue kernel flags the step as failed)
-    const int rk = (want_own && n < N) ? p.proto_rank[n] : -1;
+    // rank of the prototype inside its class = earlier prototypes of the same class (k_step_prepare's rule, loss.cu);
+    // beyond the per-class capacity of the KLD side buffers it is -1 and the prologue kernel fails the step
+    int rk = -1;
+    if (want_own && n < N) {
+      const int c = __ldg(p.proto_class + n);
+      int r = 0;
+      for (int m = 0; m < n; ++m) r += (__ldg(p.proto_class + m) == c);
+      rk = r < JMAX ? r : -1;
+    }
     pcs[n] = rk >= 0 ? p.proto_class[n] : -1;
     prs[n] = rk >= 0 ? rk : 0;
   }
@@ -266,7 +274,7 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
     // while the first tiles' MMAs and similarity epilogues run, and are collected here, at first use: one lane per
     // warp acquires the `world` flags (normally already set), sums the slots in rank order — every warp of every rank
     // gets the same bits — and CTA 0 stores the sums for the kernels that follow the forward.
-    bool have_counts = false;
+    bool have_counts = false, waited = false;
     int n_ce_global = 1;
     auto collect_counts = [&]() {
       // lane r looks at rank r's flag and slot (a system-scope acquire load costs ~1 us: never chain them)
@@ -303,6 +311,10 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
       // label and CE normaliser travel while the last-layer MMA finishes
       int tg = -1;
       float ce_sc = 0.f;
+      if (!waited) {                       // no-op unless launched with programmatic stream serialisation
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        waited = true;
+      }
       if (p.ce_accum != nullptr) {
         if (m < Mi) tg = p.target[m];
         if (p.ce_dp.seq != 0u) {
