@@ -239,6 +239,10 @@ def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
     dz_out: optional preallocated contiguous fp32 CUDA tensor shaped like z that receives dz (pipelined callers).
     dp_comm: a parallel.DpExchange — the step then runs adlm_step_fwd_bwd_dp: normalisers, dP, dW and the loss
     sums are exchanged with the peer GPUs inside the step's own kernels (no collective call afterwards).
+    need_grads: True (dz, dP, dW), False (loss values only) or "last_layer": only dW — the reference's last-layer phase
+    after push (train_and_test.last_only, module.py:106-108,384-390: features, add-on layers and prototypes are frozen).
+    In the fp32-class modes that phase runs in (`fp32`, `tf32x3`; distances of pushed prototypes are ~0 there) the
+    backward then skips the dz and dP contractions, two thirds of its work; dz and dP are None in the result.
     pre_sigmoid: `z` holds the features BEFORE the add-on Sigmoid; the step applies it in the forward kernel,
     returns z = sigmoid(input) under "z" and dz is the gradient wrt the pre-sigmoid input
     (adlm_step_fwd_bwd_pre; tf32 only, not combined with dp_comm)."""
@@ -266,19 +270,25 @@ def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
         if workspace is None or workspace.numel() < need:
             workspace = torch.empty(need, device=dev, dtype=torch.uint8)
         scalars = torch.empty(_lib.STEP_NSCALARS, device=dev, dtype=torch.float64)
+        last_only = isinstance(need_grads, str)
+        if last_only and need_grads != "last_layer":
+            raise ValueError('need_grads must be True, False or "last_layer"')
+        # the tensor-core backward (tf32) always forms all three gradients; the CUDA-core one skips what is not asked for
+        skip_zp = last_only and _prec(precision or DEFAULT_PRECISION) != _lib.PREC_TF32 and dp_comm is None \
+            and not pre_sigmoid
         if need_grads and dz_out is not None:
             if dz_out.shape != z.shape or dz_out.dtype != torch.float32 or not dz_out.is_cuda or not dz_out.is_contiguous():
                 raise ValueError("dz_out must be a contiguous CUDA float32 tensor shaped like z")
             dz = dz_out
         else:
-            dz = torch.empty_like(z) if need_grads else None
+            dz = torch.empty_like(z) if (need_grads and not skip_zp) else None
         if need_grads and grads_out is not None:
             if grads_out.dtype != torch.float32 or not grads_out.is_cuda or grads_out.numel() < N * K + C * N:
                 raise ValueError("grads_out must be a CUDA float32 buffer with >= N*K + C*N elements")
             dP = grads_out[:N * K].view(N, K)
             dW = grads_out[N * K:N * K + C * N].view(C, N)
         else:
-            dP = torch.empty((N, K), device=dev, dtype=torch.float32) if need_grads else None
+            dP = torch.empty((N, K), device=dev, dtype=torch.float32) if (need_grads and not skip_zp) else None
             dW = torch.empty((C, N), device=dev, dtype=torch.float32) if need_grads else None
         logits = torch.empty((B, h, w, C), device=dev, dtype=torch.float32) if want_logits else None
         amax = torch.empty((B, h, w), device=dev, dtype=torch.int32) if want_argmax else None
@@ -317,6 +327,8 @@ def fused_step(z, prototypes, weight, target, proto_class, ignore_void=True,
                                        _lib.ptr(dz), _lib.ptr(dP), _lib.ptr(dW), _lib.ptr(scalars),
                                        _lib.ptr(workspace), c_size_t(workspace.numel()), _lib.stream_ptr())
     _lib.check(rc, "adlm_step_fwd_bwd")
+    if last_only:
+        dz = dP = None
     if dP is not None:
         dP = dP.reshape(prototypes.shape)
     return _StepResult(scalars=scalars, dz=dz, dP=dP, dW=dW, logits=logits, argmax=amax, workspace=workspace,

@@ -270,6 +270,27 @@ def test_step_flat_gradient_buffer_and_optional_logits(prec):
 
 
 # ------------------------------------------------------------------ peer-memory data-parallel step (one device)
+@pytest.mark.parametrize("prec", list(PREC_SCALE))
+@pytest.mark.parametrize("name", ["step_small_A", "step_small_B"])
+def test_last_layer_only_step_matches_reference_step(golden, name, prec):
+    """the reference's last-layer phase (train_and_test.last_only: only last_layer.weight trains, module.py:106-108):
+    need_grads="last_layer" gives the same loss terms and dW as the reference's _step and no dz / dP; in the
+    fp32-class modes the backward skips those contractions"""
+    if not available(prec):
+        pytest.skip(f"{prec} kernels not built")
+    g = golden(name)
+    ltol, gtol = (t * PREC_SCALE[prec] for t in STEP_TOL[name])
+    res = run_step(g, prec, need_grads="last_layer")
+    full = run_step(g, prec)
+    assert res.dz is None and res.dP is None
+    sc, scf = res.scalars.cpu().numpy(), full.scalars.cpu().numpy()
+    assert np.array_equal(sc[:7], scf[:7])                       # the forward and the loss kernels are the same launches
+    assert abs(sc[0] - float(g["loss"])) <= ltol * abs(float(g["loss"]))
+    dW, ref = res.dW.cpu().numpy(), g["dW"]
+    assert np.abs(dW - ref).max() <= gtol * np.abs(ref).max()
+    assert np.abs(dW - full.dW.cpu().numpy()).max() <= 1e-6 * np.abs(ref).max() + 1e-9    # atomics reorder the sums
+
+
 def _dp_case(seed=71):
     B, K, h, w, N, C = 4, 64, 13, 17, 190, 19
     zn, Pn, Wn = synth.head_inputs(B, K, h, w, N, C, w_noise=0.1, seed=seed)
