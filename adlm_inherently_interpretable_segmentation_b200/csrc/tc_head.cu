@@ -15,6 +15,7 @@
 // Two warpgroups per CTA run this pipeline on alternating tiles, so one group's MUFU-bound epilogue
 // overlaps the other's loads and MMAs; the grid is persistent (one CTA per SM).
 // 3xTF32 keeps fp32-class distances (hi*lo + lo*hi + hi*hi) and does the last layer in fp32 FMA.
+#include <cstdlib>
 #include "tc_head.cuh"
 #include "tc_common.cuh"
 
@@ -47,14 +48,18 @@ struct FwdSmem {
   // byte offsets
   static __host__ __device__ size_t pk(int part, int Npad) { return (size_t)part * KP * Npad * 4; }
   static __host__ __device__ size_t wk(int Npad) { return (size_t)PARTS * KP * Npad * 4; }
-  static __host__ __device__ size_t wk_bytes(int Npad, int Cpad) { return (size_t)Npad * (X3 ? 32 : Cpad) * 4; }
-  static __host__ __device__ size_t abuf(int wg, int part, int Npad, int Cpad) {
-    return wk(Npad) + wk_bytes(Npad, Cpad) + ((size_t)wg * PARTS + part) * KP * TILE * 4;
+  // 3xTF32: [Npad][32] fp32 for the CUDA-core last layer, or hi + lo K-major operands (2 x Npad x Cpad) for the
+  // tensor-core one — the larger of the two, so one layout serves both (Cpad <= 32)
+  static __host__ __device__ size_t wk_bytes(int Npad, int Cpad, bool tcl = false) {
+    return (size_t)Npad * (X3 ? (tcl ? 2 * Cpad : 32) : Cpad) * 4;
   }
-  static __host__ __device__ size_t misc(int Npad, int Cpad) { return abuf(NWG, 0, Npad, Cpad); }
-  static __host__ __device__ size_t total(int Npad, int Cpad) {
+  static __host__ __device__ size_t abuf(int wg, int part, int Npad, int Cpad, bool tcl = false) {
+    return wk(Npad) + wk_bytes(Npad, Cpad, tcl) + ((size_t)wg * PARTS + part) * KP * TILE * 4;
+  }
+  static __host__ __device__ size_t misc(int Npad, int Cpad, bool tcl = false) { return abuf(NWG, 0, Npad, Cpad, tcl); }
+  static __host__ __device__ size_t total(int Npad, int Cpad, bool tcl = false) {
     // p2 [Npad] f32, class [Npad] i32, rank [Npad] i32, chunk class masks [Npad/16] u32, barriers, tmem base
-    return misc(Npad, Cpad) + (size_t)Npad * 12 + (size_t)(Npad / 16) * 4 + 64 + 16;
+    return misc(Npad, Cpad, tcl) + (size_t)Npad * 12 + (size_t)(Npad / 16) * 4 + 64 + 16;
   }
 };
 
@@ -68,7 +73,9 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
   float* Pk_hi = reinterpret_cast<float*>(smem + L::pk(0, Npad));
   float* Pk_lo = reinterpret_cast<float*>(smem + L::pk(X3 ? 1 : 0, Npad));
   float* Wk = reinterpret_cast<float*>(smem + L::wk(Npad));
-  uint8_t* misc = smem + L::misc(Npad, Cpad);
+  const bool tcl = X3 && p.x3_tensor_last != 0;          // 3xTF32 with the last layer on the tensor cores
+  float* Wk_lo = Wk + (size_t)Npad * Cpad;               // (tcl) low parts, same K-major layout
+  uint8_t* misc = smem + L::misc(Npad, Cpad, tcl);
   float* p2s = reinterpret_cast<float*>(misc);
   int* pcs = reinterpret_cast<int*>(misc + (size_t)Npad * 4);
   int* prs = reinterpret_cast<int*>(misc + (size_t)Npad * 8);
@@ -81,7 +88,7 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
 
   ADLM_PHASE(0);
   // ---- one-time setup: TMEM, barriers, prototype / last-layer operands ----
-  if (tid < 32) tmem_alloc(smem_u32(tmem_base_s), NWG * 256);
+  if (tid < 32) tmem_alloc(smem_u32(tmem_base_s), X3 ? 512 : NWG * 256);
   if (tid == 32) {
     for (int i = 0; i < 4; ++i) mbar_init(smem_u32(&bars[i]), 1);
     mbar_init_fence();
@@ -138,6 +145,17 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
         }
       }
     }
+  } else if (tcl) {
+    // hi + lo K-major B operands of the last-layer MMAs: [Npad/4][Cpad][4] each, w = hi + lo with hi = rna(w),
+    // lo = rna(w - hi); the similarities stay in natural-log units here (no ln 2 folded in)
+    for (int idx = tid; idx < Npad * Cpad; idx += NTHREADS) {
+      const int n = idx / Cpad, c = idx - n * Cpad;
+      const float wv = (c < C && n < N) ? __ldg(p.W + (size_t)c * N + n) : 0.f;
+      const float hi = rna_tf32_mask(wv);
+      const size_t o = (size_t)(n >> 2) * Cpad * 4 + c * 4 + (n & 3);
+      Wk[o] = hi;
+      Wk_lo[o] = rna_tf32_mask(wv - hi);
+    }
   } else {
     // plain fp32 [Npad][32] for the CUDA-core last layer
     for (int idx = tid; idx < Npad * 32; idx += NTHREADS) {
@@ -185,10 +203,11 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
 
   const uint32_t tmem_base = *tmem_base_s;
   const uint32_t d1 = tmem_base + wg * 256;              // [128 lanes x Npad cols]
-  const uint32_t d2 = d1 + Npad;                         // [128 lanes x Cpad cols]
+  const uint32_t slo = d1 + Npad;                        // (tcl) low parts of the similarities [128 x Npad]
+  const uint32_t d2 = d1 + (tcl ? 2 * Npad : Npad);      // [128 lanes x Cpad cols]
   const uint32_t lane_field = (uint32_t)(warp_in_wg * 32) << 16;
-  float* Ahi = reinterpret_cast<float*>(smem + L::abuf(wg, 0, Npad, Cpad));
-  float* Alo = reinterpret_cast<float*>(smem + L::abuf(wg, X3 ? 1 : 0, Npad, Cpad));
+  float* Ahi = reinterpret_cast<float*>(smem + L::abuf(wg, 0, Npad, Cpad, tcl));
+  float* Alo = reinterpret_cast<float*>(smem + L::abuf(wg, X3 ? 1 : 0, Npad, Cpad, tcl));
   const uint32_t bar_d1 = smem_u32(&bars[wg * 2]), bar_d2 = smem_u32(&bars[wg * 2 + 1]);
   const uint32_t idesc1 = make_idesc_tf32(TILE, Npad), idesc2 = make_idesc_tf32(TILE, Cpad);
   const int ksteps = (K + 7) >> 3;
@@ -294,7 +313,10 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
 #if defined(ADLM_EXP) && ADLM_EXP == 1
         if (act_log) s = (d + 1.f) - 0.5f * (d + eps);
 #else
-        if (act_log) s = X3 ? logf((d + 1.f) / (d + eps)) : lg2_approx(d + 1.f) - lg2_approx(d + eps);
+        // 3xTF32: log(1 + (1-eps)/(d+eps)) with the hardware reciprocal and log2 (each ~1 ulp; the form has no
+        // cancellation, so the similarity is good to ~3e-7 absolute — logf + a division cost ~40 instructions here,
+        // most of this kernel's time)
+        if (act_log) s = X3 ? LN2 * lg2_approx(fmaf(1.f - eps, rcp_approx(d + eps), 1.f)) : lg2_approx(d + 1.f) - lg2_approx(d + eps);
 #endif
         else s = -d;
         sv[i] = s;
@@ -302,6 +324,17 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
       }
       if (!X3) {
         tmem_st16(t1 + ch * 16, sv_bits);
+      } else if (tcl) {
+        // s = hi + lo: both parts go back to tensor memory as A operands of the last-layer MMAs
+        uint32_t lo_bits[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const float hi = rna_tf32_mask(sv[i]);
+          sv_bits[i] = __float_as_uint(hi);
+          lo_bits[i] = __float_as_uint(rna_tf32_mask(sv[i] - hi));
+        }
+        tmem_st16(t1 + ch * 16, sv_bits);
+        tmem_st16(slo + lane_field + ch * 16, lo_bits);
       } else {
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
@@ -360,16 +393,21 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
 
     ADLM_PHASE(ph); ++ph;                      // +5 epilogue 1 done
     float lg[32];
-    if (!X3) {
-      // ---- MMA2: logits = S . W^T with S read from TMEM ----
+    if (!X3 || tcl) {
+      // ---- MMA2: logits = S . W^T with S read from TMEM (3xTF32: Sh.Wh + Sh.Wl + Sl.Wh) ----
       tmem_st_wait();
       fence_before();
       named_bar_sync(1 + wg, 128);
       if (wt == 0) {
         fence_after();
-        const uint32_t wb = smem_u32(Wk);
-        for (int ks = 0; ks < Npad / 8; ++ks)
+        const uint32_t wb = smem_u32(Wk), wbl = smem_u32(Wk_lo);
+        for (int ks = 0; ks < Npad / 8; ++ks) {
           mma_ts(d2, d1 + ks * 8, make_desc(wb + ks * 2 * Cpad * 16, Cpad * 16, 128), idesc2, ks > 0 ? 1u : 0u);
+          if (tcl) {
+            mma_ts(d2, d1 + ks * 8, make_desc(wbl + ks * 2 * Cpad * 16, Cpad * 16, 128), idesc2, 1u);
+            mma_ts(d2, slo + ks * 8, make_desc(wb + ks * 2 * Cpad * 16, Cpad * 16, 128), idesc2, 1u);
+          }
+        }
         mma_commit(bar_d2);
       }
       mbar_wait(bar_d2, parity);
@@ -428,7 +466,7 @@ __global__ void __launch_bounds__(FwdSmem<KP, X3>::NWG * 128, 1) k_tc_fwd(const 
 
   __syncthreads();
   ADLM_PHASE(63);
-  if (tid < 32) tmem_dealloc(tmem_base, NWG * 256);
+  if (tid < 32) tmem_dealloc(tmem_base, X3 ? 512 : NWG * 256);
 }
 
 int g_num_sms = 0;
@@ -443,9 +481,14 @@ int num_sms() {
 }
 
 template <int KP, bool X3>
-int launch_fwd(const TcFwdParams& prm, cudaStream_t st) {
+int launch_fwd(const TcFwdParams& prm_in, cudaStream_t st) {
   using L = FwdSmem<KP, X3>;
-  const size_t bytes = L::total(prm.Npad, prm.Cpad) + 64;
+  TcFwdParams prm = prm_in;
+  // 3xTF32: the last layer runs on the tensor cores when its doubled operand fits shared memory and the low parts
+  // of the similarities fit tensor memory (2 Npad + Cpad <= 512 columns); ADLM_X3_FMA_LAST_LAYER=1 keeps the fp32 FMAs
+  prm.x3_tensor_last = (X3 && L::total(prm.Npad, prm.Cpad, true) + 64 <= 227 * 1024 && 2 * prm.Npad + prm.Cpad <= 512 &&
+                        getenv("ADLM_X3_FMA_LAST_LAYER") == nullptr) ? 1 : 0;
+  const size_t bytes = L::total(prm.Npad, prm.Cpad, prm.x3_tensor_last != 0) + 64;
   if (bytes > 227 * 1024) {
     set_error("tc_head_fwd: %zu bytes of shared memory needed (> 227 KB) for K=%d N=%d", bytes, prm.K, prm.N);
     return ADLM_E_UNSUPPORTED;

@@ -35,6 +35,9 @@ struct TcFwdParams {
   // launched right after k_step_prepare with programmatic stream serialisation: the CTAs start while the prologue
   // kernel still runs, stage their operands and only then wait for it (griddepcontrol.wait)
   int after_prepare;
+  // 3xTF32 forward (k_tc_fwd<.., true>): last layer on the tensor cores too (S and W split in hi + lo, three MMAs per
+  // k-step) when the doubled last-layer operand fits shared memory; otherwise fp32 FMAs in the epilogue threads
+  int x3_tensor_last;
 };
 // 1xTF32, K <= 64: producer / MMA / epilogue warps, double-buffered TMEM accumulators (tc_head_ws.cu)
 int tc_head_fwd_ws(const TcFwdParams& prm, cudaStream_t st);
