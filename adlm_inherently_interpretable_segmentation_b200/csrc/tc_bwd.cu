@@ -34,8 +34,16 @@ __device__ long long g_dp_phase[3][64];
   do {                                                                                              \
     if (blockIdx.x == 0 && (threadIdx.x & 31) == 0 && (i) < 64) g_dp_phase[(role)][(i)] = clock64(); \
   } while (0)
+// ... and of k_tc_bwd_dz per warpgroup (thread 0 of each): tile start, operands written, D/Gl done (h = 0), epilogue
+// done, D/Gl done (h = 1), epilogue done, dZ done, stored — 8 stamps per tile
+__device__ long long g_dz_phase[2][64];
+#define DZ_PHASE(i)                                                                          \
+  do {                                                                                       \
+    if (blockIdx.x == 0 && wt == 0 && (i) < 64) g_dz_phase[wg][(i)] = clock64();             \
+  } while (0)
 #else
 #define DP_PHASE(role, i)
+#define DZ_PHASE(i)
 #endif
 
 struct TcBwdParams {
@@ -190,11 +198,14 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
   const float eps = p.eps, epsm1 = p.eps - 1.f;
   const bool act_log = p.act_mode == ADLM_ACT_LOG;
 
+  int dzph = 1;
+  DZ_PHASE(0);
   for (; tile < p.num_tiles; tile += stride) {
     const int m = tile * TILE + wt;
     const bool valid = m < Mi;
     const int b = valid ? m / HW : 0;
     const int pix = valid ? m - b * HW : 0;
+    DZ_PHASE(dzph); ++dzph;                  // tile start
 
     // ---- operands of this tile: Zk (centred, rounded), dLk ----
     float x2 = 0.f;
@@ -228,24 +239,28 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
     fence_before();
     named_bar_sync(1 + wg, 128);
     prefetch(tile + stride);
+    DZ_PHASE(dzph); ++dzph;                  // operands written, next tile's loads issued
 
     float rs = 0.f;
     for (int h = 0; h < 2; ++h) {
-      if (wt == 0) {
+      // MMAs are issued by the warpgroup's first warp as a whole (one elected lane per instruction): from a single
+      // thread every tcgen05.mma costs ~120 cycles of descriptor shuffling into uniform registers (tc_common.cuh)
+      if (warp_in_wg == 0) {
         fence_after();
         const uint32_t a0 = smem_u32(Zk), b0 = smem_u32(Pk) + h * NH * 16;
         for (int ks = 0; ks < ksteps; ++ks)
-          mma_ss(tD, make_desc(a0 + ks * 2 * TILE * 16, TILE * 16, 128), make_desc(b0 + ks * 2 * Npad * 16, Npad * 16, 128),
-                 idesc_h, ks > 0 ? 1u : 0u);
+          mma_ss_w(tD, make_desc(a0 + ks * 2 * TILE * 16, TILE * 16, 128), make_desc(b0 + ks * 2 * Npad * 16, Npad * 16, 128),
+                   idesc_h, ks > 0 ? 1u : 0u);
         const uint32_t l0 = smem_u32(dLk), w0 = smem_u32(Wt) + h * NH * 16;
         for (int ks = 0; ks < C8 / 8; ++ks)
-          mma_ss(tG, make_desc(l0 + ks * 2 * TILE * 16, TILE * 16, 128), make_desc(w0 + ks * 2 * Npad * 16, Npad * 16, 128),
-                 idesc_h, ks > 0 ? 1u : 0u);
-        mma_commit(bar_a);
+          mma_ss_w(tG, make_desc(l0 + ks * 2 * TILE * 16, TILE * 16, 128), make_desc(w0 + ks * 2 * Npad * 16, Npad * 16, 128),
+                   idesc_h, ks > 0 ? 1u : 0u);
+        mma_commit_w(bar_a);
       }
       mbar_wait(bar_a, ph_a);
       ph_a ^= 1u;
       fence_after();
+      DZ_PHASE(dzph); ++dzph;                // D / Gl of this half done
       for (int ch = 0; ch < NH / 16; ++ch) {
         uint32_t ra[16], rg[16], out[16];
         tmem_ld16(tD + lane_field + ch * 16, ra);
@@ -294,17 +309,19 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
       tmem_st_wait();
       fence_before();
       named_bar_sync(1 + wg, 128);
-      if (wt == 0) {
+      DZ_PHASE(dzph); ++dzph;                // gradient epilogue of this half done
+      if (warp_in_wg == 0) {
         fence_after();
         const uint32_t pt0 = smem_u32(Pt) + (h * NH / 4) * KP * 16;
         for (int ks = 0; ks < NH / 8; ++ks)
-          mma_ts(tZ, tD + ks * 8, make_desc(pt0 + ks * 2 * KP * 16, KP * 16, 128), idesc_z, (h > 0 || ks > 0) ? 1u : 0u);
-        if (h == 1) mma_commit(bar_z);
+          mma_ts_w(tZ, tD + ks * 8, make_desc(pt0 + ks * 2 * KP * 16, KP * 16, 128), idesc_z, (h > 0 || ks > 0) ? 1u : 0u);
+        if (h == 1) mma_commit_w(bar_z);
       }
     }
     mbar_wait(bar_z, ph_z);
     ph_z ^= 1u;
     fence_after();
+    DZ_PHASE(dzph); ++dzph;                  // dZ accumulator complete
     // ---- dz = 2 (rowsum(G) zc - G Pc); zc re-read from the operand tile (tf32-rounded, 2^-12 relative) ----
     float* dst = p.dz + ((size_t)b * K) * HW + pix;
 #pragma unroll
@@ -333,7 +350,9 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
       }
     }
     fence_before();
+    DZ_PHASE(dzph); ++dzph;                  // stored
   }
+  DZ_PHASE(63);
   __syncthreads();
   if (tid < 32) tmem_dealloc(tmem_base, 512);
 }
@@ -1047,6 +1066,9 @@ int launch_bwd(TcBwdParams prm, float* dP, float* dW, const StepFinalize& fin, v
 }  // namespace
 
 #ifdef ADLM_PHASE_CLOCKS
+extern "C" ADLM_API int adlm_debug_dz_phase_clocks(long long* host_out) {
+  return cudaMemcpyFromSymbol(host_out, g_dz_phase, sizeof(long long) * 128) == cudaSuccess ? 0 : -3;
+}
 extern "C" ADLM_API int adlm_debug_dp_phase_clocks(long long* host_out) {
   return cudaMemcpyFromSymbol(host_out, g_dp_phase, sizeof(long long) * 192) == cudaSuccess ? 0 : -3;
 }
