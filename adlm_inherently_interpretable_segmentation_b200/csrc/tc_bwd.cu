@@ -177,11 +177,14 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
   fence_before();
   __syncthreads();
   fence_after();
-  // Inside the step this grid is launched while k_kld still runs (its own-class gradients are first read in the
-  // tile loop below); the dP/dW kernel, which reads nothing this kernel writes, may in turn start as soon as CTAs of
-  // this grid leave their SMs — CTAs with one tile less (529 tiles over 148 CTAs) hand over early.
-  asm volatile("griddepcontrol.wait;" ::: "memory");
-  asm volatile("griddepcontrol.launch_dependents;");
+  // Inside the step this grid is launched while k_kld still runs.  k_kld's output (the own-class gradients) is first
+  // touched after the first tile's operands are written (`waited` below), so staging and that conversion run under its
+  // tail; the dP/dW kernel, which reads nothing this kernel writes, may in turn start as soon as CTAs of this grid
+  // leave their SMs — CTAs with one tile less (529 tiles over 148 CTAs) hand over early.  The dependents are released
+  // only AFTER this grid's own wait: the dP/dW kernel reads k_kld's output too and has no wait of its own (a
+  // programmatic launch orders a grid after its immediate predecessor only), so it must not start before k_kld is
+  // known to be complete (test_step_many_tiles_per_cta_equals_sum_of_single_image_steps caught the other order).
+  bool waited = false;
 
   const uint32_t tmem_base = *tmem_base_s;
   const uint32_t tD = tmem_base + wg * 256;      // D1 half   [128 x NH]
@@ -229,16 +232,20 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
       *reinterpret_cast<float4*>(dLk + ((size_t)c4 * TILE + wt) * 4) = make_float4(v[0], v[1], v[2], v[3]);
     }
     int lab = -1;
-    if (kld && valid) {
-      lab = p.target[m];
-      // pull the pixel's 64-byte line of own-class KLD gradients into L1 before the epilogue needs it
-      asm volatile("prefetch.global.L1 [%0];" ::"l"(p.own_grad + (size_t)m * JMAX));
-    }
+    if (kld && valid) lab = p.target[m];
     const bool lab_ok = lab >= 0 && lab < 32;
     fence_async_smem();
     fence_before();
     named_bar_sync(1 + wg, 128);
     prefetch(tile + stride);
+    if (!waited) {                           // no-ops unless launched with programmatic stream serialisation
+      asm volatile("griddepcontrol.wait;" ::: "memory");
+      asm volatile("griddepcontrol.launch_dependents;");
+      waited = true;
+    }
+    // pull the pixel's 64-byte line of own-class KLD gradients into L1 before the epilogue needs it (after the wait:
+    // a line fetched while k_kld still writes it would sit stale in L1)
+    if (kld && valid) asm volatile("prefetch.global.L1 [%0];" ::"l"(p.own_grad + (size_t)m * JMAX));
     DZ_PHASE(dzph); ++dzph;                  // operands written, next tile's loads issued
 
     float rs = 0.f;
