@@ -410,13 +410,20 @@ def main():
         """n calls of fn between two events on the launching stream, bracketed by barrier + synchronize.  gate_us > 0
         puts a spin kernel of that length in front of the first event, so that the host has the first steps enqueued
         when the timed region starts on the device (every rank starts with a full queue; without it the first launches
-        of a short window run one by one behind the host, and at N > 1 the ranks start skewed by their host jitter)."""
+        of a short window run one by one behind the host, and at N > 1 the ranks start skewed by their host jitter).
+        At N > 1 one extra untimed step follows the gate (reported in `warmup`)."""
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         ctx = sampler if sampler is not None else _Null()
         with ctx:
             if gate_us > 0:
                 torch.cuda._sleep(int(gate_us * 1e-6 * sm_hz))
+                if world > 1:
+                    # one more untimed warm-up step behind the gate: its in-kernel exchange is a device-side barrier, so
+                    # the ranks enter the timed region within microseconds of each other instead of a host barrier's
+                    # ~0.5 ms (which a 20-step window would otherwise charge to its first step)
+                    fn(n)
+            timed.launches_before = _lib.launch_count()
             e0.record()
             for i in range(n):
                 fn(i)
@@ -443,9 +450,8 @@ def main():
     torch.cuda.synchronize()
     gate_us = min(20000.0, max(200.0, 0.5 * host_us * K_steps))
     sampler = ClockSampler(local)
-    l0 = _lib.launch_count()
     ms = timed(step, K_steps, sampler, gate_us=gate_us)
-    launches = _lib.launch_count() - l0
+    launches = _lib.launch_count() - timed.launches_before
     value = world * M * K_steps / (ms * 1e-3) / 1e6
 
     # ---- roofline leg: per-launch CUDA events around the kernel groups, same loop
@@ -577,7 +583,8 @@ def main():
     if rank == 0:
         line = {
             "metric": "proto_head_fwd_bwd_mpixels_per_s", "value": value, "unit": "Mpixels/s", "n_gpus": world,
-            "steps": K_steps, "warmup": W_steps, "ms_per_step": ms / K_steps, "higher_is_better": True,
+            "steps": K_steps, "warmup": W_steps + (1 if world > 1 else 0), "ms_per_step": ms / K_steps,
+            "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": {"fp32": "f32", "tf32": "tf32", "tf32x3": "tf32x3"}[prec],
             "data": "synthetic", "config": config_dict(prec, ring, transport), "clocks": sampler.summary(), "e2e": e2e,
             "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu, "push": push_res,
