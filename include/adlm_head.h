@@ -116,8 +116,9 @@ ADLM_API int adlm_head_fwd(const float* z, int B, int K, int HW,
 /*
  * Head forward for LARGE heads on the tensor cores (model.py:203-283 for any prototype_shape, model.py:54: BASELINE
  * configs[4], 1000 prototypes x 256-d, 100 classes): K <= 256, N <= 1024, C <= 112, single-pass TF32 on centred
- * operands like ADLM_PREC_TF32 of adlm_head_fwd.  Prototypes stream through shared memory in 16 KB chunks fetched by
- * TMA bulk copies from a copy of P / W that a small kernel of the same call stages in `workspace`
+ * operands like ADLM_PREC_TF32 of adlm_head_fwd.  The kernel runs on CTA pairs (clusters of two, tcgen05 cta_group::2):
+ * each CTA keeps one 128-pixel tile, the pair shares every prototype / last-layer chunk, which streams through shared
+ * memory by TMA bulk copies from a copy of P / W that a small kernel of the same call stages in `workspace`
  * (adlm_head_fwd_big_workspace_bytes(K, N, C) bytes, 256-byte aligned; contents need not survive the call).
  * logits [B,HW,C]; dist [B,N,HW] | NULL (at configs[4]'s full size the map is 8.4 GB per image: ask for it on crops
  * only); argmax [B,HW] | NULL.  Larger shapes: ADLM_E_UNSUPPORTED (use adlm_head_fwd with ADLM_PREC_FP32).
