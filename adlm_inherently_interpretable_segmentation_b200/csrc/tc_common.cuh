@@ -231,7 +231,7 @@ __device__ __forceinline__ void mma_pair_commit_w(uint32_t bar) {
 }
 // arrive on the barrier at this CTA's offset `bar` in CTA `cta` of the cluster.  Default semantics (release at CTA
 // scope), as CUTLASS's ClusterBarrier::arrive does: with .release.cluster ptxas puts MEMBAR.ALL.GPU in front of every
-// arrive (~1000 cycles; it serialised the large-head forward's chunk pipeline, gpurun_out/r2_cfg5_sweep4.log).  What a
+// arrive (~1000 cycles; it serialised the large-head forward's chunk pipeline, profiles/r2_cfg5_experiments.log).  What a
 // remote arrival publishes here is either nothing (a relayed TMA completion) or data its own warp wrote and fenced
 // (fence.proxy.async / tcgen05.fence::before_thread_sync) before the arrive.  Waiters use the plain mbar_wait.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t cta) {

@@ -14,7 +14,7 @@
 //   E2    logits / per-pixel argmax from D2 after the last block
 // Why pairs: with one CTA per tile every 128 pixels pulled all of P and W (1.46 MB at cfg5) from L2, 6 GB per
 // 512 x 1024 map; with the MMAs and the epilogue switched off the kernel still took 0.79 of its 1.15 ms, i.e. it sat
-// on the ~7.6 TB/s L2 -> SM ceiling at 42 % of the TF32 matmul peak (gpurun_out/r2_cfg5_sweep3.log).
+// on the ~7.6 TB/s L2 -> SM ceiling at 42 % of the TF32 matmul peak (profiles/r2_cfg5_experiments.log).
 // A pair shares each B operand, which halves that traffic.
 // D1 is double-buffered (MMA1 of block j+1 runs under the epilogue of block j), D2 by tile parity.
 // Warps (per CTA): 0-7 epilogue, 8-11 producers (thread = pixel: coalesced LDG of the NCHW tile, centre, round, |z|^2),
@@ -42,7 +42,7 @@ constexpr int P_CHUNK_FLOATS = (KCH / 4) * NHALF * 4;           // 2048 floats =
 // Chunks travel and are released in GROUPS: one bulk copy, one barrier round and one commit per PG prototype chunks
 // (WG last-layer chunks).  The fixed cost of a ring step (two barrier waits, fence, commit: ~230 cycles that do not
 // overlap the MMAs) is then paid per 8 MMAs instead of per 4; the ring's depth itself does not matter (2 slots run as
-// fast as 16, gpurun_out/r2_cfg5_sweep5.log).
+// fast as 16, profiles/r2_cfg5_experiments.log).
 // PG = 4 (16 MMAs per ring step, two slots of 32 KB) when the depth is a multiple of 128, else 2: 2.93 -> 2.75 ms at
 // cfg5.  The depth is padded to a multiple of PG chunks, so PG = 4 would double the work of a 64-deep head.
 constexpr int WG = 2;
