@@ -249,6 +249,9 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
     DZ_PHASE(dzph); ++dzph;                  // operands written, next tile's loads issued
 
     float rs = 0.f;
+    // (rolled: the tile loop's body is 64 KB of SASS when both halves are expanded, more than the instruction cache
+    // holds — ncu attributes ~19 % of the warps' time to instruction fetch, profiles/r2_ncu_full_step_tf32.txt)
+#pragma unroll 1
     for (int h = 0; h < 2; ++h) {
       // MMAs are issued by the warpgroup's first warp as a whole (one elected lane per instruction): from a single
       // thread every tcgen05.mma costs ~120 cycles of descriptor shuffling into uniform registers (tc_common.cuh)
@@ -331,7 +334,7 @@ __global__ void __launch_bounds__(256, 1) k_tc_bwd_dz(const TcBwdParams p) {
     DZ_PHASE(dzph); ++dzph;                  // dZ accumulator complete
     // ---- dz = 2 (rowsum(G) zc - G Pc); zc re-read from the operand tile (tf32-rounded, 2^-12 relative) ----
     float* dst = p.dz + ((size_t)b * K) * HW + pix;
-#pragma unroll
+#pragma unroll 1
     for (int ch = 0; ch < KP / 16; ++ch) {
       uint32_t r[16];
       tmem_ld16(tZ + lane_field + ch * 16, r);

@@ -221,42 +221,43 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
       if (warp == 8) WS_PHASE(2, 4 + it * 4);
     }
   } else if (warp == 12) {
-    // ================= MMA issuer =================
-    if (lane == 0) {
+    // ================= MMA issuer (whole warp, one elected lane per instruction; one call site per MMA group) ======
+    {
       const uint32_t idesc1 = make_idesc_tf32(TILE, Npad), idesc2 = make_idesc_tf32(TILE, Cpad);
       const int ksteps = (K + 7) >> 3;
       const uint64_t db_p = make_desc(smem_u32(Pk), Npad * 16, 128);
       const uint64_t db_w = make_desc(smem_u32(Wk), Cpad * 16, 128);
       const uint32_t a_kstep = (2u * TILE * 16u) >> 4, p_kstep = (uint32_t)(2 * Npad * 16) >> 4,
                      w_kstep = (uint32_t)(2 * Cpad * 16) >> 4;
-      auto mma2 = [&](int t) {
-        const int b = t & 1, jb = t >> 1;
-        const uint32_t d1 = tD1 + b * Npad, d2 = tD2 + b * Cpad;
-        mbar_wait(bar(B_SREADY + b), (uint32_t)jb & 1u);
-        fence_after();
-        for (int ks = 0; ks < Npad / 8; ++ks)
-          mma_ts(d2, d1 + ks * 8, db_w + (uint64_t)(ks * w_kstep), idesc2, ks > 0 ? 1u : 0u);
-        mma_commit(bar(B_D2FULL + b));
-      };
-      for (int it = 0; it < iters; ++it) {
-        const int a = it & 1, j = it >> 1;
-        const uint64_t da = make_desc(smem_u32(smem + L::abuf(a, Npad, Cpad)), TILE * 16, 128);
-        WS_PHASE(3, 1 + it * 4);
-        mbar_wait(bar(B_FULL + a), (uint32_t)j & 1u);
-        fence_after();
-        WS_PHASE(3, 2 + it * 4);
-        const uint32_t d1 = tD1 + a * Npad;
-#pragma unroll
-        for (int ks = 0; ks < KP / 8; ++ks)
-          if (ks < ksteps)
-            mma_ss(d1, da + (uint64_t)(ks * a_kstep), db_p + (uint64_t)(ks * p_kstep), idesc1, ks > 0 ? 1u : 0u);
-        mma_commit(bar(B_SFREE + a));
-        mma_commit(bar(B_D1FULL + a));
-        WS_PHASE(3, 3 + it * 4);
-        if (it > 0) mma2(it - 1);
-        WS_PHASE(3, 4 + it * 4);
+#pragma unroll 1
+      for (int it = 0; it <= iters; ++it) {
+        if (it < iters) {
+          const int a = it & 1, j = it >> 1;
+          const uint64_t da = make_desc(smem_u32(smem + L::abuf(a, Npad, Cpad)), TILE * 16, 128);
+          if (lane == 0) WS_PHASE(3, 1 + it * 4);
+          mbar_wait(bar(B_FULL + a), (uint32_t)j & 1u);
+          fence_after();
+          if (lane == 0) WS_PHASE(3, 2 + it * 4);
+          const uint32_t d1 = tD1 + a * Npad;
+#pragma unroll 1
+          for (int ks = 0; ks < ksteps; ++ks)
+            mma_ss_w(d1, da + (uint64_t)(ks * a_kstep), db_p + (uint64_t)(ks * p_kstep), idesc1, ks > 0 ? 1u : 0u);
+          mma_commit_w(bar(B_SFREE + a));
+          mma_commit_w(bar(B_D1FULL + a));
+          if (lane == 0) WS_PHASE(3, 3 + it * 4);
+        }
+        if (it > 0) {                            // last layer of the previous tile
+          const int t = it - 1, b = t & 1, jb = t >> 1;
+          const uint32_t d1 = tD1 + b * Npad, d2 = tD2 + b * Cpad;
+          mbar_wait(bar(B_SREADY + b), (uint32_t)jb & 1u);
+          fence_after();
+#pragma unroll 1
+          for (int ks = 0; ks < Npad / 8; ++ks)
+            mma_ts_w(d2, d1 + ks * 8, db_w + (uint64_t)(ks * w_kstep), idesc2, ks > 0 ? 1u : 0u);
+          mma_commit_w(bar(B_D2FULL + b));
+        }
+        if (lane == 0 && it < iters) WS_PHASE(3, 4 + it * 4);
       }
-      if (iters > 0) mma2(iters - 1);
     }
   } else {
     // ================= epilogue warps =================
@@ -404,7 +405,12 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
       }
     };
 
-    for (int it = 0; it < iters; ++it) {
+    // One more trip than there are tiles: trip `it` turns the distances of tile it into similarities (it < iters) and
+    // then takes the logits of tile it-1.  A single call site keeps ONE copy of the logits epilogue in the kernel — the
+    // three warp roles share the instruction cache, and ncu attributes a fifth of the warps' time to instruction fetch.
+#pragma unroll 1
+    for (int it = 0; it <= iters; ++it) {
+      if (it < iters) {
       const int a = it & 1, j = it >> 1;
       const int m = tile_of(it) * TILE + row;
       const bool valid = m < Mi;
@@ -481,11 +487,11 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k_tc_fwd_ws(const TcFwdParams p
       fence_before();
       mbar_arrive(bar(B_SREADY + a));
       if (q == 0) WS_PHASE(half, 3 + it * 4);
+      }
       // logits of the previous tile: the two halves alternate
       if (it > 0 && ((it - 1) & 1) == half) epilogue2(it - 1);
       if (q == 0) WS_PHASE(half, 4 + it * 4);
     }
-    if (iters > 0 && ((iters - 1) & 1) == half) epilogue2(iters - 1);
   }
   fence_before();
   __syncthreads();
