@@ -567,8 +567,8 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
       if (warp == 8) DP_PHASE(0, 4 + it * 8);
     }
   } else if (warp == 12) {
-    // ================= MMA issuer =================
-    if (lane == 0) {
+    // ================= MMA issuer (the whole warp, one elected lane per instruction: tc_common.cuh) =================
+    {
       const uint32_t idesc_t = make_idesc_tf32(128, UW), idesc_p = make_idesc_tf32(128, KP), idesc_w = make_idesc_tf32(128, 32);
       const int ksteps = (K + 7) >> 3;
       // unit j of a tile: block j >> 1, pixel half j & 1
@@ -576,14 +576,14 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
         const int blk = j >> 1, h = j & 1, b = j & 1;
         const uint32_t a0 = smem_u32(PkA) + blk * 128 * 16, b0 = smem_u32(ZkB) + h * UW * 16;
         for (int ks = 0; ks < ksteps; ++ks)
-          mma_ss(tDb(b), make_desc(a0 + ks * 2 * Npad2 * 16, Npad2 * 16, 128), make_desc(b0 + ks * 2 * TILE * 16, TILE * 16, 128),
+          mma_ss_w(tDb(b), make_desc(a0 + ks * 2 * Npad2 * 16, Npad2 * 16, 128), make_desc(b0 + ks * 2 * TILE * 16, TILE * 16, 128),
                  idesc_t, ks > 0 ? 1u : 0u);
         const uint32_t w0 = smem_u32(WtA) + blk * 128 * 16, l0 = smem_u32(dLkB) + h * UW * 16;
         for (int ks = 0; ks < C8 / 8; ++ks)
-          mma_ss(tDb(b) + UW, make_desc(w0 + ks * 2 * Npad2 * 16, Npad2 * 16, 128), make_desc(l0 + ks * 2 * TILE * 16, TILE * 16, 128),
+          mma_ss_w(tDb(b) + UW, make_desc(w0 + ks * 2 * Npad2 * 16, Npad2 * 16, 128), make_desc(l0 + ks * 2 * TILE * 16, TILE * 16, 128),
                  idesc_t, ks > 0 ? 1u : 0u);
-        mma_commit(bar_acc0 + b * 8);
-        if (j == NU - 1) mma_commit(bar_kfree);
+        mma_commit_w(bar_acc0 + b * 8);
+        if (j == NU - 1) mma_commit_w(bar_kfree);
       };
       uint32_t gcnt[2] = {0u, 0u};
       mbar_wait(bar_full, 0u);
@@ -604,10 +604,10 @@ __global__ void __launch_bounds__(DP_THREADS, 1) k_tc_bwd_dp(const TcBwdParams p
           for (int k8 = 0; k8 < UW / 8; ++k8) {
             const int ks = h * (UW / 8) + k8;
             const uint32_t acc = (it > 0 || ks > 0) ? 1u : 0u;
-            mma_ts(tP0 + blk * KP, tDb(b) + k8 * 8, make_desc_sw128(zt0 + (ks >> 2) * KP * 128 + (ks & 3) * 32), idesc_p, acc);
-            mma_ts(tW0 + blk * 32, tDb(b) + UW + k8 * 8, make_desc_sw128(lt0 + (ks >> 2) * 32 * 128 + (ks & 3) * 32), idesc_w, acc);
+            mma_ts_w(tP0 + blk * KP, tDb(b) + k8 * 8, make_desc_sw128(zt0 + (ks >> 2) * KP * 128 + (ks & 3) * 32), idesc_p, acc);
+            mma_ts_w(tW0 + blk * 32, tDb(b) + UW + k8 * 8, make_desc_sw128(lt0 + (ks >> 2) * 32 * 128 + (ks & 3) * 32), idesc_w, acc);
           }
-          if (j == NU - 1) mma_commit(bar_free);
+          if (j == NU - 1) mma_commit_w(bar_free);
           // the distance MMAs two units ahead go into the buffer the accumulate MMAs above read: issue order
           if (j + 2 < NU) {
             issue_d(j + 2);
